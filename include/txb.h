@@ -1,0 +1,136 @@
+/* txb.h -- C ABI of libtxb.so: B200 (sm_100a) kernels for thermoextrap's hot path.
+ *
+ * This is the drop-in boundary.  The reference (usnistgov/thermoextrap, pure
+ * Python) reaches its numeric backend, the third-party package `cmomy`
+ * (numba, CPU), through the call sites cited on each entry point below
+ * (paths relative to /root/reference/src/thermoextrap).  A maintainer binds
+ * these symbols with ctypes; no torch / numpy types
+ * appear in any signature.
+ *
+ * Conventions
+ *  - every function returns an int status (TXB_OK == 0); on failure
+ *    txb_last_error_string() describes the problem.  No exceptions cross
+ *    the boundary.
+ *  - all data pointers are DEVICE pointers (fp64 unless stated), caller
+ *    owned; inputs are const, outputs fully overwritten; the library never
+ *    allocates device memory: scratch comes from the caller's `workspace`
+ *    (size from the matching *_workspace_bytes query).
+ *  - work is enqueued on `stream` (a cudaStream_t passed as void*; NULL =
+ *    legacy default stream); no hidden synchronisation.
+ *  - samples ("rec") are rows: x[nsamp, ldx] row-major, channel ("val")
+ *    fastest, nchan <= ldx.  u is u[nsamp] when ldu == 0, else u[nsamp, ldu]
+ *    (one energy per channel).  w is w[nsamp] or NULL.
+ *  - comoment layout (data.py:1233-1236): out[..., 2, order+1] with
+ *    [0,0]=sum w, [1,0]=<x>, [0,1]=<u>, else <dx^i du^j>.
+ *
+ * Intermediate "pivot sums" (additive across thread blocks, GPUs and streamed
+ * chunks that share one pivot):
+ *    pivot = { cx[nchan], cu[nu] }                nu = 1 (ldu==0) or nchan
+ *    S0[nrep][nu   ][K+1] = sum_s f w (u-cu)^j
+ *    S1[nrep][nchan][K+1] = sum_s f w (x-cx) (u-cu)^j
+ * txb_finalize_f64 re-centres them into the cmomy layout.
+ */
+#ifndef TXB_H
+#define TXB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    TXB_OK = 0,
+    TXB_ERR_BAD_ARG = 1,
+    TXB_ERR_UNSUPPORTED = 2,
+    TXB_ERR_CUDA = 3,
+    TXB_ERR_WORKSPACE = 4,
+    TXB_ERR_OVERFLOW = 5
+};
+
+/* element type of a frequency table */
+enum { TXB_I64 = 0, TXB_I32 = 1, TXB_U16 = 2, TXB_U8 = 3 };
+
+/* finalize modes */
+enum {
+    TXB_MODE_COMOMENTS = 0, /* S0 (order K) + S1 (order K) -> [nchan,2,K+1]           */
+    TXB_MODE_X_IS_U = 1     /* S0 only, order K+1 -> moments_to_comoments(mom=(1,K))  */
+};
+
+int txb_version(void);
+const char* txb_last_error_string(void);
+/* highest supported `order` (u-moment order of the accumulated sums) */
+int txb_max_order(void);
+
+/* ---- pivot (cheap strided pre-pass, <= 1024 rows) ------------------------
+ * pivot[0:nchan] ~ mean x per channel (omitted when x == NULL),
+ * pivot[nchan : nchan+nu] ~ mean u.  Any value near the mean works; sums are
+ * exact for ANY pivot up to rounding, the pivot only controls conditioning. */
+int txb_pivot_f64(const double* x, const double* u, int64_t nsamp, int64_t nchan, int64_t ldx,
+                  int64_t ldu, double* pivot, void* stream);
+
+/* ---- K1: reduce_vals ------------------------------------------------------
+ * replaces cmomy.wrap_reduce_vals(x, u, weight=, mom=(1,order), dim=rec)
+ * data.py:485-489, 528-532, 1183-1203, 1632-1640; lnpi.py:278-282.          */
+size_t txb_reduce_workspace_bytes(int64_t nsamp, int64_t nchan, int order);
+int txb_reduce_sums_f64(const double* x, const double* u, const double* w, int64_t nsamp,
+                        int64_t nchan, int64_t ldx, int64_t ldu, int order, const double* pivot,
+                        double* S0, double* S1, void* workspace, size_t ws_bytes, void* stream);
+/* x == NULL -> u-only sums (S1 untouched).  */
+
+int txb_finalize_f64(const double* S0, const double* S1, const double* pivot, int64_t nrep,
+                     int64_t nchan, int64_t nu, int order, int mode, double* out, void* stream);
+
+/* pivot + sums + finalize in one call; `pivot_scratch` = nchan + nu doubles,
+ * carved from the workspace.  mode TXB_MODE_X_IS_U: x must be NULL and the
+ * sums run to order+1 (data.py:1182-1191).                                    */
+int txb_reduce_vals_f64(const double* x, const double* u, const double* w, int64_t nsamp,
+                        int64_t nchan, int64_t ldx, int64_t ldu, int order, int mode, double* out,
+                        void* workspace, size_t ws_bytes, void* stream);
+
+/* ---- K6: indices -> freq -------------------------------------------------
+ * replaces cmomy's indices_to_freq inside factory_sampler
+ * (data.py:420-421, 1028-1037, 1344-1352, 1782-1789).  Integer, bit-exact.
+ * indices[nrep, nsamp] int64 in [0, ndat);  freq[nrep, ldf] of `freq_dtype`
+ * is zero-filled then incremented.  *status (device int, may be NULL) is set
+ * non-zero on out-of-range indices (1) or narrow-type overflow (2).          */
+int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t nsamp, int64_t ndat,
+                        void* freq, int freq_dtype, int64_t ldf, int* status, void* stream);
+
+/* ---- K2: resample_vals ----------------------------------------------------
+ * replaces cmomy.wrap_resample_vals(x, u, weight=, sampler=, mom=(1,order))
+ * data.py:1354-1366, 1803-1810.  freq[nrep, ldf] is the sampler's table
+ * (int64 unchanged, or a narrowed copy).  Counts must be < 2^31.             */
+size_t txb_resample_workspace_bytes(int64_t nsamp, int64_t nchan, int order, int64_t nrep);
+int txb_resample_sums_f64(const double* x, const double* u, const double* w, int64_t nsamp,
+                          int64_t nchan, int64_t ldx, int64_t ldu, int order, const double* pivot,
+                          const void* freq, int freq_dtype, int64_t nrep, int64_t ldf, double* S0,
+                          double* S1, void* workspace, size_t ws_bytes, void* stream);
+int txb_resample_vals_f64(const double* x, const double* u, const double* w, int64_t nsamp,
+                          int64_t nchan, int64_t ldx, int64_t ldu, int order, int mode,
+                          const void* freq, int freq_dtype, int64_t nrep, int64_t ldf, double* out,
+                          void* workspace, size_t ws_bytes, void* stream);
+
+/* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------
+ * data[nblock, nval, 2, order+1] (cmomy layout).
+ * txb_reduce_data_f64   : CentralMomentsData.reduce(dim)          data.py:996
+ * txb_resample_data_f64 : .resample_and_reduce(sampler)           data.py:1048-1052
+ *                         freq[nrep, nblock] int64                            */
+int txb_reduce_data_f64(const double* data, int64_t nblock, int64_t nval, int order, double* out,
+                        void* stream);
+int txb_resample_data_f64(const double* data, const int64_t* freq, int64_t nrep, int64_t nblock,
+                          int64_t nval, int order, double* out, void* stream);
+
+/* ---- K5: conversions on the (2, order+1) tail -------------------------------
+ * kind 0: central -> raw   (.rmom(),  data.py:845-847)  out[0,0] = 1
+ * kind 1: raw -> central   (convert.moments_type(to="central"), data.py:1108-1115)
+ * kind 2: central -> cmom  (.cmom(),  data.py:850-852)  [0,0]=1,[1,0]=[0,1]=0
+ * nelem = number of (2, order+1) tails.                                       */
+int txb_convert_f64(const double* in, double* out, int64_t nelem, int order, int kind,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TXB_H */

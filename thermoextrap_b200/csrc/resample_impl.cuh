@@ -1,0 +1,104 @@
+// Host-side planning + launch of k_resample for one frequency element type.
+#pragma once
+#include "resample.cuh"
+
+namespace txb {
+
+int launch_sum_parts(const double* ws, int64_t nparts, int64_t n, double* out, cudaStream_t st);
+
+struct RsPlan {
+    int64_t nctile, nreptile, nslab, slab_len;
+};
+
+inline RsPlan rs_plan(int64_t nsamp, int64_t nchan, int64_t nrep, int rt, int st, int ct) {
+    RsPlan p;
+    p.nctile = ct > 0 ? (nchan + ct - 1) / ct : 1;
+    p.nreptile = (nrep + rt - 1) / rt;
+    const int64_t target = (int64_t)sm_count() * 2;
+    int64_t nslab = target / (p.nctile * p.nreptile);
+    if (nslab < 1) nslab = 1;
+    int64_t slab_len = (nsamp + nslab - 1) / nslab;
+    slab_len = (slab_len + st - 1) / st * st;
+    p.slab_len = slab_len;
+    p.nslab = (nsamp + slab_len - 1) / slab_len;
+    return p;
+}
+
+// upper bound on the number of slabs any configuration will use
+inline int64_t rs_max_slabs(int64_t nrep, int64_t nchan_tiles_min) {
+    const int64_t target = (int64_t)sm_count() * 2;
+    int64_t nreptile = (nrep + 127) / 128;
+    int64_t n = target / (nreptile * (nchan_tiles_min < 1 ? 1 : nchan_tiles_min));
+    return n < 1 ? 1 : n;
+}
+
+template <int K, int MODE, int NCG, typename FT>
+int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
+    using C = RsCfg<K, MODE, NCG, FT>;
+    const RsPlan p = rs_plan(a.nsamp, a.nchan, a.nrep, C::RT, C::ST, MODE == RS_WIDE ? C::CT : 0);
+    const bool upc = a.ldu != 0;
+    const int64_t nu = upc ? a.nchan : 1;
+    const int64_t n0 = a.nrep * nu * (K + 1);
+    const int64_t n1 = a.nrep * a.nchan * (K + 1);
+    const bool want0 = (MODE == RS_SCALAR) || upc;
+    const bool want1 = a.x != nullptr;
+    a.ws0 = ws;
+    a.ws1 = ws + (want0 ? p.nslab * n0 : 0);
+    a.slab_len = p.slab_len;
+    const int es = FreqElem<FT>::ES;
+    a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(k_resample<K, MODE, NCG, FT>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM) != cudaSuccess) {
+            set_error("k_resample: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        attr_done = true;
+    }
+    const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
+    k_resample<K, MODE, NCG, FT><<<grid, 256, C::SMEM, st>>>(a);
+    TXB_CUDA_LAUNCH_CHECK("k_resample");
+    int rc = TXB_OK;
+    if (want0) rc = launch_sum_parts(a.ws0, p.nslab, n0, S0, st);
+    if (rc == TXB_OK && want1) rc = launch_sum_parts(a.ws1, p.nslab, n1, S1, st);
+    return rc;
+}
+
+template <typename FT>
+int resample_sums_ft(const double* x, const double* u, const double* w, int64_t nsamp, int64_t nchan,
+                     int64_t ldx, int64_t ldu, int order, const double* pivot, const void* freq,
+                     int64_t nrep, int64_t ldf, double* S0, double* S1, double* ws, cudaStream_t st);
+
+#define TXB_RESAMPLE_FT_IMPL(FT)                                                                     \
+    template <>                                                                                      \
+    int resample_sums_ft<FT>(const double* x, const double* u, const double* w, int64_t nsamp,       \
+                             int64_t nchan, int64_t ldx, int64_t ldu, int order,                     \
+                             const double* pivot, const void* freq, int64_t nrep, int64_t ldf,       \
+                             double* S0, double* S1, double* ws, cudaStream_t st) {                  \
+        RsArgs a;                                                                                    \
+        a.x = x; a.u = u; a.w = w; a.freq = freq; a.pivot = pivot; a.ws0 = a.ws1 = nullptr;          \
+        a.nsamp = nsamp; a.nchan = nchan; a.ldx = ldx; a.ldu = ldu; a.nrep = nrep; a.ldf = ldf;      \
+        a.slab_len = 0; a.aligned = 0;                                                               \
+        int rc = TXB_OK;                                                                             \
+        TXB_DISPATCH_ORDER(order, {                                                                  \
+            if (ldu == 0 && (!x || nchan == 1)) {                                                    \
+                a.nchan = 1;                                                                         \
+                rc = rs_launch<K, RS_SCALAR, 1, FT>(a, S0, S1, ws, st);                              \
+            } else if (ldu == 0) {                                                                   \
+                RsArgs b = a;                                                                        \
+                b.x = nullptr; b.nchan = 1; b.ldx = 0; b.pivot = pivot + nchan;                      \
+                rc = rs_launch<K, RS_SCALAR, 1, FT>(b, S0, nullptr, ws, st);                         \
+                if (rc == TXB_OK)                                                                    \
+                    rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                \
+                                    : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);               \
+            } else {                                                                                 \
+                rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                    \
+                                : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);                   \
+            }                                                                                        \
+        });                                                                                          \
+        return rc;                                                                                   \
+    }
+
+}  // namespace txb

@@ -1,0 +1,4 @@
+#include "resample_impl.cuh"
+namespace txb {
+TXB_RESAMPLE_FT_IMPL(uint16_t)
+}
