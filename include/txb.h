@@ -130,6 +130,10 @@ int txb_resample_data_f64(const double* data, const int64_t* freq, int64_t nrep,
 int txb_convert_f64(const double* in, double* out, int64_t nelem, int order, int kind,
                     void* stream);
 
+/* ---- measurement helper: fp64 FMA peak micro-benchmark (bench.py roofline) ---
+ * scratch: >= 1 device double; *flops (HOST pointer) = flop count of the launch. */
+int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* flops, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,86 @@
+"""ctypes binding of ``libtxb.so`` (declared in ``include/txb.h``).
+
+The product path has NO CPU fallback: if the shared library is missing or a
+CUDA device is unavailable the calls raise.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libtxb.so"
+
+TXB_OK = 0
+TXB_I64, TXB_I32, TXB_U16, TXB_U8 = 0, 1, 2, 3
+MODE_COMOMENTS, MODE_X_IS_U = 0, 1
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_int = C.c_int
+_sz = C.c_size_t
+
+#: name -> (restype, argtypes); mirrors include/txb.h one to one
+SIGNATURES = {
+    "txb_version": (_int, []),
+    "txb_last_error_string": (C.c_char_p, []),
+    "txb_max_order": (_int, []),
+    "txb_pivot_f64": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p]),
+    "txb_reduce_workspace_bytes": (_sz, [_i64, _i64, _int]),
+    "txb_reduce_sums_f64": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _p, _p, _p, _p, _sz, _p]),
+    "txb_finalize_f64": (_int, [_p, _p, _p, _i64, _i64, _i64, _int, _int, _p, _p]),
+    "txb_reduce_vals_f64": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p, _p, _sz, _p]),
+    "txb_indices_to_freq": (_int, [_p, _i64, _i64, _i64, _p, _int, _i64, _p, _p]),
+    "txb_resample_workspace_bytes": (_sz, [_i64, _i64, _int, _i64]),
+    "txb_resample_sums_f64": (
+        _int,
+        [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _p, _p, _int, _i64, _i64, _p, _p, _p, _sz, _p],
+    ),
+    "txb_resample_vals_f64": (
+        _int,
+        [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p, _int, _i64, _i64, _p, _p, _sz, _p],
+    ),
+    "txb_reduce_data_f64": (_int, [_p, _i64, _i64, _int, _p, _p]),
+    "txb_resample_data_f64": (_int, [_p, _p, _i64, _i64, _i64, _int, _p, _p]),
+    "txb_convert_f64": (_int, [_p, _p, _i64, _int, _int, _p]),
+    "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),
+}
+
+_lib = None
+
+
+class TxbError(RuntimeError):
+    """Non-zero status from libtxb."""
+
+
+def lib_path() -> Path:
+    return Path(os.environ.get("TXB_LIBRARY", str(_LIB_PATH)))
+
+
+def load():
+    """Load libtxb.so (once) and attach the signatures."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not path.exists():
+        msg = (
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C thermoextrap_b200/csrc`.  There is no CPU fallback."
+        )
+        raise ImportError(msg)
+    lib = C.CDLL(str(path))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str) -> None:
+    if status != TXB_OK:
+        msg = load().txb_last_error_string().decode(errors="replace")
+        exc = ValueError if status in (1, 2) else TxbError
+        raise exc(f"{what} failed (status {status}): {msg}")

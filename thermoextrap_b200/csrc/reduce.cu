@@ -437,7 +437,7 @@ extern "C" int txb_pivot_f64(const double* x, const double* u, int64_t nsamp, in
 }
 
 static size_t reduce_partials_doubles(int64_t nsamp, int64_t nchan, int order) {
-    const int64_t kp = order + 2;  // x_is_u runs one order higher
+    const int64_t kp = order + 1;
     const int64_t sc = 2 * scalar_blocks(nsamp) * kp;
     const int64_t wd = 2 * max_wide_parts_x_chan(nsamp, nchan < 1 ? 1 : nchan) * kp;
     return (size_t)(sc > wd ? sc : wd);
@@ -446,7 +446,7 @@ static size_t reduce_partials_doubles(int64_t nsamp, int64_t nchan, int order) {
 extern "C" size_t txb_reduce_workspace_bytes(int64_t nsamp, int64_t nchan, int order) {
     if (nchan < 1) nchan = 1;
     const size_t sums = (size_t)(2 * nchan * (order + 2)) + (size_t)(2 * nchan + 2);
-    return align_up((reduce_partials_doubles(nsamp, nchan, order) + sums) * sizeof(double) + 256, 256);
+    return align_up((reduce_partials_doubles(nsamp, nchan, order + 1) + sums) * sizeof(double) + 256, 256);
 }
 
 extern "C" int txb_reduce_sums_f64(const double* x, const double* u, const double* w, int64_t nsamp,

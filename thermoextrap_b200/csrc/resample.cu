@@ -86,7 +86,7 @@ extern "C" int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t
 
 static size_t rs_partials_doubles(int64_t nsamp, int64_t nchan, int order, int64_t nrep) {
     (void)nsamp;
-    const int64_t kp = order + 2;
+    const int64_t kp = order + 1;
     const int64_t ch = nchan < 1 ? 1 : nchan;
     // scalar pass: nslab * nrep * 2 (K+1);  wide pass: nslab * nrep * nchan * (K+1)
     const int64_t sc = rs_max_slabs(nrep, 1) * nrep * 2 * kp;
@@ -97,7 +97,7 @@ static size_t rs_partials_doubles(int64_t nsamp, int64_t nchan, int order, int64
 extern "C" size_t txb_resample_workspace_bytes(int64_t nsamp, int64_t nchan, int order, int64_t nrep) {
     const int64_t ch = nchan < 1 ? 1 : nchan;
     const size_t sums = (size_t)(2 * nrep * ch * (order + 2)) + (size_t)(2 * ch + 2);
-    return align_up((rs_partials_doubles(nsamp, nchan, order, nrep) + sums) * sizeof(double) + 256, 256);
+    return align_up((rs_partials_doubles(nsamp, nchan, order + 1, nrep) + sums) * sizeof(double) + 256, 256);
 }
 
 extern "C" int txb_resample_sums_f64(const double* x, const double* u, const double* w, int64_t nsamp,

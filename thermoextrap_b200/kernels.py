@@ -1,0 +1,261 @@
+"""Device-level wrappers over the C ABI (torch CUDA tensors in, torch CUDA tensors out).
+
+torch is plumbing here: device memory, streams, pinned host staging.  All
+arithmetic happens in ``libtxb.so``.
+"""
+
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import MODE_COMOMENTS, MODE_X_IS_U, TXB_I32, TXB_I64, TXB_U8, TXB_U16, check
+
+_FREQ_DTYPES = {
+    torch.int64: TXB_I64,
+    torch.int32: TXB_I32,
+    torch.uint16: TXB_U16,
+    torch.uint8: TXB_U8,
+}
+
+_workspaces: dict[tuple[int, int], torch.Tensor] = {}
+
+#: incremented by every kernel-launching ABI call (for bench.py's gpu_launches)
+launch_count = 0
+
+
+def device() -> torch.device:
+    """CUDA device of this process (one process per GPU: LOCAL_RANK)."""
+    if not torch.cuda.is_available():
+        msg = "thermoextrap_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback."
+        raise RuntimeError(msg)
+    return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _workspace(nbytes: int, dev: torch.device) -> torch.Tensor:
+    key = (dev.index or 0, torch.cuda.current_stream().cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+def _ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _as_f64(t, dev) -> torch.Tensor:
+    if isinstance(t, np.ndarray):
+        t = torch.from_numpy(np.ascontiguousarray(t, dtype=np.float64))
+    if t.dtype != torch.float64:
+        t = t.to(torch.float64)
+    if t.device != dev:
+        t = t.to(dev, non_blocking=True)
+    return t.contiguous()
+
+
+def _layout(x, u, w, dev):
+    """Normalise (x, u, w) to x[nsamp, nchan] | None, u[nsamp] | u[nsamp, nchan], w[nsamp] | None."""
+    u = _as_f64(u, dev)
+    nsamp = u.shape[0]
+    ldu = 0
+    if u.ndim > 1:
+        u = u.reshape(nsamp, -1)
+        ldu = u.shape[1]
+    val_shape: tuple[int, ...] = ()
+    nchan = 1
+    if x is not None:
+        x = _as_f64(x, dev)
+        if x.shape[0] != nsamp:
+            msg = f"x has {x.shape[0]} samples but u has {nsamp}"
+            raise ValueError(msg)
+        val_shape = tuple(x.shape[1:])
+        x = x.reshape(nsamp, -1)
+        nchan = x.shape[1]
+        if ldu not in (0, nchan):
+            msg = f"u channels {ldu} do not match x channels {nchan}"
+            raise ValueError(msg)
+    elif ldu:
+        nchan = ldu
+        val_shape = tuple(u.shape[1:])
+    if w is not None:
+        w = _as_f64(w, dev)
+        if w.shape != (nsamp,):
+            msg = f"weight must have shape ({nsamp},), got {tuple(w.shape)}"
+            raise ValueError(msg)
+    return x, u, w, nsamp, nchan, ldu, val_shape
+
+
+def reduce_vals(x, u, order: int, w=None, x_is_u: bool = False) -> torch.Tensor:
+    """K1.  Comoments ``[*val, 2, order+1]`` (cmomy layout) of samples along axis 0."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    if x_is_u:
+        x = None
+    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    if x is None and not x_is_u:
+        msg = "x is None requires x_is_u=True"
+        raise ValueError(msg)
+    if nsamp == 0:
+        msg = "cannot reduce zero samples"
+        raise ValueError(msg)
+    out = torch.empty((nchan, 2, order + 1), dtype=torch.float64, device=dev)
+    nb = lib.txb_reduce_workspace_bytes(nsamp, nchan, order)
+    ws = _workspace(nb, dev)
+    mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    with torch.cuda.device(dev):
+        st = lib.txb_reduce_vals_f64(
+            _ptr(x), _ptr(u), _ptr(w), nsamp, nchan, nchan, ldu, order, mode,
+            out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(),
+        )
+    check(st, "txb_reduce_vals_f64")
+    launch_count += 1
+    return out.reshape(*val_shape, 2, order + 1)
+
+
+def indices_to_freq(indices, ndat: int | None = None, dtype: torch.dtype = torch.int64) -> torch.Tensor:
+    """K6.  ``freq[r, i] = #{j: indices[r, j] == i}`` on the device (bit-exact integers)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    if isinstance(indices, np.ndarray):
+        indices = torch.from_numpy(np.ascontiguousarray(indices, dtype=np.int64))
+    indices = indices.to(device=dev, dtype=torch.int64).contiguous()
+    if indices.ndim != 2:
+        msg = "indices must be 2-D [nrep, nsamp]"
+        raise ValueError(msg)
+    nrep, nsamp = indices.shape
+    ndat = nsamp if ndat is None else int(ndat)
+    es = torch.empty((), dtype=dtype).element_size()
+    ldf = (ndat * es + 15) // 16 * 16 // es  # rows 16-byte aligned for the cp.async path
+    buf = torch.empty((nrep, ldf), dtype=dtype, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_indices_to_freq(
+            indices.data_ptr(), nrep, nsamp, ndat, buf.data_ptr(), _FREQ_DTYPES[dtype], ldf,
+            status.data_ptr(), _stream_ptr(),
+        )
+    check(st, "txb_indices_to_freq")
+    launch_count += 1
+    flag = int(status.item())
+    if flag & 1:
+        msg = f"indices out of range [0, {ndat})"
+        raise ValueError(msg)
+    if flag & 2:
+        msg = f"frequency overflow for dtype {dtype}"
+        raise OverflowError(msg)
+    return buf[:, :ndat]
+
+
+def resample_vals(x, u, freq: torch.Tensor, order: int, w=None, x_is_u: bool = False) -> torch.Tensor:
+    """K2.  ``out[rep, *val, 2, order+1]`` = comoments reweighted by ``freq[rep, samp]``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    if x_is_u:
+        x = None
+    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    if isinstance(freq, np.ndarray):
+        freq = torch.from_numpy(freq)
+    if freq.dtype not in _FREQ_DTYPES:
+        msg = f"freq dtype {freq.dtype} not supported (int64, int32, uint16, uint8)"
+        raise TypeError(msg)
+    if freq.device != dev:
+        freq = freq.to(dev)
+    if freq.ndim != 2 or freq.shape[1] != nsamp:
+        msg = f"freq must be [nrep, {nsamp}], got {tuple(freq.shape)}"
+        raise ValueError(msg)
+    if freq.stride(1) != 1:
+        freq = freq.contiguous()
+    nrep, ldf = freq.shape[0], freq.stride(0)
+    out = torch.empty((nrep, nchan, 2, order + 1), dtype=torch.float64, device=dev)
+    nb = lib.txb_resample_workspace_bytes(nsamp, nchan, order, nrep)
+    ws = _workspace(nb, dev)
+    mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    with torch.cuda.device(dev):
+        st = lib.txb_resample_vals_f64(
+            _ptr(x), _ptr(u), _ptr(w), nsamp, nchan, nchan, ldu, order, mode,
+            freq.data_ptr(), _FREQ_DTYPES[freq.dtype], nrep, ldf,
+            out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(),
+        )
+    check(st, "txb_resample_vals_f64")
+    launch_count += 1
+    return out.reshape(nrep, *val_shape, 2, order + 1)
+
+
+def _tails(data, dev):
+    data = _as_f64(data, dev)
+    if data.ndim < 2 or data.shape[-2] != 2:
+        msg = f"comoment array must end in (2, order+1), got {tuple(data.shape)}"
+        raise ValueError(msg)
+    return data, data.shape[-1] - 1
+
+
+def reduce_data(data) -> torch.Tensor:
+    """K4.  Merge blocks along axis 0: ``[nblock, *val, 2, k+1] -> [*val, 2, k+1]``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    data, order = _tails(data, dev)
+    nblock = data.shape[0]
+    val_shape = tuple(data.shape[1:-2])
+    nval = int(np.prod(val_shape, dtype=np.int64))
+    out = torch.empty((*val_shape, 2, order + 1), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_reduce_data_f64(data.data_ptr(), nblock, nval, order, out.data_ptr(), _stream_ptr())
+    check(st, "txb_reduce_data_f64")
+    launch_count += 1
+    return out
+
+
+def resample_data(data, freq) -> torch.Tensor:
+    """K3.  ``out[rep] = merge(data[block] * freq[rep, block])``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    data, order = _tails(data, dev)
+    if isinstance(freq, np.ndarray):
+        freq = torch.from_numpy(freq)
+    freq = freq.to(device=dev, dtype=torch.int64).contiguous()
+    nblock = data.shape[0]
+    if freq.ndim != 2 or freq.shape[1] != nblock:
+        msg = f"freq must be [nrep, {nblock}], got {tuple(freq.shape)}"
+        raise ValueError(msg)
+    nrep = freq.shape[0]
+    val_shape = tuple(data.shape[1:-2])
+    nval = int(np.prod(val_shape, dtype=np.int64))
+    out = torch.empty((nrep, *val_shape, 2, order + 1), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_resample_data_f64(
+            data.data_ptr(), freq.data_ptr(), nrep, nblock, nval, order, out.data_ptr(), _stream_ptr()
+        )
+    check(st, "txb_resample_data_f64")
+    launch_count += 1
+    return out
+
+
+CONVERT_CENTRAL_TO_RAW, CONVERT_RAW_TO_CENTRAL, CONVERT_CENTRAL_TO_CMOM = 0, 1, 2
+
+
+def convert(data, kind: int) -> torch.Tensor:
+    """K5 on ``[..., 2, k+1]`` tails."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    data, order = _tails(data, dev)
+    out = torch.empty_like(data)
+    nelem = data.numel() // (2 * (order + 1))
+    with torch.cuda.device(dev):
+        st = lib.txb_convert_f64(data.data_ptr(), out.data_ptr(), nelem, order, kind, _stream_ptr())
+    check(st, "txb_convert_f64")
+    launch_count += 1
+    return out

@@ -1,0 +1,122 @@
+"""Kernel-level timing on the GPU box (development tool; bench.py is the judged harness).
+
+usage: python tools/kbench.py [reduce|resample|hist|peak ...]
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import json
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import torch
+
+from thermoextrap_b200 import _lib
+from thermoextrap_b200 import kernels as K
+
+
+def timeit(fn, warm=3, rep=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(rep):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e-3)
+    return min(ts), sorted(ts)[len(ts) // 2]
+
+
+def peak():
+    lib = _lib.load()
+    scratch = torch.zeros(8, dtype=torch.float64, device="cuda")
+    fl = C.c_double()
+    out = {}
+    for bps in (4, 8):
+        def run():
+            _lib.check(lib.txb_fp64_peak_launch(20000, bps, scratch.data_ptr(), C.byref(fl), None), "peak")
+        t, _ = timeit(run)
+        out[f"fp64_tflops_bps{bps}"] = fl.value / t / 1e12
+    print(json.dumps({"peak": out}))
+
+
+def reduce():
+    for n, nv, order in [(100_000_000, 0, 8), (100_000_000, 0, 6), (100_000_000, 0, 2), (4_000_000, 64, 6), (400_000, 2000, 4), (16_000_000, 16, 6)]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+        x = torch.randn((n, nv) if nv else (n,), dtype=torch.float64, device="cuda") * 0.02 + 1e-3 * (u[:, None] if nv else u)
+        t, tm = timeit(lambda: K.reduce_vals(x, u, order))
+        byts = 8 * n * (max(nv, 1) + 1)
+        print(json.dumps({"reduce": [n, nv, order], "ms": t * 1e3, "ms_med": tm * 1e3, "GBs": byts / t / 1e9, "samples_per_s": n / t}))
+        del x, u
+    # x_is_u wide (lnPi shape)
+    n, nv, order = 400_000, 2000, 4
+    u = torch.randn((n, nv), dtype=torch.float64, device="cuda")
+    t, tm = timeit(lambda: K.reduce_vals(None, u, order, x_is_u=True))
+    print(json.dumps({"reduce_x_is_u": [n, nv, order], "ms": t * 1e3, "GBs": 8 * n * nv / t / 1e9}))
+
+
+def reduce_big():
+    for n, nv, order in [(1_000_000_000, 0, 8), (1_000_000_000, 0, 2), (50_000_000, 64, 6)]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda")
+        u.mul_(5.3).add_(175)
+        x = torch.randn((n, nv) if nv else (n,), dtype=torch.float64, device="cuda")
+        t, tm = timeit(lambda: K.reduce_vals(x, u, order))
+        byts = 8 * n * (max(nv, 1) + 1)
+        print(json.dumps({"reduce_big": [n, nv, order], "ms": t * 1e3, "ms_med": tm * 1e3, "GBs": byts / t / 1e9, "samples_per_s": n / t}))
+        del x, u
+
+
+def ncu_case():
+    """small fixed sequence for the ncu launch list"""
+    n = 100_000_000
+    u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+    x = torch.randn(n, dtype=torch.float64, device="cuda")
+    K.reduce_vals(x, u, 8)
+    xw = torch.randn((4_000_000, 64), dtype=torch.float64, device="cuda")
+    K.reduce_vals(xw, u[:4_000_000], 6)
+    freq = torch.randint(0, 4, (128, 10_000_000), device="cuda", dtype=torch.int32)
+    K.resample_vals(x[:10_000_000], u[:10_000_000], freq.to(torch.int64), 8)
+    K.resample_vals(x[:10_000_000], u[:10_000_000], freq.to(torch.uint8), 8)
+    K.resample_vals(xw[:1_000_000], u[:1_000_000], freq[:, :1_000_000].to(torch.uint8), 6)
+    torch.cuda.synchronize()
+
+
+def resample():
+    for n, nv, order, nrep, dt in [
+        (10_000_000, 0, 8, 128, torch.int64),
+        (10_000_000, 0, 8, 128, torch.int32),
+        (10_000_000, 0, 8, 128, torch.uint8),
+        (10_000_000, 0, 8, 1024, torch.uint8),
+        (10_000_000, 0, 2, 128, torch.int64),
+        (1_000_000, 64, 6, 128, torch.uint8),
+        (1_000_000, 64, 6, 1024, torch.uint8),
+    ]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+        x = torch.randn((n, nv) if nv else (n,), dtype=torch.float64, device="cuda") * 0.02 + 1e-3 * (u[:, None] if nv else u)
+        freq = torch.randint(0, 4, (nrep, n), device="cuda", dtype=torch.int32).to(dt)
+        t, tm = timeit(lambda: K.resample_vals(x, u, freq, order), warm=2, rep=3)
+        ncol = (order + 1) * (max(nv, 1) + 1)
+        flops = 2.0 * nrep * n * ncol
+        print(json.dumps({"resample": [n, nv, order, nrep, str(dt)], "ms": t * 1e3, "ms_med": tm * 1e3,
+                          "TFLOPs": flops / t / 1e12, "freq_GBs": freq.element_size() * nrep * n / t / 1e9,
+                          "reps_per_s": nrep / t}))
+        del x, u, freq
+
+
+def hist():
+    for nrep, n, dt in [(64, 10_000_000, torch.int64), (64, 10_000_000, torch.int32), (64, 10_000_000, torch.uint8)]:
+        idx = torch.randint(0, n, (nrep, n), device="cuda", dtype=torch.int64)
+        t, tm = timeit(lambda: K.indices_to_freq(idx, n, dtype=dt), warm=2, rep=3)
+        print(json.dumps({"hist": [nrep, n, str(dt)], "ms": t * 1e3, "draws_per_s": nrep * n / t, "idx_GBs": 8 * nrep * n / t / 1e9}))
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["peak", "reduce", "resample", "hist"]
+    for w in which:
+        globals()[w]()
