@@ -112,6 +112,24 @@ int txb_resample_vals_f64(const double* x, const double* u, const double* w, int
                           const void* freq, int freq_dtype, int64_t nrep, int64_t ldf, double* out,
                           void* workspace, size_t ws_bytes, void* stream);
 
+/* ---- K2 (index form): bootstrap straight from the sampler's index table ------
+ * scalar x only (x[ndat] with stride ldx, or x == NULL for x_is_u): one random
+ * 16-byte gather per draw instead of one atomic per draw + a contraction.
+ * indices[nrep, ldi] int64, ndraw draws per replicate, values in [0, ndat)
+ * (data.py:420-431 gather semantics == data.py:1803-1810 freq semantics,
+ * pinned by tests/test_data.py:94-112).  *status (device int, may be NULL) is
+ * set to 1 when an index is out of range.  nrep <= 65535 per call.             */
+size_t txb_resample_indices_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t ndraw);
+int txb_resample_indices_sums_f64(const double* x, const double* u, const double* w, int64_t ndat,
+                                  int64_t ldx, int order, const double* pivot,
+                                  const int64_t* indices, int64_t nrep, int64_t ndraw, int64_t ldi,
+                                  double* S0, double* S1, int* status, void* workspace,
+                                  size_t ws_bytes, void* stream);
+int txb_resample_indices_f64(const double* x, const double* u, const double* w, int64_t ndat,
+                             int64_t ldx, int order, int mode, const int64_t* indices,
+                             int64_t nrep, int64_t ndraw, int64_t ldi, double* out, int* status,
+                             void* workspace, size_t ws_bytes, void* stream);
+
 /* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------
  * data[nblock, nval, 2, order+1] (cmomy layout).
  * txb_reduce_data_f64   : CentralMomentsData.reduce(dim)          data.py:996

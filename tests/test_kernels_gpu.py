@@ -198,6 +198,42 @@ def test_resample_identity_freq_equals_reduce(K):
     assert np.array_equal(a[0], a[1])
 
 
+@pytest.mark.parametrize("n,ndraw,nrep,order", [(1000, 1000, 7, 8), (4099, 4099, 13, 3), (100_000, 100_000, 5, 6), (501, 1203, 3, 5)])
+def test_resample_indices_scalar(K, n, ndraw, nrep, order):
+    x, u, rng = make(n, 0, seed=13)
+    idx = rng.choice(n, (nrep, ndraw), replace=True)
+    out = K.resample_indices(x, u, idx, order).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, order, idx)
+    assert out.shape == ref.shape
+    scale = oc.tolerance_scale(x, u, order)
+    assert relerr(out, ref, scale) < TOL
+    # same answer through the frequency-table path (tests/test_data.py:94-112)
+    if ndraw == n:
+        viaf = K.resample_vals(x, u, K.indices_to_freq(idx, n), order).cpu().numpy()
+        assert relerr(viaf, ref, scale) < TOL
+
+
+def test_resample_indices_weighted_x_is_u_and_errors(K):
+    x, u, rng = make(3000, 0, seed=14)
+    w = rng.random(3000)
+    idx = rng.choice(3000, (4, 3000), replace=True)
+    out = K.resample_indices(x, u, idx, 6, w=w).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, 6, idx, w=w)
+    assert relerr(out, ref, oc.tolerance_scale(x, u, 6)) < TOL
+    out = K.resample_indices(None, u, idx, 5, x_is_u=True).cpu().numpy()
+    ref = oc.resample_vals_gather(u, u, 5, idx)
+    assert relerr(out, ref, oc.tolerance_scale(u, u, 5)) < TOL
+    bad = idx.copy()
+    bad[2, 17] = 3000
+    with pytest.raises(ValueError):
+        K.resample_indices(x, u, bad, 6)
+    # odd row pitch -> unaligned rows take the scalar-load path
+    idx2 = rng.choice(3000, (3, 2999), replace=True)
+    out = K.resample_indices(x, u, idx2, 4).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, 4, idx2)
+    assert relerr(out, ref, oc.tolerance_scale(x, u, 4)) < TOL
+
+
 # ------------------------------------------------------------------ K3/K4/K5
 def test_reduce_and_resample_data(K):
     x, u, rng = make(1000, 3, seed=11)

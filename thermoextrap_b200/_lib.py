@@ -41,6 +41,15 @@ SIGNATURES = {
         _int,
         [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p, _int, _i64, _i64, _p, _p, _sz, _p],
     ),
+    "txb_resample_indices_workspace_bytes": (_sz, [_i64, _int, _i64, _i64]),
+    "txb_resample_indices_sums_f64": (
+        _int,
+        [_p, _p, _p, _i64, _i64, _int, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _sz, _p],
+    ),
+    "txb_resample_indices_f64": (
+        _int,
+        [_p, _p, _p, _i64, _i64, _int, _int, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p],
+    ),
     "txb_reduce_data_f64": (_int, [_p, _i64, _i64, _int, _p, _p]),
     "txb_resample_data_f64": (_int, [_p, _p, _i64, _i64, _i64, _int, _p, _p]),
     "txb_convert_f64": (_int, [_p, _p, _i64, _int, _int, _p]),

@@ -33,21 +33,26 @@ int sm_count() {
 }
 
 // ---------------------------------------------------------------- pivot
-// Column means over <= 1024 strided rows.  block = 32 columns x 8 row phases.
+// Column means over <= 256 strided rows.  block = 32 columns x 8 row phases,
+// 32 independent loads per thread (one latency round).
 __global__ void __launch_bounds__(256) k_colmean_sample(const double* __restrict__ a,
                                                         int64_t nsamp, int64_t ncol, int64_t ld,
                                                         double* __restrict__ out) {
     __shared__ double sm[8][33];
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int64_t c = (int64_t)blockIdx.x * 32 + lane;
-    const int64_t nrows = nsamp < 1024 ? nsamp : 1024;
+    const int nrows = nsamp < 256 ? (int)nsamp : 256;
     double acc = 0.0;
     if (c < ncol) {
-#pragma unroll 4
-        for (int64_t i = wrp; i < nrows; i += 8) {
-            const int64_t r = (int64_t)(((__int128)i * nsamp) / nrows);
-            acc += a[r * ld + c];
+        double v[32];
+#pragma unroll
+        for (int q = 0; q < 32; ++q) {
+            const int i = wrp + 8 * q;
+            const int64_t r = ((int64_t)i * nsamp) / nrows;
+            v[q] = i < nrows ? a[r * ld + c] : 0.0;
         }
+#pragma unroll
+        for (int q = 0; q < 32; ++q) acc += v[q];
     }
     sm[wrp][lane] = acc;
     __syncthreads();
@@ -175,8 +180,17 @@ __global__ void __launch_bounds__(256)
     const int lane_c = tid & (lanes_c - 1);
     const int rowslot = tid / lanes_c;
     const int rows = 256 / lanes_c;
-    const int64_t c0 = ((int64_t)blockIdx.x * lanes_c + lane_c) * CPT;
-    const bool active = c0 < nchan;
+    // channel of element cc of this thread: pairs are interleaved across lanes so that one
+    // LDG.128 instruction reads 32 B * lanes_c contiguous bytes per row (full sectors)
+    const int64_t tile_base = (int64_t)blockIdx.x * lanes_c * CPT;
+    auto chan_of = [&](int cc) -> int64_t {
+        return CPT == 1 ? tile_base + lane_c
+                        : tile_base + (int64_t)(cc >> 1) * 2 * lanes_c + 2 * lane_c + (cc & 1);
+    };
+    bool act[CPT];
+    bool active = false;
+#pragma unroll
+    for (int cc = 0; cc < CPT; ++cc) act[cc] = chan_of(cc) < nchan, active = active || act[cc];
     const bool has_w = (w != nullptr);
 
     const int64_t rows_per_slab = (nsamp + gridDim.y - 1) / gridDim.y;
@@ -186,8 +200,8 @@ __global__ void __launch_bounds__(256)
     double cx[CPT], cu[CPT];
 #pragma unroll
     for (int cc = 0; cc < CPT; ++cc) {
-        cx[cc] = (HAS_X && active) ? pivot[c0 + cc] : 0.0;
-        cu[cc] = UPC ? (active ? pivot[(HAS_X ? nchan : 0) + c0 + cc] : 0.0) : pivot[nchan];
+        cx[cc] = (HAS_X && act[cc]) ? pivot[chan_of(cc)] : 0.0;
+        cu[cc] = UPC ? (act[cc] ? pivot[(HAS_X ? nchan : 0) + chan_of(cc)] : 0.0) : pivot[nchan];
     }
     double s0[UPC ? CPT : 1][K + 1], s1[HAS_X ? CPT : 1][K + 1];
 #pragma unroll
@@ -198,13 +212,15 @@ __global__ void __launch_bounds__(256)
         for (int cc = 0; cc < (HAS_X ? CPT : 1); ++cc) s1[cc][j] = 0.0;
     }
 
+    // p = row base pointer
     auto load_vec = [&](const double* p, double (&v)[CPT]) {
         if (CPT == 1) {
-            v[0] = ldg_stream1(p);
+            v[0] = ldg_stream1(p + chan_of(0));
         } else {
 #pragma unroll
             for (int h = 0; h < CPT / 2; ++h) {
-                const double2 t = ldg_stream2(p + 2 * h);
+                double2 t = make_double2(0.0, 0.0);
+                if (act[2 * h]) t = ldg_stream2(p + chan_of(2 * h));
                 v[2 * h] = t.x;
                 v[2 * h + 1] = t.y;
             }
@@ -251,8 +267,8 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
             for (int q = 0; q < UNR; ++q) {
                 const int64_t rr = r + (int64_t)q * rows;
-                if (HAS_X) load_vec(x + rr * ldx + c0, xv[q]);
-                if (UPC) load_vec(u + rr * ldu + c0, uv[q]);
+                if (HAS_X) load_vec(x + rr * ldx, xv[q]);
+                if (UPC) load_vec(u + rr * ldu, uv[q]);
                 else uv[q][0] = __ldg(u + rr);
                 wv[q] = has_w ? __ldg(w + rr) : 1.0;
             }
@@ -261,8 +277,8 @@ __global__ void __launch_bounds__(256)
         }
         for (; r < r_end; r += rows) {
             double xv[CPT], uv[CPT];
-            if (HAS_X) load_vec(x + r * ldx + c0, xv);
-            if (UPC) load_vec(u + r * ldu + c0, uv);
+            if (HAS_X) load_vec(x + r * ldx, xv);
+            if (UPC) load_vec(u + r * ldu, uv);
             else uv[0] = __ldg(u + r);
             body(xv, uv, has_w ? __ldg(w + r) : 1.0);
         }
@@ -270,51 +286,66 @@ __global__ void __launch_bounds__(256)
 
     // block merge over the row slots that share a channel lane
     __shared__ double sm[256];
-    auto block_merge = [&](double v, double* dst) {
+    auto block_merge = [&](double v, double* dst, bool ok) {
         sm[tid] = v;
         __syncthreads();
-        if (tid < lanes_c && active) {
+        if (tid < lanes_c && ok) {
             double t = 0.0;
             for (int rs = 0; rs < rows; ++rs) t += sm[rs * lanes_c + tid];
             *dst = t;
         }
         __syncthreads();
     };
-    const int64_t base = ((int64_t)blockIdx.y * nchan + c0) * (K + 1);
 #pragma unroll
     for (int cc = 0; cc < CPT; ++cc) {
+        const int64_t base = ((int64_t)blockIdx.y * nchan + chan_of(cc)) * (K + 1);
 #pragma unroll
         for (int j = 0; j <= K; ++j) {
-            if (UPC) block_merge(s0[cc][j], ws0 + base + (int64_t)cc * (K + 1) + j);
-            if (HAS_X) block_merge(s1[cc][j], ws1 + base + (int64_t)cc * (K + 1) + j);
+            if (UPC) block_merge(s0[cc][j], ws0 + base + j, act[cc]);
+            if (HAS_X) block_merge(s1[cc][j], ws1 + base + j, act[cc]);
         }
     }
 }
 
-// out[i] = sum_p ws[p][i]  (fixed order -> deterministic)
+// out[i] = sum_p ws[p][i]  (fixed association -> deterministic).
+// block = out_l outputs x (256 / out_l) part phases; phases merged through smem.
 __global__ void __launch_bounds__(256) k_sum_parts(const double* __restrict__ ws, int64_t nparts,
-                                                   int64_t n, double* __restrict__ out) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+                                                   int64_t n, int out_l, double* __restrict__ out) {
+    __shared__ double sm[256];
+    const int tid = threadIdx.x;
+    const int lo = tid & (out_l - 1);
+    const int ph = tid / out_l;
+    const int nph = 256 / out_l;
+    const int64_t i = (int64_t)blockIdx.x * out_l + lo;
     double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
-    int64_t p = 0;
-    for (; p + 3 < nparts; p += 4) {
-        t0 += ws[p * n + i];
-        t1 += ws[(p + 1) * n + i];
-        t2 += ws[(p + 2) * n + i];
-        t3 += ws[(p + 3) * n + i];
+    if (i < n) {
+        int64_t p = ph;
+        for (; p + 3 * nph < nparts; p += 4 * nph) {
+            t0 += ws[p * n + i];
+            t1 += ws[(p + nph) * n + i];
+            t2 += ws[(p + 2 * nph) * n + i];
+            t3 += ws[(p + 3 * nph) * n + i];
+        }
+        for (; p < nparts; p += nph) t0 += ws[p * n + i];
     }
-    for (; p < nparts; ++p) t0 += ws[p * n + i];
-    out[i] = (t0 + t1) + (t2 + t3);
+    sm[tid] = (t0 + t1) + (t2 + t3);
+    __syncthreads();
+    if (ph == 0 && i < n) {
+        double t = 0.0;
+        for (int k = 0; k < nph; ++k) t += sm[k * out_l + lo];
+        out[i] = t;
+    }
 }
 
 int launch_sum_parts(const double* ws, int64_t nparts, int64_t n, double* out, cudaStream_t st) {
     if (n <= 0) return TXB_OK;
-    k_sum_parts<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ws, nparts, n, out);
+    // few outputs / many parts -> more part phases per block
+    int out_l = 32;
+    while (out_l > 1 && (out_l / 2 >= n || (n <= 4096 && nparts >= 64 && out_l > 8))) out_l >>= 1;
+    k_sum_parts<<<(unsigned)((n + out_l - 1) / out_l), 256, 0, st>>>(ws, nparts, n, out_l, out);
     TXB_CUDA_LAUNCH_CHECK("k_sum_parts");
     return TXB_OK;
 }
-
 
 // ---------------------------------------------------------------- planning
 struct WidePlan {

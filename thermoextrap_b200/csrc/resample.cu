@@ -10,16 +10,16 @@ namespace txb {
 template <typename FT>
 __global__ void __launch_bounds__(256)
     k_indices_to_freq(const int64_t* __restrict__ idx, int64_t nrep, int64_t nsamp, int64_t ndat,
-                      FT* __restrict__ freq, int64_t ldf, int* __restrict__ status) {
-    const int64_t total = nrep * nsamp;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+                      FT* __restrict__ freq, int64_t ldf, int64_t slab_len, int* __restrict__ status) {
+    const int64_t r = blockIdx.y;
+    const int64_t j0 = (int64_t)blockIdx.x * slab_len;
+    const int64_t j1 = min(nsamp, j0 + slab_len);
+    const int64_t* row = idx + r * nsamp;
     int bad = 0;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-        const int64_t r = e / nsamp;
-        const int64_t i = idx[e];
-        if (i < 0 || i >= ndat) {
+    auto bump = [&](int64_t i) {
+        if ((uint64_t)i >= (uint64_t)ndat) {
             bad |= 1;
-            continue;
+            return;
         }
         const int64_t off = r * ldf + i;
         if (sizeof(FT) == 8) {
@@ -36,7 +36,17 @@ __global__ void __launch_bounds__(256)
             const unsigned old = atomicAdd(word, 1u << sh);
             if (((old >> sh) & MASK) == MASK) bad |= 2;
         }
+    };
+    constexpr int UNR = 8;
+    int64_t j = j0 + threadIdx.x;
+    for (; j + (UNR - 1) * 256 < j1; j += UNR * 256) {
+        int64_t ii[UNR];
+#pragma unroll
+        for (int t = 0; t < UNR; ++t) ii[t] = __ldcs(row + j + t * 256);
+#pragma unroll
+        for (int t = 0; t < UNR; ++t) bump(ii[t]);
     }
+    for (; j < j1; j += 256) bump(row[j]);
     if (bad && status) atomicOr(status, bad);
 }
 
@@ -69,16 +79,21 @@ extern "C" int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
-    const int64_t total = nrep * nsamp;
-    if (total == 0) return TXB_OK;
-    int64_t nb = (total + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 16;
-    if (nb > cap) nb = cap;
+    if (nrep * nsamp == 0) return TXB_OK;
+    TXB_CHECK_ARG(nrep <= 65535, "txb_indices_to_freq: nrep must be <= 65535 per call");
+    // many slabs per row: rows are processed (almost) one at a time, so the row being
+    // incremented stays L2-resident
+    int64_t ns = (int64_t)sm_count() * 4;
+    const int64_t maxs = (nsamp + 2047) / 2048;
+    if (ns > maxs) ns = maxs;
+    if (ns < 1) ns = 1;
+    const int64_t slab_len = (nsamp + ns - 1) / ns;
+    const dim3 grid((unsigned)((nsamp + slab_len - 1) / slab_len), (unsigned)nrep);
     switch (freq_dtype) {
-        case TXB_I64: k_indices_to_freq<int64_t><<<(unsigned)nb, 256, 0, st>>>(indices, nrep, nsamp, ndat, (int64_t*)freq, ldf, status); break;
-        case TXB_I32: k_indices_to_freq<int32_t><<<(unsigned)nb, 256, 0, st>>>(indices, nrep, nsamp, ndat, (int32_t*)freq, ldf, status); break;
-        case TXB_U16: k_indices_to_freq<uint16_t><<<(unsigned)nb, 256, 0, st>>>(indices, nrep, nsamp, ndat, (uint16_t*)freq, ldf, status); break;
-        default:      k_indices_to_freq<uint8_t><<<(unsigned)nb, 256, 0, st>>>(indices, nrep, nsamp, ndat, (uint8_t*)freq, ldf, status); break;
+        case TXB_I64: k_indices_to_freq<int64_t><<<grid, 256, 0, st>>>(indices, nrep, nsamp, ndat, (int64_t*)freq, ldf, slab_len, status); break;
+        case TXB_I32: k_indices_to_freq<int32_t><<<grid, 256, 0, st>>>(indices, nrep, nsamp, ndat, (int32_t*)freq, ldf, slab_len, status); break;
+        case TXB_U16: k_indices_to_freq<uint16_t><<<grid, 256, 0, st>>>(indices, nrep, nsamp, ndat, (uint16_t*)freq, ldf, slab_len, status); break;
+        default:      k_indices_to_freq<uint8_t><<<grid, 256, 0, st>>>(indices, nrep, nsamp, ndat, (uint8_t*)freq, ldf, slab_len, status); break;
     }
     TXB_CUDA_LAUNCH_CHECK("k_indices_to_freq");
     return TXB_OK;

@@ -192,6 +192,50 @@ def resample_vals(x, u, freq: torch.Tensor, order: int, w=None, x_is_u: bool = F
     return out.reshape(nrep, *val_shape, 2, order + 1)
 
 
+def resample_indices(x, u, indices, order: int, w=None, x_is_u: bool = False) -> torch.Tensor:
+    """K2, index form (scalar x): ``out[rep] = comoments(x[idx[rep]], u[idx[rep]])``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    if x_is_u:
+        x = None
+    x, u, w, ndat, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    if nchan != 1 or ldu != 0:
+        msg = "resample_indices handles scalar x only; use indices_to_freq + resample_vals"
+        raise ValueError(msg)
+    if isinstance(indices, np.ndarray):
+        indices = torch.from_numpy(np.ascontiguousarray(indices, dtype=np.int64))
+    indices = indices.to(device=dev, dtype=torch.int64)
+    if indices.ndim != 2:
+        msg = "indices must be 2-D [nrep, nsamp]"
+        raise ValueError(msg)
+    if indices.stride(1) != 1:
+        indices = indices.contiguous()
+    nrep_total, ndraw = indices.shape
+    out = torch.empty((nrep_total, 1, 2, order + 1), dtype=torch.float64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    flag = 0
+    with torch.cuda.device(dev):
+        for r0 in range(0, nrep_total, 32768):
+            sub = indices[r0 : r0 + 32768]
+            nrep = sub.shape[0]
+            nb = lib.txb_resample_indices_workspace_bytes(ndat, order, nrep, ndraw)
+            ws = _workspace(nb, dev)
+            st = lib.txb_resample_indices_f64(
+                _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, sub.data_ptr(), nrep, ndraw,
+                sub.stride(0), out[r0:].data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(),
+                _stream_ptr(),
+            )
+            check(st, "txb_resample_indices_f64")
+            launch_count += 1
+            flag |= int(status.item())
+    if flag:
+        msg = f"indices out of range [0, {ndat})"
+        raise ValueError(msg)
+    return out.reshape(nrep_total, *val_shape, 2, order + 1)
+
+
 def _tails(data, dev):
     data = _as_f64(data, dev)
     if data.ndim < 2 or data.shape[-2] != 2:

@@ -87,6 +87,25 @@ def ncu_case():
     torch.cuda.synchronize()
 
 
+def ncu_full():
+    """one launch of each hot kernel for `ncu --set full`"""
+    n = 10_000_000
+    u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+    x = torch.randn(n, dtype=torch.float64, device="cuda")
+    idx = torch.randint(0, n, (16, n), device="cuda", dtype=torch.int64)
+    K.resample_indices(x, u, idx, 8)
+    f8 = K.indices_to_freq(idx, n, dtype=torch.uint8)
+    f8 = f8.repeat(8, 1)
+    K.resample_vals(x, u, f8, 8)
+    K.resample_vals(x, u, f8.to(torch.int64), 8)
+    xw = torch.randn((2_000_000, 64), dtype=torch.float64, device="cuda")
+    K.reduce_vals(xw, u[:2_000_000], 6)
+    K.resample_vals(xw[:500_000], u[:500_000], f8[:, :500_000].contiguous(), 6)
+    xs = torch.randn(100_000_000, dtype=torch.float64, device="cuda")
+    K.reduce_vals(xs, xs, 8)
+    torch.cuda.synchronize()
+
+
 def resample():
     for n, nv, order, nrep, dt in [
         (10_000_000, 0, 8, 128, torch.int64),
@@ -107,6 +126,17 @@ def resample():
                           "TFLOPs": flops / t / 1e12, "freq_GBs": freq.element_size() * nrep * n / t / 1e9,
                           "reps_per_s": nrep / t}))
         del x, u, freq
+
+
+def gather():
+    for n, order, nrep in [(10_000_000, 8, 64), (10_000_000, 8, 256), (10_000_000, 2, 64), (1_000_000, 8, 256)]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+        x = torch.randn(n, dtype=torch.float64, device="cuda")
+        idx = torch.randint(0, n, (nrep, n), device="cuda", dtype=torch.int64)
+        t, tm = timeit(lambda: K.resample_indices(x, u, idx, order), warm=2, rep=3)
+        print(json.dumps({"gather": [n, order, nrep], "ms": t * 1e3, "ms_med": tm * 1e3, "draws_per_s": nrep * n / t,
+                          "idx_GBs": 8 * nrep * n / t / 1e9, "reps_per_s": nrep / t}))
+        del x, u, idx
 
 
 def hist():
