@@ -148,6 +148,26 @@ int txb_resample_data_f64(const double* data, const int64_t* freq, int64_t nrep,
 int txb_convert_f64(const double* in, double* out, int64_t nelem, int order, int kind,
                     void* stream);
 
+/* ---- K7: derivative expressions and Taylor / polynomial prediction -----------
+ * txb_eval_exprs_f64 replaces  [funcs[i](*args) for i in range(order+1)]
+ * (models.py:241-243, 371; expressions from beta.py:32-266, lnpi.py:42-116,
+ * volume.py:63-78, -log transform models.py:261-281).
+ *   vars[nvar][nelem] fp64; expression i = sum over terms t in
+ *   [term_ptr[i], term_ptr[i+1]) of coef[t] * prod over factors f in
+ *   [fac_ptr[t], fac_ptr[t+1]) of vars[fac_var[f]] ^ fac_pow[f]
+ *   (integer power, may be negative; 127 = natural log).  out[nexpr][nelem].
+ *   All table pointers are DEVICE pointers (int32 / fp64).
+ * txb_poly_predict_f64 replaces the Taylor sum of ExtrapModel.predict
+ * (models.py:535-565) and InterpModel.predict (models.py:929-932):
+ *   coefs[np1][nelem], dalpha[nalpha] (device) ->
+ *   mode 0: out[nalpha][nelem] = sum_p coefs[p] dalpha^p
+ *   mode 1: out[nalpha][np1][nelem] running sum (cumsum); mode 2: individual terms. */
+int txb_eval_exprs_f64(const double* vars, int64_t nelem, int nexpr, const int* term_ptr,
+                       const double* coef, const int* fac_ptr, const int* fac_var,
+                       const int* fac_pow, double* out, void* stream);
+int txb_poly_predict_f64(const double* coefs, int np1, int64_t nelem, const double* dalpha,
+                         int nalpha, int mode, double* out, void* stream);
+
 /* ---- measurement helper: fp64 FMA peak micro-benchmark (bench.py roofline) ---
  * scratch: >= 1 device double; *flops (HOST pointer) = flop count of the launch. */
 int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* flops, void* stream);

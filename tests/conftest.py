@@ -26,3 +26,26 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture
+def backend_kernels(monkeypatch):
+    """Real CUDA kernels on a GPU box; the oracle-backed stand-in (tests/fake_kernels.py) elsewhere.
+
+    Only host logic is being tested through the stand-in; kernel parity lives in the
+    ``-m gpu`` tests.
+    """
+    import torch
+
+    if torch.cuda.is_available():
+        from thermoextrap_b200 import kernels
+
+        return kernels
+    sys.path.insert(0, str(Path(__file__).parent))
+    import fake_kernels
+
+    import thermoextrap_b200.backend as backend
+
+    monkeypatch.setattr(backend, "K", fake_kernels)
+    backend.clear_device_cache()
+    return fake_kernels

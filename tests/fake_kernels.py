@@ -1,0 +1,110 @@
+"""TEST-ONLY stand-in for ``thermoextrap_b200.kernels`` backed by the CPU oracle.
+
+Lets the ``-m "not gpu"`` suite exercise the HOST logic (dims, samplers, data classes,
+models, factories) in a container without a GPU.  The product never imports this module;
+on a GPU box the same tests run against the real CUDA kernels.
+"""
+
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from oracle import comoments as oc
+
+CONVERT_CENTRAL_TO_RAW, CONVERT_RAW_TO_CENTRAL, CONVERT_CENTRAL_TO_CMOM = 0, 1, 2
+launch_count = 0
+
+
+def device():
+    return torch.device("cpu")
+
+
+def _np(t):
+    if t is None:
+        return None
+    return t.numpy() if isinstance(t, torch.Tensor) else np.asarray(t)
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def reduce_vals(x, u, order, w=None, x_is_u=False):
+    u = _np(u)
+    x = u if x_is_u else _np(x)
+    if order < 1 or order > 12:
+        raise ValueError("order")
+    out = oc.comoments_two_pass(x, u, order, w=_np(w))
+    return _t(out)
+
+
+def indices_to_freq(indices, ndat=None, dtype=torch.int64):
+    f = oc.indices_to_freq(_np(indices), ndat)
+    info = torch.iinfo(dtype)
+    if f.max() > info.max:
+        raise OverflowError
+    return _t(f).to(dtype)
+
+
+def resample_vals(x, u, freq, order, w=None, x_is_u=False):
+    u = _np(u)
+    x = u if x_is_u else _np(x)
+    return _t(oc.resample_vals_freq(x, u, order, _np(freq).astype(np.int64), w=_np(w)))
+
+
+def resample_indices(x, u, indices, order, w=None, x_is_u=False):
+    u = _np(u)
+    x = u if x_is_u else _np(x)
+    return _t(oc.resample_vals_gather(x, u, order, _np(indices), w=_np(w)))
+
+
+def reduce_data(data):
+    return _t(oc.merge_blocks(_np(data)))
+
+
+def resample_data(data, freq):
+    return _t(oc.resample_blocks(_np(data), _np(freq)))
+
+
+def convert(data, kind):
+    d = _np(data)
+    if kind == CONVERT_CENTRAL_TO_RAW:
+        return _t(oc.central_to_raw(d))
+    if kind == CONVERT_RAW_TO_CENTRAL:
+        return _t(oc.raw_to_central(d))
+    out = d.copy()
+    out[..., 0, 0] = 1.0
+    out[..., 0, 1] = 0.0
+    out[..., 1, 0] = 0.0
+    return _t(out)
+
+
+PREDICT_SUM, PREDICT_CUMSUM, PREDICT_TERMS = 0, 1, 2
+
+
+def eval_exprs(vars_, term_ptr, coef, fac_ptr, fac_var, fac_pow):
+    v = _np(vars_).astype(np.float64)
+    nexpr = len(term_ptr) - 1
+    out = np.zeros((nexpr, v.shape[1]))
+    for i in range(nexpr):
+        for t in range(term_ptr[i], term_ptr[i + 1]):
+            term = np.full(v.shape[1], float(coef[t]))
+            for f in range(fac_ptr[t], fac_ptr[t + 1]):
+                p = int(fac_pow[f])
+                x = v[int(fac_var[f])]
+                term = term * (np.log(x) if p == 127 else x ** float(p) if p < 0 else x**p)
+            out[i] += term
+    return _t(out)
+
+
+def poly_predict(coefs, dalpha, mode=0):
+    c = _np(coefs)
+    d = np.atleast_1d(np.asarray(dalpha, dtype=np.float64))
+    p = np.arange(c.shape[0])
+    terms = d[:, None, None] ** p[None, :, None] * c[None]
+    if mode == 0:
+        return _t(terms.sum(axis=1))
+    if mode == 1:
+        return _t(np.cumsum(terms, axis=1))
+    return _t(terms)

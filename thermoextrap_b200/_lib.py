@@ -53,6 +53,8 @@ SIGNATURES = {
     "txb_reduce_data_f64": (_int, [_p, _i64, _i64, _int, _p, _p]),
     "txb_resample_data_f64": (_int, [_p, _p, _i64, _i64, _i64, _int, _p, _p]),
     "txb_convert_f64": (_int, [_p, _p, _i64, _int, _int, _p]),
+    "txb_eval_exprs_f64": (_int, [_p, _i64, _int, _p, _p, _p, _p, _p, _p, _p]),
+    "txb_poly_predict_f64": (_int, [_p, _int, _i64, _p, _int, _int, _p, _p]),
     "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),
 }
 

@@ -1,0 +1,576 @@
+"""Numeric backend: the subset of cmomy's functional API that thermoextrap calls,
+implemented as host glue over the sm_100a kernels in ``libtxb.so``.
+
+Mirrors (names, argument meaning, error behaviour) the call sites listed in
+SURVEY.md 8(b): ``wrap_reduce_vals`` (data.py:485-489, 528-532, 1183-1203,
+1632-1640), ``wrap_resample_vals`` (data.py:1354-1366, 1803-1810),
+``resample_and_reduce`` (data.py:1048-1052), ``reduce`` (data.py:996),
+``wrap`` (data.py:1266-1272), ``select_moment`` / ``assign_moment``
+(data.py:486, 857-906, 1449-1460), ``convert.moments_type`` (data.py:1109-1115),
+``convert.comoments_to_moments`` (data.py:868, 900), ``factory_sampler`` /
+``IndexSampler`` (data.py:420, 1028, 1344, 1782; models.py:628) and
+``random.validate_rng`` (idealgas.py:17).
+
+All arithmetic on samples runs on the GPU; there is no CPU fallback.
+"""
+
+from __future__ import annotations
+
+import weakref
+from collections.abc import Mapping
+from typing import Any
+
+import numpy as np
+
+from . import kernels as K
+from .core.xr import DataArray, is_dataarray
+
+
+class _Missing:
+    def __repr__(self) -> str:
+        return "<MISSING>"
+
+    def __bool__(self) -> bool:
+        return False
+
+
+MISSING = _Missing()
+
+
+# ------------------------------------------------------------------ device cache
+_dev_cache: dict[tuple, tuple[Any, Any]] = {}
+
+
+def to_device(arr: np.ndarray):
+    """Upload a host array once; later calls with the same buffer reuse the device copy."""
+    import torch
+
+    arr = np.asarray(arr)
+    key = (arr.__array_interface__["data"][0], arr.shape, arr.strides, arr.dtype.str)
+    hit = _dev_cache.get(key)
+    if hit is not None and hit[0]() is not None:
+        return hit[1]
+    dev = K.device()
+    host = np.ascontiguousarray(arr)
+    t = torch.from_numpy(host)
+    if host.nbytes >= (1 << 20) and dev.type == "cuda":
+        t = t.pin_memory()
+    t = t.to(dev, non_blocking=True)
+    try:
+        base = arr if arr.base is None else arr
+        ref = weakref.ref(base, lambda _r, k=key: _dev_cache.pop(k, None))
+        _dev_cache[key] = (ref, t)
+    except TypeError:
+        pass
+    return t
+
+
+def clear_device_cache() -> None:
+    _dev_cache.clear()
+
+
+# ------------------------------------------------------------------ random
+class _Random:
+    """``cmomy.random``: a process-global numpy Generator (PCG64)."""
+
+    _rng: np.random.Generator | None = None
+
+    def default_rng(self, seed=None) -> np.random.Generator:
+        if self._rng is None or seed is not None:
+            self._rng = np.random.default_rng(seed)
+        return self._rng
+
+    def validate_rng(self, rng=None) -> np.random.Generator:
+        if rng is None:
+            return self.default_rng()
+        if isinstance(rng, np.random.Generator):
+            return rng
+        return np.random.default_rng(rng)
+
+
+random = _Random()
+
+
+# ------------------------------------------------------------------ sampler
+class IndexSampler:
+    """Bootstrap index / frequency table (``cmomy.IndexSampler`` protocol: ``.indices``, ``.freq``).
+
+    ``indices[nrep, nsamp]`` int64 in ``[0, ndat)``; ``freq[nrep, ndat]`` int64 with
+    ``freq[r, i] = #{j: indices[r, j] == i}``.  Either may be given; ``freq`` is derived
+    on the device (K6, bit-exact) when needed.
+    """
+
+    def __init__(self, indices=None, freq=None, ndat: int | None = None) -> None:
+        if indices is None and freq is None:
+            msg = "must specify indices or freq"
+            raise ValueError(msg)
+        self._indices = None if indices is None else np.asarray(_values(indices), dtype=np.int64)
+        self._freq = None if freq is None else np.asarray(_values(freq), dtype=np.int64)
+        if self._indices is not None and self._indices.ndim != 2:
+            msg = "indices must be 2-D [nrep, nsamp]"
+            raise ValueError(msg)
+        if self._freq is not None and self._freq.ndim != 2:
+            msg = "freq must be 2-D [nrep, ndat]"
+            raise ValueError(msg)
+        if ndat is None:
+            ndat = self._freq.shape[1] if self._freq is not None else self._indices.shape[1]
+        self.ndat = int(ndat)
+        self._freq_dev = None
+
+    @property
+    def indices(self) -> np.ndarray:
+        if self._indices is None:
+            # any index table with these frequencies (sorted expansion), as cmomy does
+            self._indices = np.stack([np.repeat(np.arange(self.ndat), f) for f in self._freq])
+        return self._indices
+
+    @property
+    def has_indices(self) -> bool:
+        return self._indices is not None
+
+    @property
+    def nrep(self) -> int:
+        return (self._indices if self._indices is not None else self._freq).shape[0]
+
+    def freq_device(self, narrow: bool = True):
+        """Frequency table as a CUDA tensor (uint8 when it cannot overflow, else int32/int64)."""
+        import torch
+
+        if self._freq_dev is not None:
+            return self._freq_dev
+        if self._freq is not None:
+            self._freq_dev = to_device(self._freq)
+            return self._freq_dev
+        idx = to_device(self._indices)
+        out = None
+        for dt in ((torch.uint8, torch.int32) if narrow else (torch.int64,)):
+            try:
+                out = K.indices_to_freq(idx, self.ndat, dtype=dt)
+                break
+            except OverflowError:
+                continue
+        self._freq_dev = out
+        return out
+
+    @property
+    def freq(self) -> np.ndarray:
+        if self._freq is None:
+            self._freq = self.freq_device().to("cpu").numpy().astype(np.int64)
+        return self._freq
+
+
+def _values(x):
+    return x.values if is_dataarray(x) else x
+
+
+def _axis_of(data, axis, dim, mom_ndim=0) -> int:
+    if dim is not MISSING and dim is not None:
+        if not is_dataarray(data):
+            msg = "dim requires a DataArray"
+            raise ValueError(msg)
+        if dim not in data.dims:
+            msg = f"dimension {dim!r} not in {data.dims}"
+            raise ValueError(msg)
+        return data.dims.index(dim)
+    if axis is MISSING or axis is None:
+        msg = "must specify axis or dim"
+        raise ValueError(msg)
+    if isinstance(axis, str):
+        return data.dims.index(axis)
+    nd = np.ndim(_values(data)) - mom_ndim
+    return int(axis) % nd
+
+
+def factory_sampler(
+    sampler=None, *, nrep=None, ndat=None, nsamp=None, indices=None, freq=None, rng=None,
+    replace=True, data=None, axis=MISSING, dim=MISSING, mom_ndim=None, mom_dims=None,
+    rep_dim="rep", parallel=None, **_kw,
+) -> IndexSampler:
+    """``cmomy.factory_sampler``: IndexSampler | int (nrep) | Mapping (kwargs) | array (indices)."""
+    if isinstance(sampler, IndexSampler):
+        return sampler
+    if isinstance(sampler, Mapping):
+        kw = dict(sampler)
+        return factory_sampler(
+            None, data=data, axis=axis, dim=dim, mom_ndim=mom_ndim, mom_dims=mom_dims, rep_dim=rep_dim,
+            **{"nrep": nrep, "ndat": ndat, "nsamp": nsamp, "indices": indices, "freq": freq, "rng": rng, **kw},
+        )
+    if isinstance(sampler, (int, np.integer)):
+        nrep = int(sampler)
+    elif sampler is not None:
+        indices = sampler
+    if ndat is None and data is not None:
+        nm = mom_ndim or 0
+        ax = _axis_of(data, axis, dim, nm)
+        ndat = np.shape(_values(data))[ax]
+    if indices is not None or freq is not None:
+        return IndexSampler(indices=indices, freq=freq, ndat=ndat)
+    if nrep is None or ndat is None:
+        msg = "must specify nrep and ndat (or data) to create random indices"
+        raise ValueError(msg)
+    nsamp = ndat if nsamp is None else nsamp
+    g = random.validate_rng(rng)
+    idx = g.choice(ndat, size=(nrep, nsamp), replace=replace)
+    return IndexSampler(indices=idx, ndat=ndat)
+
+
+# ------------------------------------------------------------------ helpers
+def _mom_dims_tuple(mom_dims, mom_ndim):
+    if mom_dims is None:
+        return ("mom_0",) if mom_ndim == 1 else ("mom_0", "mom_1")
+    return (mom_dims,) if isinstance(mom_dims, str) else tuple(mom_dims)
+
+
+def _host(t) -> np.ndarray:
+    return t.to("cpu").numpy()
+
+
+def _move_first(da: DataArray, dim) -> DataArray:
+    return da.transpose(dim, ...)
+
+
+def _prep_samples(x, u, weight, axis, dim):
+    """Return (xd, ud, wd, rest_dims, lead): sample axis first, numpy-contiguous on the device."""
+    if not is_dataarray(x):
+        ax = _axis_of(x, axis, MISSING)
+        xv = np.moveaxis(np.asarray(x), ax, 0)
+        x = DataArray(xv, dims=("_rec", *[f"dim_{i}" for i in range(xv.ndim - 1)]))
+        dim = "_rec"
+        if u is not None and not is_dataarray(u):
+            uv = np.asarray(u)
+            u = DataArray(np.moveaxis(uv, ax if uv.ndim > 1 else 0, 0), dims=x.dims[: uv.ndim]) if uv.ndim else u
+        if weight is not None and not is_dataarray(weight):
+            weight = DataArray(np.asarray(weight), dims=("_rec",))
+    else:
+        dim = x.dims[_axis_of(x, axis, dim)]
+    x = _move_first(x, dim)
+    if u is not None:
+        if dim not in u.dims:
+            msg = f"dimension {dim!r} not in {u.dims}"
+            raise ValueError(msg)
+        u = _move_first(u, dim)
+    if weight is not None:
+        if not is_dataarray(weight):
+            weight = DataArray(np.asarray(weight, dtype=np.float64), dims=(dim,))
+        if weight.dims != (dim,):
+            if dim in weight.dims and weight.ndim > 1:
+                msg = "only 1-D weights along the sample dimension are supported"
+                raise NotImplementedError(msg)
+            weight = DataArray(np.broadcast_to(np.asarray(weight.values, dtype=np.float64), (x.sizes[dim],)).copy(), dims=(dim,))
+    return x, u, weight, dim
+
+
+class CentralMomentsData:
+    """Comoment array + the methods thermoextrap calls on ``cmomy.CentralMomentsData``.
+
+    ``obj`` is a DataArray whose last ``mom_ndim`` dims are the moment dims
+    (layout of data.py:1233-1236).
+    """
+
+    def __init__(self, obj: DataArray, mom_ndim: int = 2, mom_dims=None, **_kw) -> None:
+        if not is_dataarray(obj):
+            msg = f"type(obj)={type(obj)} must be a DataArray."
+            raise TypeError(msg)
+        if mom_dims is None:
+            mom_dims = obj.dims[-mom_ndim:]
+        self.mom_dims = _mom_dims_tuple(mom_dims, mom_ndim)
+        self.mom_ndim = len(self.mom_dims)
+        for d in self.mom_dims:
+            if d not in obj.dims:
+                msg = f"moment dimension {d!r} not in {obj.dims}"
+                raise ValueError(msg)
+        self.obj = obj.transpose(..., *self.mom_dims)
+
+    # -- protocol ------------------------------------------------------------
+    @property
+    def sizes(self):
+        return self.obj.sizes
+
+    @property
+    def dims(self):
+        return self.obj.dims
+
+    @property
+    def values(self):
+        return self.obj
+
+    @property
+    def mom(self) -> tuple[int, ...]:
+        return tuple(self.obj.sizes[d] - 1 for d in self.mom_dims)
+
+    def new_like(self, obj: DataArray) -> CentralMomentsData:
+        return type(self)(obj, mom_ndim=self.mom_ndim, mom_dims=self.mom_dims)
+
+    def transpose(self, *dims, **_kw) -> CentralMomentsData:
+        lead = [d for d in dims if d is Ellipsis or d not in self.mom_dims]
+        if Ellipsis not in lead:
+            lead.append(...)
+        return self.new_like(self.obj.transpose(*lead, *self.mom_dims))
+
+    def _convert(self, kind: int) -> DataArray:
+        if self.mom_ndim == 2:
+            return _like(self.obj, _host(K.convert(np.ascontiguousarray(self.obj.values, dtype=np.float64), kind)))
+        # 1-D moments: embed as the u-row of a comoment tail (x-row unused)
+        v = np.asarray(self.obj.values, dtype=np.float64)
+        pad = np.zeros((*v.shape[:-1], 2, v.shape[-1]))
+        pad[..., 0, :] = v
+        out = _host(K.convert(pad, kind))[..., 0, :]
+        return _like(self.obj, out)
+
+    def cmom(self) -> DataArray:
+        """Central moments with ``[0,0]=1, [1,0]=[0,1]=0`` (data.py:850-852)."""
+        return self._convert(K.CONVERT_CENTRAL_TO_CMOM)
+
+    def rmom(self) -> DataArray:
+        """Raw moments ``<x^i u^j>`` with ``[0,0]=1`` (data.py:845-847)."""
+        return self._convert(K.CONVERT_CENTRAL_TO_RAW)
+
+    def select_moment(self, name: str, **kw) -> DataArray:
+        return select_moment(self.obj, name, mom_ndim=self.mom_ndim, mom_dims=self.mom_dims, **kw)
+
+    def moments_to_comoments(self, *, mom, mom_dims_out=None, **_kw) -> CentralMomentsData:
+        """1-D moments of order n -> comoments ``mom=(1, k)`` (data.py:1191, 1266-1268)."""
+        if self.mom_ndim != 1:
+            msg = "moments_to_comoments needs 1-D moments"
+            raise ValueError(msg)
+        v = np.asarray(self.obj.values)
+        n = v.shape[-1] - 1
+        k = mom[1] if mom[1] >= 0 else n - 1
+        if mom[0] != 1 or k + 1 > n:
+            msg = f"cannot build comoments {mom} from moments of order {n}"
+            raise ValueError(msg)
+        out = np.empty((*v.shape[:-1], 2, k + 1), dtype=v.dtype)
+        out[..., 0, :] = v[..., : k + 1]
+        out[..., 1, :] = v[..., 1 : k + 2]
+        dims_out = _mom_dims_tuple(mom_dims_out, 2)
+        da = DataArray(out, dims=(*self.obj.dims[:-1], *dims_out))
+        return CentralMomentsData(da, mom_ndim=2, mom_dims=dims_out)
+
+    def reduce(self, dim=MISSING, axis=MISSING, **_kw) -> CentralMomentsData:
+        """Merge blocks along ``dim`` (K4, data.py:996)."""
+        ax = _axis_of(self.obj, axis, dim, self.mom_ndim)
+        d = self.obj.dims[ax]
+        obj = self.obj.transpose(d, ...)
+        data = np.ascontiguousarray(obj.values, dtype=np.float64)
+        if self.mom_ndim == 1:
+            msg = "reduce of 1-D moment blocks is not needed by thermoextrap"
+            raise NotImplementedError(msg)
+        out = _host(K.reduce_data(data))
+        return self.new_like(DataArray(out, dims=obj.dims[1:]))
+
+    def resample_and_reduce(self, *, sampler, dim=MISSING, axis=MISSING, rep_dim="rep", **_kw) -> CentralMomentsData:
+        """Frequency-weighted merge of blocks (K3, data.py:1048-1052)."""
+        ax = _axis_of(self.obj, axis, dim, self.mom_ndim)
+        d = self.obj.dims[ax]
+        sampler = factory_sampler(sampler, data=self.obj, dim=d, mom_ndim=self.mom_ndim)
+        obj = self.obj.transpose(d, ...)
+        data = np.ascontiguousarray(obj.values, dtype=np.float64)
+        freq = sampler.freq
+        if freq.shape[1] != data.shape[0]:
+            msg = f"sampler ndat={freq.shape[1]} does not match {data.shape[0]} blocks"
+            raise ValueError(msg)
+        out = _host(K.resample_data(data, freq))
+        # cmomy puts rep_dim where the reduced dim was
+        new = DataArray(out, dims=(rep_dim, *obj.dims[1:]))
+        order = list(self.obj.dims)
+        order[ax] = rep_dim
+        return self.new_like(new.transpose(*order))
+
+
+def _like(da: DataArray, values: np.ndarray) -> DataArray:
+    return DataArray(values, dims=da.dims, coords={k: v for k, v in da.coords.items() if k in da.dims} or None)
+
+
+# ------------------------------------------------------------------ functional API
+def wrap(obj, *, mom_ndim: int = 2, mom_dims=None, **_kw) -> CentralMomentsData:
+    """``cmomy.wrap`` (data.py:1266-1272)."""
+    return CentralMomentsData(obj, mom_ndim=mom_ndim, mom_dims=mom_dims)
+
+
+def _moments_1d_from_x_is_u(out: np.ndarray, m: int) -> np.ndarray:
+    """comoment layout (order m-1) from the x_is_u kernel -> 1-D moments of order m."""
+    mom = np.empty((*out.shape[:-2], m + 1))
+    k = out.shape[-1] - 1
+    mom[..., : min(k, m) + 1] = out[..., 0, : min(k, m) + 1]
+    if m == k + 1:
+        mom[..., m] = out[..., 1, k]
+    return mom
+
+
+def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dims=None, **_kw) -> CentralMomentsData:
+    """``cmomy.wrap_reduce_vals``: central (co)moments of samples along ``dim`` (K1).
+
+    ``wrap_reduce_vals(x, u, mom=(1, k))`` -> ``[..., 2, k+1]``; ``wrap_reduce_vals(u, mom=n)``
+    -> 1-D moments ``[..., n+1]``.
+    """
+    u = y[0] if y else None
+    if len(y) > 1:
+        msg = "at most two variables (x, u) are supported"
+        raise ValueError(msg)
+    two = u is not None
+    if two:
+        mom = tuple(mom)
+        if len(mom) != 2 or mom[0] != 1:
+            msg = f"thermoextrap only uses mom=(1, k); got {mom}"
+            raise ValueError(msg)
+    else:
+        mom = int(mom[0]) if isinstance(mom, (tuple, list)) else int(mom)
+    x, u, weight, dim = _prep_samples(x, u, weight, axis, dim)
+    wd = None if weight is None else to_device(np.ascontiguousarray(weight.values, dtype=np.float64))
+    rest_dims = x.dims[1:]
+    if not two:
+        xd = to_device(np.asarray(x.values, dtype=np.float64))
+        m = mom
+        if m < 1:
+            msg = "mom must be >= 1"
+            raise ValueError(msg)
+        k = max(m - 1, 1)
+        out = _host(K.reduce_vals(None, xd, k, w=wd, x_is_u=True))
+        vals = _moments_1d_from_x_is_u(out, m)
+        md = _mom_dims_tuple(mom_dims, 1)
+        return CentralMomentsData(DataArray(vals, dims=(*rest_dims, *md)), mom_ndim=1, mom_dims=md)
+    k = mom[1]
+    md = _mom_dims_tuple(mom_dims, 2)
+    extra = [d for d in u.dims[1:] if d not in rest_dims]
+    if extra:
+        msg = f"u has dims {extra} that x lacks"
+        raise ValueError(msg)
+    if u.ndim == 1:
+        out = _host(K.reduce_vals(to_device(np.asarray(x.values, dtype=np.float64)), to_device(np.asarray(u.values, dtype=np.float64)), k, w=wd))
+        return CentralMomentsData(DataArray(out, dims=(*rest_dims, *md)), mom_ndim=2, mom_dims=md)
+    # u carries some of x's other dims (e.g. a leading `rep` dim): batch over those
+    shared = tuple(u.dims[1:])
+    xt = x.transpose(*shared, dim, ...)
+    ut = u.transpose(*shared, dim)
+    lead_shape = tuple(xt.sizes[d] for d in shared)
+    xs = np.asarray(xt.values, dtype=np.float64)
+    us = np.asarray(ut.values, dtype=np.float64)
+    outs = []
+    for ii in np.ndindex(*lead_shape):
+        outs.append(_host(K.reduce_vals(np.ascontiguousarray(xs[ii]), np.ascontiguousarray(us[ii]), k, w=wd)))
+    tail_dims = xt.dims[len(shared) + 1 :]
+    out = np.stack(outs).reshape(*lead_shape, *outs[0].shape)
+    res = DataArray(out, dims=(*shared, *tail_dims, *md))
+    return CentralMomentsData(res.transpose(*rest_dims, *md), mom_ndim=2, mom_dims=md)
+
+
+def wrap_resample_vals(
+    x, *y, mom, sampler, weight=None, axis=MISSING, dim=MISSING, rep_dim="rep", mom_dims=None, **_kw
+) -> CentralMomentsData:
+    """``cmomy.wrap_resample_vals`` (K2): ``out[rep, ...] = reduce_vals`` with weights ``w * freq[rep]``.
+
+    ``rep_dim`` takes the place of the reduced dimension (thermoextrap then moves it first,
+    data.py:1812).
+    """
+    u = y[0] if y else None
+    if u is None or len(y) != 1:
+        msg = "wrap_resample_vals needs (x, u)"
+        raise ValueError(msg)
+    mom = tuple(mom)
+    if len(mom) != 2 or mom[0] != 1:
+        msg = f"thermoextrap only uses mom=(1, k); got {mom}"
+        raise ValueError(msg)
+    k = mom[1]
+    x_in_dims = x.dims if is_dataarray(x) else None
+    x, u, weight, dim = _prep_samples(x, u, weight, axis, dim)
+    sampler = factory_sampler(sampler, data=x, dim=dim)
+    if sampler.ndat != x.sizes[dim]:
+        msg = f"sampler ndat={sampler.ndat} does not match {x.sizes[dim]} samples"
+        raise ValueError(msg)
+    if u.ndim != 1:
+        msg = "resampling needs u[rec]"
+        raise NotImplementedError(msg)
+    md = _mom_dims_tuple(mom_dims, 2)
+    wd = None if weight is None else to_device(np.ascontiguousarray(weight.values, dtype=np.float64))
+    xd = to_device(np.asarray(x.values, dtype=np.float64))
+    ud = to_device(np.asarray(u.values, dtype=np.float64))
+    out = _host(resample_device(xd, ud, wd, sampler, k))
+    rest_dims = x.dims[1:]
+    res = DataArray(out, dims=(rep_dim, *rest_dims, *md))
+    if x_in_dims is not None:
+        order = [rep_dim if d == dim else d for d in x_in_dims]
+        res = res.transpose(*order, *md)
+    return CentralMomentsData(res, mom_ndim=2, mom_dims=md)
+
+
+def resample_device(xd, ud, wd, sampler: IndexSampler, order: int, x_is_u: bool = False):
+    """Route one bootstrap to the best kernel: index gather (scalar x) or freq contraction."""
+    scalar = x_is_u and ud.ndim == 1 or (xd is not None and xd.ndim == 1)
+    if scalar and sampler.has_indices and sampler._freq is None:
+        return K.resample_indices(xd, ud, to_device(sampler.indices), order, w=wd, x_is_u=x_is_u)
+    return K.resample_vals(xd, ud, sampler.freq_device(), order, w=wd, x_is_u=x_is_u)
+
+
+# ------------------------------------------------------------------ moment selection
+def select_moment(data, name: str, *, mom_ndim: int, mom_dims=None, **_kw):
+    """``cmomy.select_moment`` for the names thermoextrap uses (data.py:486-492, 857-906)."""
+    if not is_dataarray(data):
+        msg = "select_moment needs a DataArray"
+        raise TypeError(msg)
+    md = _mom_dims_tuple(mom_dims if mom_dims is not None else data.dims[-mom_ndim:], mom_ndim)
+    if mom_ndim == 2:
+        xd, ud = md
+        table = {
+            "weight": {xd: 0, ud: 0}, "xave": {xd: 1, ud: 0}, "yave": {xd: 0, ud: 1},
+            "xmom_0": {xd: 0}, "xmom_1": {xd: 1}, "ymom_0": {ud: 0}, "ymom_1": {ud: 1},
+        }
+    else:
+        (ud,) = md
+        table = {"weight": {ud: 0}, "ave": {ud: 1}, "var": {ud: 2}}
+    if name not in table:
+        msg = f"unknown moment name {name!r}"
+        raise ValueError(msg)
+    return data.isel(table[name], drop=True)
+
+
+def assign_moment(data, *, mom_dims=None, mom_ndim=None, copy=True, **moments):
+    """``cmomy.assign_moment`` (only ``weight=`` is used: data.py:1449-1460)."""
+    md = _mom_dims_tuple(mom_dims, mom_ndim or 2)
+    out = data.copy(deep=True)
+    vals = out.values
+    for name, val in moments.items():
+        if name != "weight":
+            msg = f"assign_moment({name}=...) is not used by thermoextrap"
+            raise NotImplementedError(msg)
+        idx = tuple(0 if d in md else slice(None) for d in out.dims)
+        v = _values(val)
+        vals[idx] = np.broadcast_to(np.asarray(v, dtype=vals.dtype), vals[idx].shape)
+    return out
+
+
+class _Convert:
+    """``cmomy.convert`` subset."""
+
+    @staticmethod
+    def moments_type(raw, *, mom_ndim: int, mom_dims=None, to: str = "central", **_kw):
+        """raw -> central (data.py:1108-1115); ``[0(,0)]`` (the weight) is preserved."""
+        if to != "central":
+            msg = "only to='central' is used by thermoextrap"
+            raise NotImplementedError(msg)
+        md = _mom_dims_tuple(mom_dims, mom_ndim)
+        r = raw.transpose(..., *md)
+        v = np.ascontiguousarray(r.values, dtype=np.float64)
+        if mom_ndim == 2:
+            out = _host(K.convert(v, K.CONVERT_RAW_TO_CENTRAL))
+        else:
+            pad = np.zeros((*v.shape[:-1], 2, v.shape[-1]))
+            pad[..., 0, :] = v
+            out = _host(K.convert(pad, K.CONVERT_RAW_TO_CENTRAL))[..., 0, :]
+        return _like(r, out)
+
+    @staticmethod
+    def comoments_to_moments(data, *, mom_dims=None, mom_dims_out=None, **_kw):
+        """Inverse of moments_to_comoments for ``x == u`` (data.py:868-872, 900-902):
+        ``m[j] = c[0, j]`` for ``j <= k`` and ``m[k+1] = c[1, k]``."""
+        md = _mom_dims_tuple(mom_dims, 2)
+        c = data.transpose(..., *md)
+        v = np.asarray(c.values)
+        k = v.shape[-1] - 1
+        out = np.empty((*v.shape[:-2], k + 2), dtype=v.dtype)
+        out[..., : k + 1] = v[..., 0, :]
+        out[..., k + 1] = v[..., 1, k]
+        dim_out = mom_dims_out if mom_dims_out is not None else md[1]
+        return DataArray(out, dims=(*c.dims[:-2], dim_out))
+
+
+convert = _Convert()

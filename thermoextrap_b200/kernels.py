@@ -303,3 +303,49 @@ def convert(data, kind: int) -> torch.Tensor:
     check(st, "txb_convert_f64")
     launch_count += 1
     return out
+
+
+def eval_exprs(vars_, term_ptr, coef, fac_ptr, fac_var, fac_pow) -> torch.Tensor:
+    """K7.  ``out[nexpr, nelem]`` from the monomial tables (see ``include/txb.h``)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    v = _as_f64(vars_, dev)
+    nvar, nelem = v.shape
+    nexpr = len(term_ptr) - 1
+
+    def i32(a):
+        return torch.as_tensor(np.asarray(a, dtype=np.int32), device=dev)
+
+    tp, fp, fv, fw = i32(term_ptr), i32(fac_ptr), i32(fac_var), i32(fac_pow)
+    cf = torch.as_tensor(np.asarray(coef, dtype=np.float64), device=dev)
+    out = torch.empty((nexpr, nelem), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_eval_exprs_f64(
+            v.data_ptr(), nelem, nexpr, tp.data_ptr(), cf.data_ptr(), fp.data_ptr(), fv.data_ptr(),
+            fw.data_ptr(), out.data_ptr(), _stream_ptr(),
+        )
+    check(st, "txb_eval_exprs_f64")
+    launch_count += 1
+    return out
+
+
+PREDICT_SUM, PREDICT_CUMSUM, PREDICT_TERMS = 0, 1, 2
+
+
+def poly_predict(coefs, dalpha, mode: int = PREDICT_SUM) -> torch.Tensor:
+    """``sum_p coefs[p, e] * dalpha[a]**p`` -> ``[nalpha, nelem]`` (or ``[nalpha, np1, nelem]``)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    c = _as_f64(coefs, dev)
+    d = _as_f64(np.atleast_1d(np.asarray(dalpha, dtype=np.float64)), dev)
+    np1, nelem = c.shape
+    na = d.shape[0]
+    shape = (na, nelem) if mode == PREDICT_SUM else (na, np1, nelem)
+    out = torch.empty(shape, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_poly_predict_f64(c.data_ptr(), np1, nelem, d.data_ptr(), na, mode, out.data_ptr(), _stream_ptr())
+    check(st, "txb_poly_predict_f64")
+    launch_count += 1
+    return out
