@@ -130,6 +130,39 @@ int txb_resample_indices_f64(const double* x, const double* u, const double* w, 
                              int64_t nrep, int64_t ndraw, int64_t ldi, double* out, int* status,
                              void* workspace, size_t ws_bytes, void* stream);
 
+/* ---- K6 on the device: the reference sampler's stream, bit-exact ----------------
+ * Reproduces numpy Generator(PCG64).integers(0, ndat, size) == .choice(ndat, size,
+ * replace=True), the call cmomy.factory_sampler / thermoextrap make for {"nrep": n}
+ * specs (adaptive_interp.py:543-544, tests/test_data.py:98-100, data.py:1782-1789),
+ * for ndat <= 2^32 - 1, continuing from the generator state *rng
+ * (bit_generator.state: state, inc, has_uint32, uinteger).  rng is a HOST struct.
+ * *raw_used (device int64, may be NULL) receives the number of raw 32-bit draws the
+ * outputs consumed; txb_pcg64_advance (host only, no GPU work) moves *rng past them
+ * so the caller's numpy Generator continues exactly where numpy would have.
+ * *status (device int, may be NULL): 2 = narrow table overflow, 4 = internal raw-range
+ * estimate too short (never observed; > 12 sigma).
+ *   txb_sampler_indices : indices[count] int64              (IndexSampler.indices)
+ *   txb_sampler_freq    : freq[nrep, ldf] of freq_dtype     (IndexSampler.freq)
+ *   txb_sampler_resample_f64 : K2 fused with the generator for scalar x -- neither
+ *       table is materialised; out[nrep, 2, order+1] as txb_resample_indices_f64.  */
+typedef struct txb_pcg64 {
+    uint64_t state_hi, state_lo, inc_hi, inc_lo;
+    uint32_t has_uint32, uinteger;
+} txb_pcg64;
+size_t txb_sampler_workspace_bytes(void);
+int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used);
+int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
+                        int64_t* raw_used, int* status, void* workspace, size_t ws_bytes,
+                        void* stream);
+int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp, void* freq,
+                     int freq_dtype, int64_t ldf, int64_t* raw_used, int* status, void* workspace,
+                     size_t ws_bytes, void* stream);
+size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep);
+int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
+                             const double* w, int64_t ndat, int64_t ldx, int order, int mode,
+                             int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
+                             int* status, void* workspace, size_t ws_bytes, void* stream);
+
 /* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------
  * data[nblock, nval, 2, order+1] (cmomy layout).
  * txb_reduce_data_f64   : CentralMomentsData.reduce(dim)          data.py:996

@@ -1,0 +1,134 @@
+"""Device sampler (K6): bit-exact against live numpy -- the reference's own sampler.
+
+The reference draws ``rng.choice(ndat, (nrep, nsamp), replace=True)`` on a numpy
+``Generator(PCG64)`` (adaptive_interp.py:543-544, tests/test_data.py:98-100); integer
+tables must be identical, and the generator must be left in the state numpy would
+leave it in (so later draws agree too).  The fused bootstrap is compared with the
+oracle's gather-then-reduce on the numpy table (tests/test_data.py:94-112 semantics),
+tolerance ``1e-10 * max(|ref|, sigma_x^i sigma_u^j)``.
+"""
+
+import numpy as np
+import pytest
+
+from oracle import comoments as oc
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def K():
+    from thermoextrap_b200 import kernels
+
+    return kernels
+
+
+def _same_state(a, b):
+    sa, sb = a.bit_generator.state, b.bit_generator.state
+    return (sa["state"] == sb["state"] and sa["has_uint32"] == sb["has_uint32"]
+            and (not sa["has_uint32"] or sa["uinteger"] == sb["uinteger"]))
+
+
+CASES = [
+    (2, 5, 1),  # ndat == 1: numpy returns zeros and consumes nothing
+    (3, 100, 100),
+    (10, 1000, 1000),
+    (7, 4096, 4096),
+    (5, 4097, 5000),
+    (64, 100_000, 100_000),
+    (2, 3_000_000, 3_000_000),
+    (3, 1_000_003, 3_000_000_000),  # 30 % rejection
+    (2, 2_000_000, 2_147_483_649),  # ~50 % rejection
+    (4, 65_537, 100_000_000),       # 2.2 % rejection
+]
+
+
+@pytest.mark.parametrize("nrep,nsamp,ndat", CASES)
+@pytest.mark.parametrize("odd_start", [False, True])
+def test_indices_bit_exact(K, nrep, nsamp, ndat, odd_start):
+    a, b = np.random.default_rng(11), np.random.default_rng(11)
+    if odd_start:  # leave a buffered 32-bit half in the generator
+        assert a.integers(0, 10, 3).tolist() == b.integers(0, 10, 3).tolist()
+        assert a.bit_generator.state["has_uint32"] == 1
+    ref = a.choice(ndat, size=(nrep, nsamp), replace=True)
+    out = K.sampler_indices(b, nrep, nsamp, ndat).cpu().numpy()
+    assert out.dtype == np.int64
+    assert np.array_equal(out, ref)
+    assert _same_state(a, b)
+    # and the streams keep agreeing afterwards
+    assert np.array_equal(a.integers(0, 1000, 5), b.integers(0, 1000, 5))
+
+
+@pytest.mark.parametrize("dtype_name", ["uint8", "uint16", "int32", "int64"])
+@pytest.mark.parametrize("nrep,nsamp,ndat", [(3, 100, 100), (9, 5000, 4097), (33, 100_000, 100_000), (2, 1_000_000, 999_999)])
+def test_freq_bit_exact(K, nrep, nsamp, ndat, dtype_name):
+    import torch
+
+    a, b = np.random.default_rng(3), np.random.default_rng(3)
+    idx = a.choice(ndat, size=(nrep, nsamp), replace=True)
+    ref = oc.indices_to_freq(idx, ndat)
+    out = K.sampler_freq(b, nrep, nsamp, ndat, dtype=getattr(torch, dtype_name)).cpu().numpy()
+    assert np.array_equal(out.astype(np.int64), ref)
+    assert out.sum(axis=1).tolist() == [nsamp] * nrep
+    assert _same_state(a, b)
+
+
+def test_freq_overflow_is_loud(K):
+    import torch
+
+    with pytest.raises(OverflowError):
+        K.sampler_freq(np.random.default_rng(0), 1, 5000, 3, dtype=torch.uint8)
+
+
+@pytest.mark.parametrize("order", [1, 6, 8])
+@pytest.mark.parametrize("nrep,n", [(5, 100), (16, 4096), (7, 10_000), (3, 300_000)])
+def test_fused_resample_matches_numpy_table(K, nrep, n, order):
+    rng = np.random.default_rng(1)
+    u = rng.normal(175.0, 5.3, n)
+    x = 1e-3 * u + rng.normal(0.0, 0.02, n)
+    a, b = np.random.default_rng(21), np.random.default_rng(21)
+    idx = a.choice(n, size=(nrep, n), replace=True)
+    ref = oc.resample_vals_gather(x, u, order, idx)
+    out = K.sampler_resample(b, x, u, nrep, order).cpu().numpy()
+    scale = oc.tolerance_scale(x, u, order)
+    assert out.shape == ref.shape
+    assert float((np.abs(out - ref) / np.maximum(np.abs(ref), scale)).max()) < TOL
+    assert _same_state(a, b)
+
+
+def test_fused_resample_weighted_and_x_is_u(K):
+    n, nrep, order = 5000, 6, 5
+    rng = np.random.default_rng(2)
+    u = rng.normal(-3.0, 2.0, n)
+    x = 0.5 * u + rng.normal(0.0, 1.0, n)
+    w = rng.random(n)
+    a, b, c = (np.random.default_rng(8) for _ in range(3))
+    idx = a.choice(n, size=(nrep, n), replace=True)
+    scale = oc.tolerance_scale(x, u, order)
+    out = K.sampler_resample(b, x, u, nrep, order, w=w).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, order, idx, w=w)
+    assert float((np.abs(out - ref) / np.maximum(np.abs(ref), scale)).max()) < TOL
+    out = K.sampler_resample(c, None, u, nrep, order, x_is_u=True).cpu().numpy()
+    ref = K.resample_indices(None, u, idx, order, x_is_u=True).cpu().numpy()
+    assert np.allclose(out, ref, rtol=1e-11, atol=0)
+
+
+def test_full_size_properties(K):
+    """BASELINE config-2 width (ndat = 1e7), a slice of its replicates: row sums and parity of two routes."""
+    import torch
+
+    n, nrep, order = 10_000_000, 8, 8
+    g = torch.Generator(device="cuda").manual_seed(0)
+    u = torch.randn(n, dtype=torch.float64, device="cuda", generator=g) * 5.3 + 175.0
+    x = 1e-3 * u + 0.02 * torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
+    a, b, c = (np.random.default_rng(4) for _ in range(3))
+    fused = K.sampler_resample(a, x, u, nrep, order)
+    idx = K.sampler_indices(b, nrep, n)
+    assert np.array_equal(idx[0, :1000].cpu().numpy(), c.choice(n, size=(nrep, n))[0, :1000])
+    via_table = K.resample_indices(x, u, idx, order)
+    assert torch.allclose(fused, via_table, rtol=1e-9, atol=0)
+    assert fused[:, 0, 0].tolist() == [float(n)] * nrep
+    freq = K.indices_to_freq(idx, n, dtype=torch.uint8)
+    via_freq = K.resample_vals(x, u, freq, order)
+    assert torch.allclose(fused, via_freq, rtol=1e-9, atol=0)

@@ -50,6 +50,15 @@ SIGNATURES = {
         _int,
         [_p, _p, _p, _i64, _i64, _int, _int, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p],
     ),
+    "txb_sampler_workspace_bytes": (_sz, []),
+    "txb_pcg64_advance": (_int, [_p, _i64]),
+    "txb_sampler_indices": (_int, [_p, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
+    "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _p, _sz, _p]),
+    "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64]),
+    "txb_sampler_resample_f64": (
+        _int,
+        [_p, _p, _p, _p, _i64, _i64, _int, _int, _i64, _i64, _p, _p, _p, _p, _sz, _p],
+    ),
     "txb_reduce_data_f64": (_int, [_p, _i64, _i64, _int, _p, _p]),
     "txb_resample_data_f64": (_int, [_p, _p, _i64, _i64, _i64, _int, _p, _p]),
     "txb_convert_f64": (_int, [_p, _p, _i64, _int, _int, _p]),
@@ -57,6 +66,17 @@ SIGNATURES = {
     "txb_poly_predict_f64": (_int, [_p, _int, _i64, _p, _int, _int, _p, _p]),
     "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),
 }
+
+
+
+class Pcg64State(C.Structure):
+    """``txb_pcg64``: numpy ``Generator(PCG64).bit_generator.state`` as plain integers."""
+
+    _fields_ = [
+        ("state_hi", C.c_uint64), ("state_lo", C.c_uint64), ("inc_hi", C.c_uint64), ("inc_lo", C.c_uint64),
+        ("has_uint32", C.c_uint32), ("uinteger", C.c_uint32),
+    ]
+
 
 _lib = None
 

@@ -26,6 +26,13 @@ __global__ void __launch_bounds__(256)
     packed[i] = make_double2(dx, du);
 }
 
+int launch_pack_shifted(const double* x, int64_t ldx, const double* u, int64_t nsamp,
+                        const double* pivot, double2* packed, cudaStream_t st) {
+    k_pack_shifted<<<(unsigned)((nsamp + 255) / 256), 256, 0, st>>>(x, ldx, u, nsamp, pivot, packed);
+    TXB_CUDA_LAUNCH_CHECK("k_pack_shifted");
+    return TXB_OK;
+}
+
 template <int K, bool HAS_X, bool HAS_W>
 __global__ void __launch_bounds__(256, 2)
     k_resample_gather(const double2* __restrict__ packed, const double* __restrict__ w,

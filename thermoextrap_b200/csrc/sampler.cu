@@ -1,0 +1,624 @@
+// K6 on the device: the reference sampler's integer stream, bit-exact, never leaving HBM.
+//
+// The reference draws bootstrap indices with numpy:
+//     rng.choice(ndat, (nrep, nsamp), replace=True)  ==  rng.integers(0, ndat, (nrep, nsamp))
+// (/root/reference/src/thermoextrap/adaptive_interp.py:543-544, tests/test_data.py:98-100,
+//  legacy/extrap.py:133-136; cmomy.factory_sampler does the same for {"nrep": ...} specs,
+//  data.py:1782-1789).  numpy's Generator(PCG64) produces that stream as
+//     next64 : s = s * M + inc (mod 2^128);  x = hi64(s) ^ lo64(s);  rotr64(x, s >> 122)
+//     next32 : low half of a next64 first, then its high half (has_uint32 / uinteger buffer)
+//     draw   : m = next32 * ndat;  rejected iff lo32(m) < 2^32 mod ndat;  value = hi32(m)
+// so raw 32-bit draw #p depends only on jump(s0, p / 2), acceptance only on that draw, and the
+// output is the stream compaction of the accepted raw draws.
+//
+// Device scheme (integer work; every thread block owns one contiguous range of LCG steps):
+//   pass A  k_sampler<MODE_COUNT>  : accepted draws per block
+//   scan    k_sampler_scan         : exclusive prefix -> first output position of each block
+//   pass B  k_sampler<MODE_...>    : regenerate the range and, per accepted draw at output
+//                                    position p (replicate p / nsamp):
+//             FILL   indices[p] = value                         (sampler.indices)
+//             HIST   freq[p / nsamp, value] += 1                (sampler.freq, any width)
+//             GATHER S[p / nsamp, :] += powers(x[value], u[value])   (K2 fused, scalar x)
+// Regenerating the stream costs ~15 integer instructions per draw, far below the price of
+// storing and re-reading an int64 table (8 B/draw; 80 GB at BASELINE config 2).
+#include "txb_common.cuh"
+
+namespace txb {
+
+int launch_pack_shifted(const double* x, int64_t ldx, const double* u, int64_t nsamp,
+                        const double* pivot, double2* packed, cudaStream_t st);
+
+constexpr uint64_t PCG_MULT_HI = 0x2360ED051FC65DA4ull;
+constexpr uint64_t PCG_MULT_LO = 0x4385DF649FCCF645ull;
+constexpr int SMP_T = 8;          // LCG steps per thread per iteration (16 raw draws)
+constexpr int SMP_THREADS = 256;
+constexpr int SMP_NPOW = 48;      // jump table covers step offsets < 2^48
+
+struct Affine {  // s -> a * s + c  (mod 2^128)
+    uint64_t a_hi, a_lo, c_hi, c_lo;
+};
+
+struct SamplerArgs {
+    uint64_t s_hi, s_lo, inc_hi, inc_lo;
+    uint32_t pre_valid, pre_u32;  // numpy's has_uint32 / uinteger
+    uint32_t n, thresh;           // ndat, 2^32 mod ndat
+    int64_t count;                // accepted draws wanted (nrep * nsamp)
+    int64_t nsamp;                // draws per replicate
+    int64_t steps_per_block;      // multiple of SMP_THREADS * SMP_T
+    Affine iter_jump;             // (SMP_THREADS - 1) * SMP_T steps
+    Affine pow2[SMP_NPOW];        // 2^i steps
+};
+
+enum { MODE_COUNT = 0, MODE_FILL = 1, MODE_HIST = 2, MODE_GATHER = 3 };
+
+__device__ __forceinline__ void affine_apply(uint64_t& hi, uint64_t& lo, const Affine& f) {
+    const uint64_t plo = f.a_lo * lo;
+    const uint64_t phi = __umul64hi(f.a_lo, lo) + f.a_lo * hi + f.a_hi * lo;
+    const uint64_t rlo = plo + f.c_lo;
+    hi = phi + f.c_hi + (rlo < plo ? 1ull : 0ull);
+    lo = rlo;
+}
+
+__device__ __forceinline__ uint64_t pcg_step_out(uint64_t& hi, uint64_t& lo, uint64_t inc_hi,
+                                                 uint64_t inc_lo) {
+    const uint64_t plo = PCG_MULT_LO * lo;
+    const uint64_t phi = __umul64hi(PCG_MULT_LO, lo) + PCG_MULT_LO * hi + PCG_MULT_HI * lo;
+    const uint64_t rlo = plo + inc_lo;
+    hi = phi + inc_hi + (rlo < plo ? 1ull : 0ull);
+    lo = rlo;
+    const uint64_t x = hi ^ lo;
+    const unsigned rot = (unsigned)(hi >> 58);
+    return (x >> rot) | (x << ((64u - rot) & 63u));
+}
+
+// exclusive block scan of one int per thread (256 threads); returns the block total in `total`
+__device__ __forceinline__ int block_scan_excl(int v, int* sm_warp, int& total) {
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();  // previous users of sm_warp are done
+    if (lane == 31) sm_warp[wrp] = inc;
+    __syncthreads();
+    int base = 0, tot = 0;
+#pragma unroll
+    for (int k = 0; k < SMP_THREADS / 32; ++k) {
+        const int w = sm_warp[k];
+        if (k < wrp) base += w;
+        tot += w;
+    }
+    total = tot;
+    return base + inc - v;
+}
+
+struct EmitArgs {
+    const int64_t* block_base;  // pass B: first output position of each block
+    int64_t* block_count;       // pass A: accepted draws per block
+    int64_t* raw_used;          // device scalar: raw 32-bit draws consumed by `count` outputs
+    int* status;                // 1 = index out of range, 2 = narrow-table overflow
+    int64_t* indices;           // FILL
+    void* freq;                 // HIST
+    int64_t ldf;
+    const double2* packed;      // GATHER: (x - cx, u - cu) pairs
+    const double* w;
+    double* S0;                 // [nrep, K+1]  (zeroed by the host wrapper)
+    double* S1;
+};
+
+template <typename FT>
+__device__ __forceinline__ void freq_bump(FT* freq, int64_t off, int& bad) {
+    if (sizeof(FT) == 8) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(freq) + off, 1ull);
+    } else if (sizeof(FT) == 4) {
+        const unsigned old = atomicAdd(reinterpret_cast<unsigned*>(freq) + off, 1u);
+        if (old == 0x7fffffffu) bad |= 2;
+    } else {
+        constexpr int BITS = 8 * (int)sizeof(FT);
+        constexpr unsigned MASK = (1u << BITS) - 1u;
+        const int64_t boff = off * (int64_t)sizeof(FT);
+        unsigned* word = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(freq) + (boff & ~3ll));
+        const int sh = (int)(boff & 3) * 8;
+        const unsigned old = atomicAdd(word, 1u << sh);
+        if (((old >> sh) & MASK) == MASK) bad |= 2;
+    }
+}
+
+template <int K, bool HAS_X>
+struct Acc {
+    double s0[K + 1], s1[K + 1];
+    __device__ __forceinline__ void zero() {
+#pragma unroll
+        for (int j = 0; j <= K; ++j) s0[j] = 0.0, s1[j] = 0.0;
+    }
+    // p0 = weight of the draw (0 for an empty slot)
+    __device__ __forceinline__ void push(double2 v, double p0) {
+        double p = p0;
+        s0[0] += p;
+        if (HAS_X) s1[0] = fma(p, v.x, s1[0]);
+#pragma unroll
+        for (int j = 1; j <= K; ++j) {
+            p *= v.y;
+            s0[j] += p;
+            if (HAS_X) s1[j] = fma(p, v.x, s1[j]);
+        }
+    }
+    __device__ __forceinline__ void flush_thread(double* S0, double* S1, int64_t rep) {
+#pragma unroll
+        for (int j = 0; j <= K; ++j) {
+            atomicAdd(S0 + rep * (K + 1) + j, s0[j]);
+            if (HAS_X) atomicAdd(S1 + rep * (K + 1) + j, s1[j]);
+        }
+    }
+    // all threads of the block must call this
+    __device__ __forceinline__ void flush_block(double (*sm)[2 * (K + 1)], double* S0, double* S1,
+                                                int64_t rep) {
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j <= K; ++j) {
+            const double a = warp_sum(s0[j]);
+            const double b = HAS_X ? warp_sum(s1[j]) : 0.0;
+            if (lane == 0) sm[wrp][j] = a, sm[wrp][K + 1 + j] = b;
+        }
+        __syncthreads();
+        if (threadIdx.x < 2 * (K + 1)) {
+            double t = 0.0;
+#pragma unroll
+            for (int k = 0; k < SMP_THREADS / 32; ++k) t += sm[k][threadIdx.x];
+            if (threadIdx.x <= K)
+                atomicAdd(S0 + rep * (K + 1) + threadIdx.x, t);
+            else if (HAS_X)
+                atomicAdd(S1 + rep * (K + 1) + threadIdx.x - (K + 1), t);
+        }
+    }
+};
+
+template <int MODE, int K, bool HAS_X, bool HAS_W, typename FT>
+__global__ void __launch_bounds__(SMP_THREADS, 2)
+    k_sampler(const __grid_constant__ SamplerArgs a, const EmitArgs e) {
+    constexpr int T = SMP_T;
+    constexpr int NSLOT = 2 * T;
+    constexpr int STAGE = SMP_THREADS * NSLOT + 1;  // + the buffered 32-bit half
+    __shared__ int sm_warp[SMP_THREADS / 32];
+    __shared__ uint32_t sm_val[MODE == MODE_COUNT ? 1 : STAGE];
+    __shared__ double sm_red[MODE == MODE_GATHER ? SMP_THREADS / 32 : 1][2 * (K + 1)];
+
+    int64_t P = 0;
+    if (MODE != MODE_COUNT) {
+        P = e.block_base[blockIdx.x];
+        if (P >= a.count) return;
+    }
+    const int64_t q_block = (int64_t)blockIdx.x * a.steps_per_block;
+    uint64_t hi = a.s_hi, lo = a.s_lo;
+    {
+        uint64_t q = (uint64_t)q_block + (uint64_t)threadIdx.x * T;
+        for (int i = 0; q != 0 && i < SMP_NPOW; ++i, q >>= 1)
+            if (q & 1) affine_apply(hi, lo, a.pow2[i]);
+    }
+    const int64_t niter = a.steps_per_block / (SMP_THREADS * T);
+    const uint32_t n = a.n, thresh = a.thresh;
+    long long cnt_total = 0;
+    int bad = 0;
+
+    // GATHER state
+    Acc<K, HAS_X> acc;
+    acc.zero();
+    bool dirty = false;
+    int64_t cur_rep = 0, next_boundary = 0;
+    if (MODE == MODE_HIST || MODE == MODE_GATHER) {
+        cur_rep = P / a.nsamp;
+        next_boundary = (cur_rep + 1) * a.nsamp;
+    }
+
+    for (int64_t it = 0; it < niter; ++it) {
+        uint32_t val[NSLOT];
+        uint32_t mask = 0;
+#pragma unroll
+        for (int k = 0; k < T; ++k) {
+            const uint64_t o = pcg_step_out(hi, lo, a.inc_hi, a.inc_lo);
+            const uint64_t m0 = (uint64_t)(uint32_t)o * n;
+            const uint64_t m1 = (o >> 32) * (uint64_t)n;
+            val[2 * k] = (uint32_t)(m0 >> 32);
+            val[2 * k + 1] = (uint32_t)(m1 >> 32);
+            if ((uint32_t)m0 >= thresh) mask |= 1u << (2 * k);
+            if ((uint32_t)m1 >= thresh) mask |= 1u << (2 * k + 1);
+        }
+        const bool pre = it == 0 && blockIdx.x == 0 && threadIdx.x == 0 && a.pre_valid != 0;
+        uint32_t pre_val = 0;
+        bool pre_acc = false;
+        if (pre) {
+            const uint64_t m = (uint64_t)a.pre_u32 * n;
+            pre_val = (uint32_t)(m >> 32);
+            pre_acc = (uint32_t)m >= thresh;
+        }
+        const int c = __popc(mask) + (pre_acc ? 1 : 0);
+        if (MODE == MODE_COUNT) {
+            cnt_total += c;
+            affine_apply(hi, lo, a.iter_jump);
+            continue;
+        }
+
+        int total;
+        int off = block_scan_excl(c, sm_warp, total);  // (syncs: previous readers of sm_val done)
+        {
+            // raw 32-bit draw number of slot 0 of this thread (0-based, the buffered half is #0)
+            const int64_t q0 = q_block + (it * SMP_THREADS + threadIdx.x) * T;
+            const int64_t raw0 = (int64_t)a.pre_valid + 2 * q0;
+            if (pre_acc) {
+                if (P + off == a.count - 1) *e.raw_used = 1;
+                sm_val[off++] = pre_val;
+            }
+#pragma unroll
+            for (int k = 0; k < NSLOT; ++k) {
+                if (mask & (1u << k)) {
+                    if (P + off == a.count - 1) *e.raw_used = raw0 + k + 1;
+                    sm_val[off++] = val[k];
+                }
+            }
+        }
+        __syncthreads();
+        const int64_t limit = a.count - P;  // entries >= limit are past the requested count
+        const int nvalid = (int64_t)total < limit ? total : (int)limit;
+
+        if (MODE == MODE_FILL) {
+            for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS) e.indices[P + i] = (int64_t)sm_val[i];
+        } else if (MODE == MODE_HIST) {
+            FT* freq = reinterpret_cast<FT*>(e.freq);
+            if (P + nvalid <= next_boundary) {
+                const int64_t row = cur_rep * e.ldf;
+                for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS) freq_bump<FT>(freq, row + sm_val[i], bad);
+            } else {
+                for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS)
+                    freq_bump<FT>(freq, ((P + i) / a.nsamp) * e.ldf + sm_val[i], bad);
+            }
+        } else if (MODE == MODE_GATHER) {
+            if (P + nvalid <= next_boundary) {
+                // fast path: every draw of this iteration belongs to replicate cur_rep
+                constexpr int G = 8;
+                for (int i0 = threadIdx.x; i0 < nvalid; i0 += G * SMP_THREADS) {
+                    double2 v[G];
+                    double pw[G];
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        const int i = i0 + g * SMP_THREADS;
+                        const bool ok = i < nvalid;
+                        const uint32_t s = ok ? sm_val[i] : 0u;
+                        v[g] = ok ? __ldg(e.packed + s) : make_double2(0.0, 0.0);
+                        pw[g] = ok ? (HAS_W ? __ldg(e.w + s) : 1.0) : 0.0;
+                    }
+#pragma unroll
+                    for (int g = 0; g < G; ++g) acc.push(v[g], pw[g]);
+                }
+                dirty = true;
+            } else {
+                // replicate boundary inside this iteration: thread-local tagged accumulation
+                if (dirty) {
+                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+                    acc.zero();
+                    dirty = false;
+                }
+                const int per = (nvalid + SMP_THREADS - 1) / SMP_THREADS;
+                const int i_lo = threadIdx.x * per;
+                const int i_hi = min(nvalid, i_lo + per);
+                int64_t tag = -1;
+                for (int i = i_lo; i < i_hi; ++i) {
+                    const int64_t rep = (P + i) / a.nsamp;
+                    if (rep != tag) {
+                        if (tag >= 0) {
+                            acc.flush_thread(e.S0, e.S1, tag);
+                            acc.zero();
+                        }
+                        tag = rep;
+                    }
+                    const uint32_t s = sm_val[i];
+                    acc.push(__ldg(e.packed + s), HAS_W ? __ldg(e.w + s) : 1.0);
+                }
+                if (tag >= 0) {
+                    acc.flush_thread(e.S0, e.S1, tag);
+                    acc.zero();
+                }
+            }
+        }
+
+        P += total;
+        if (P >= a.count) break;
+        if (MODE == MODE_HIST || MODE == MODE_GATHER) {
+            if (P >= next_boundary) {
+                if (MODE == MODE_GATHER && dirty) {
+                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+                    acc.zero();
+                    dirty = false;
+                }
+                while (P >= next_boundary) ++cur_rep, next_boundary += a.nsamp;
+            }
+        }
+        affine_apply(hi, lo, a.iter_jump);
+    }
+
+    if (MODE == MODE_COUNT) {
+        __shared__ long long sm_cnt[SMP_THREADS / 32];
+        long long v = cnt_total;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) sm_cnt[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            long long t = 0;
+            for (int k = 0; k < SMP_THREADS / 32; ++k) t += sm_cnt[k];
+            e.block_count[blockIdx.x] = t;
+        }
+    }
+    if (MODE == MODE_GATHER && dirty) acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+    if (MODE == MODE_HIST && bad && e.status) atomicOr(e.status, bad);
+}
+
+// exclusive scan of the per-block counts (a few thousand entries); flags a short raw range
+__global__ void k_sampler_scan(const int64_t* __restrict__ cnt, int64_t* __restrict__ base, int nblocks,
+                               int64_t count, int* __restrict__ status) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int64_t run = 0;
+    for (int b = 0; b < nblocks; ++b) {
+        const int64_t c = cnt[b];
+        base[b] = run;
+        run += c;
+    }
+    if (run < count && status) atomicOr(status, 4);
+}
+
+}  // namespace txb
+
+// ------------------------------------------------------------------ host side
+using namespace txb;
+typedef unsigned __int128 u128;
+
+namespace {
+
+constexpr size_t SMP_WS_HEAD = 64 * 1024;  // block counts + bases + scalars
+
+inline u128 mk128(uint64_t hi, uint64_t lo) { return ((u128)hi << 64) | lo; }
+inline Affine mk_affine(u128 a, u128 c) {
+    return Affine{(uint64_t)(a >> 64), (uint64_t)a, (uint64_t)(c >> 64), (uint64_t)c};
+}
+
+struct Plan {
+    SamplerArgs a;
+    int nblocks;
+};
+
+// (a, c) of `delta` LCG steps
+void lcg_jump(u128 inc, uint64_t delta, u128& a_out, u128& c_out) {
+    u128 acc_a = 1, acc_c = 0, cur_a = mk128(PCG_MULT_HI, PCG_MULT_LO), cur_c = inc;
+    while (delta) {
+        if (delta & 1) {
+            acc_a = acc_a * cur_a;
+            acc_c = acc_c * cur_a + cur_c;
+        }
+        cur_c = (cur_a + 1) * cur_c;
+        cur_a = cur_a * cur_a;
+        delta >>= 1;
+    }
+    a_out = acc_a;
+    c_out = acc_c;
+}
+
+int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, Plan& p) {
+    TXB_CHECK_ARG(rng != nullptr, "sampler: rng state is NULL");
+    // ndat == 1 consumes no draws in numpy (rng == 0 shortcut); the Python layer handles it
+    TXB_CHECK_ARG(ndat >= 2 && ndat <= 0xFFFFFFFFll,
+                  "sampler: ndat=%lld outside [2, 2^32-1] (numpy's 32-bit Lemire path)", (long long)ndat);
+    TXB_CHECK_ARG(count >= 1 && nsamp >= 1, "sampler: count=%lld nsamp=%lld must be >= 1",
+                  (long long)count, (long long)nsamp);
+    SamplerArgs& a = p.a;
+    a.s_hi = rng->state_hi, a.s_lo = rng->state_lo, a.inc_hi = rng->inc_hi, a.inc_lo = rng->inc_lo;
+    a.pre_valid = rng->has_uint32 ? 1u : 0u;
+    a.pre_u32 = rng->uinteger;
+    a.n = (uint32_t)ndat;
+    a.thresh = (uint32_t)((0x100000000ull - (uint64_t)ndat) % (uint64_t)ndat);
+    a.count = count;
+    a.nsamp = nsamp;
+    // raw draws needed: mean count / (1 - p) plus a > 12 sigma margin
+    const double prej = (double)a.thresh / 4294967296.0;
+    const double want = ((double)count + 12.0 * sqrt((double)count) + 4096.0) / (1.0 - prej);
+    TXB_CHECK_ARG(want < 1.0e14, "sampler: %lld draws is beyond the jump table", (long long)count);
+    const int64_t raw = (int64_t)want + 1;
+    const int64_t steps = (raw + 1) / 2;
+    const int64_t per_iter = (int64_t)SMP_THREADS * SMP_T;
+    const int64_t iters = (steps + per_iter - 1) / per_iter;
+    int64_t nb = (int64_t)sm_count() * 8;
+    if (nb > iters) nb = iters;
+    const int64_t ipb = (iters + nb - 1) / nb;
+    nb = (iters + ipb - 1) / ipb;
+    p.nblocks = (int)nb;
+    a.steps_per_block = ipb * per_iter;
+    const u128 inc = mk128(rng->inc_hi, rng->inc_lo);
+    u128 ja, jc;
+    lcg_jump(inc, (uint64_t)(SMP_THREADS - 1) * SMP_T, ja, jc);
+    a.iter_jump = mk_affine(ja, jc);
+    u128 ca = mk128(PCG_MULT_HI, PCG_MULT_LO), cc = inc;
+    for (int i = 0; i < SMP_NPOW; ++i) {
+        a.pow2[i] = mk_affine(ca, cc);
+        cc = (ca + 1) * cc;
+        ca = ca * ca;
+    }
+    TXB_CHECK_ARG((size_t)p.nblocks * 16 + 64 <= SMP_WS_HEAD, "sampler: too many blocks");
+    return TXB_OK;
+}
+
+struct Head {
+    int64_t* block_count;
+    int64_t* block_base;
+    int64_t* raw_used;
+};
+
+Head carve_head(void* ws, int nblocks) {
+    int64_t* p = reinterpret_cast<int64_t*>(ws);
+    return Head{p + 8, p + 8 + nblocks, p};
+}
+
+// pass A + scan; leaves e.block_base / e.raw_used ready for pass B
+int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status, cudaStream_t st) {
+    Head h = carve_head(ws, p.nblocks);
+    e.block_count = h.block_count;
+    e.block_base = h.block_base;
+    e.raw_used = raw_used ? raw_used : h.raw_used;
+    e.status = status;
+    if (cudaMemsetAsync(e.raw_used, 0, sizeof(int64_t), st) != cudaSuccess ||
+        (status && cudaMemsetAsync(status, 0, sizeof(int), st) != cudaSuccess)) {
+        set_error("sampler: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    k_sampler<MODE_COUNT, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<count>");
+    k_sampler_scan<<<1, 32, 0, st>>>(h.block_count, h.block_base, p.nblocks, p.a.count, status);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
+    return TXB_OK;
+}
+
+}  // namespace
+
+extern "C" size_t txb_sampler_workspace_bytes(void) { return SMP_WS_HEAD; }
+
+extern "C" int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used) {
+    TXB_CHECK_ARG(rng && raw_used >= 0, "txb_pcg64_advance: bad argument");
+    int64_t r = raw_used;
+    if (r == 0) return TXB_OK;
+    if (rng->has_uint32) {
+        rng->has_uint32 = 0;  // numpy leaves the stale `uinteger` in place
+        --r;
+        if (r == 0) return TXB_OK;
+    }
+    const uint64_t steps = (uint64_t)(r + 1) / 2;
+    u128 ja, jc;
+    lcg_jump(mk128(rng->inc_hi, rng->inc_lo), steps, ja, jc);
+    const u128 s = ja * mk128(rng->state_hi, rng->state_lo) + jc;
+    rng->state_hi = (uint64_t)(s >> 64);
+    rng->state_lo = (uint64_t)s;
+    {  // the high half of the last 64-bit output is buffered (still pending when r is odd)
+        const uint64_t x = rng->state_hi ^ rng->state_lo;
+        const unsigned rot = (unsigned)(rng->state_hi >> 58);
+        const uint64_t o = (x >> rot) | (x << ((64u - rot) & 63u));
+        rng->has_uint32 = (uint32_t)(r & 1);
+        rng->uinteger = (uint32_t)(o >> 32);
+    }
+    return TXB_OK;
+}
+
+extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
+                                   int64_t* raw_used, int* status, void* workspace, size_t ws_bytes,
+                                   void* stream) {
+    TXB_CHECK_ARG(indices && workspace, "txb_sampler_indices: null pointer");
+    if (ws_bytes < SMP_WS_HEAD) {
+        set_error("txb_sampler_indices: workspace too small");
+        return TXB_ERR_WORKSPACE;
+    }
+    Plan p;
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    EmitArgs e{};
+    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    if (rc != TXB_OK) return rc;
+    e.indices = indices;
+    k_sampler<MODE_FILL, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<fill>");
+    return TXB_OK;
+}
+
+extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                                void* freq, int freq_dtype, int64_t ldf, int64_t* raw_used, int* status,
+                                void* workspace, size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(freq && workspace, "txb_sampler_freq: null pointer");
+    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat, "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld",
+                  (long long)nrep, (long long)ldf, (long long)ndat);
+    TXB_CHECK_ARG(freq_dtype >= 0 && freq_dtype <= 3, "txb_sampler_freq: bad freq_dtype %d", freq_dtype);
+    static const size_t esz[4] = {8, 4, 2, 1};
+    TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
+                  "txb_sampler_freq: narrow table rows must be 4-byte aligned");
+    if (ws_bytes < SMP_WS_HEAD) {
+        set_error("txb_sampler_freq: workspace too small");
+        return TXB_ERR_WORKSPACE;
+    }
+    Plan p;
+    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    if (rc != TXB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(freq, 0, (size_t)nrep * ldf * esz[freq_dtype], st) != cudaSuccess) {
+        set_error("txb_sampler_freq: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    EmitArgs e{};
+    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    if (rc != TXB_OK) return rc;
+    e.freq = freq;
+    e.ldf = ldf;
+    switch (freq_dtype) {
+        case TXB_I64: k_sampler<MODE_HIST, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        case TXB_I32: k_sampler<MODE_HIST, 1, false, false, int32_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        case TXB_U16: k_sampler<MODE_HIST, 1, false, false, uint16_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        default:      k_sampler<MODE_HIST, 1, false, false, uint8_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+    }
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
+    return TXB_OK;
+}
+
+extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep) {
+    const size_t dbl = (size_t)(2 * ndat) + (size_t)(2 * nrep * (order + 2)) + 16;
+    return align_up(SMP_WS_HEAD + dbl * sizeof(double) + 512, 256);
+}
+
+extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
+                                        const double* w, int64_t ndat, int64_t ldx, int order, int mode,
+                                        int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
+                                        int* status, void* workspace, size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(u && out && workspace, "txb_sampler_resample_f64: null pointer");
+    TXB_CHECK_ARG(order >= 1 && nrep >= 1, "txb_sampler_resample_f64: order=%d nrep=%lld", order, (long long)nrep);
+    TXB_CHECK_ARG(mode == TXB_MODE_COMOMENTS ? x != nullptr : (mode == TXB_MODE_X_IS_U && x == nullptr),
+                  "txb_sampler_resample_f64: mode COMOMENTS needs x, mode X_IS_U needs x == NULL");
+    if (ws_bytes < txb_sampler_resample_workspace_bytes(ndat, order, nrep)) {
+        set_error("txb_sampler_resample_f64: workspace too small");
+        return TXB_ERR_WORKSPACE;
+    }
+    Plan p;
+    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    if (rc != TXB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ks = mode == TXB_MODE_X_IS_U ? order + 1 : order;
+    char* base = reinterpret_cast<char*>(workspace) + SMP_WS_HEAD;
+    base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(base) + 15) & ~(uintptr_t)15);
+    double2* packed = reinterpret_cast<double2*>(base);
+    double* pivot = reinterpret_cast<double*>(packed + ndat);
+    double* S0 = pivot + 4;
+    double* S1 = S0 + nrep * (order + 2);
+    rc = txb_pivot_f64(x, u, ndat, 1, x ? ldx : 1, 0, pivot, stream);
+    if (rc != TXB_OK) return rc;
+    rc = launch_pack_shifted(x, x ? ldx : 0, u, ndat, pivot, packed, st);
+    if (rc != TXB_OK) return rc;
+    if (cudaMemsetAsync(S0, 0, sizeof(double) * 2 * nrep * (order + 2), st) != cudaSuccess) {
+        set_error("txb_sampler_resample_f64: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    EmitArgs e{};
+    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    if (rc != TXB_OK) return rc;
+    e.packed = packed;
+    e.w = w;
+    e.S0 = S0;
+    e.S1 = S1;
+    TXB_DISPATCH_ORDER(ks, {
+        if (x) {
+            if (w) k_sampler<MODE_GATHER, K, true, true, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+            else   k_sampler<MODE_GATHER, K, true, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+        } else {
+            if (w) k_sampler<MODE_GATHER, K, false, true, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+            else   k_sampler<MODE_GATHER, K, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+        }
+    });
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<gather>");
+    return txb_finalize_f64(S0, S1, pivot, nrep, 1, 1, order, mode, out, stream);
+}

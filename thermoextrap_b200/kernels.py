@@ -6,6 +6,7 @@ arithmetic happens in ``libtxb.so``.
 
 from __future__ import annotations
 
+import ctypes as C
 import os
 
 import numpy as np
@@ -234,6 +235,120 @@ def resample_indices(x, u, indices, order: int, w=None, x_is_u: bool = False) ->
         msg = f"indices out of range [0, {ndat})"
         raise ValueError(msg)
     return out.reshape(nrep_total, *val_shape, 2, order + 1)
+
+
+# ------------------------------------------------------------------ device sampler (K6)
+def pcg64_state(rng: np.random.Generator) -> _lib.Pcg64State:
+    """Snapshot a numpy ``Generator(PCG64)`` as the C ABI's ``txb_pcg64``."""
+    st = rng.bit_generator.state
+    if st.get("bit_generator") != "PCG64":
+        msg = f"the device sampler reproduces PCG64 only, got {st.get('bit_generator')!r}"
+        raise ValueError(msg)
+    s, inc = st["state"]["state"], st["state"]["inc"]
+    m = (1 << 64) - 1
+    return _lib.Pcg64State(s >> 64, s & m, inc >> 64, inc & m, int(st["has_uint32"]), int(st["uinteger"]))
+
+
+def pcg64_commit(rng: np.random.Generator, state: _lib.Pcg64State, raw_used: int) -> None:
+    """Move ``rng`` past ``raw_used`` raw 32-bit draws, exactly as numpy itself would have."""
+    lib = _lib.load()
+    check(lib.txb_pcg64_advance(C.byref(state), int(raw_used)), "txb_pcg64_advance")
+    st = rng.bit_generator.state
+    st["state"]["state"] = (state.state_hi << 64) | state.state_lo
+    st["has_uint32"] = int(state.has_uint32)
+    st["uinteger"] = int(state.uinteger)
+    rng.bit_generator.state = st
+
+
+def _sampler_flags(status: torch.Tensor, what: str) -> None:
+    flag = int(status.item())
+    if flag & 2:
+        raise OverflowError(f"{what}: frequency count exceeds the table's integer type")
+    if flag & 4:
+        raise _lib.TxbError(f"{what}: raw-draw range estimate too short (report this)")
+
+
+def sampler_indices(rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None) -> torch.Tensor:
+    """``rng.choice(ndat, (nrep, nsamp), replace=True)`` generated on the device, bit-exact (int64)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    ndat = nsamp if ndat is None else ndat
+    if ndat == 1:  # numpy draws nothing for a single-valued range
+        return torch.zeros((nrep, nsamp), dtype=torch.int64, device=dev)
+    state = pcg64_state(rng)
+    out = torch.empty((nrep, nsamp), dtype=torch.int64, device=dev)
+    aux = torch.zeros(2, dtype=torch.int64, device=dev)
+    status = aux[1:].view(torch.int32)
+    with torch.cuda.device(dev):
+        ws = _workspace(lib.txb_sampler_workspace_bytes(), dev)
+        st = lib.txb_sampler_indices(C.byref(state), ndat, nrep * nsamp, out.data_ptr(), aux.data_ptr(),
+                                     status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_sampler_indices")
+    launch_count += 3
+    _sampler_flags(status[:1], "txb_sampler_indices")
+    pcg64_commit(rng, state, int(aux[0].item()))
+    return out
+
+
+def sampler_freq(rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None,
+                 dtype: torch.dtype = torch.uint8) -> torch.Tensor:
+    """Frequency table of the same stream, histogrammed on the device without the index table."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    ndat = nsamp if ndat is None else ndat
+    state = pcg64_state(rng)
+    esz = torch.empty((), dtype=dtype).element_size()
+    ldf = -(-ndat * esz // 4) * 4 // esz
+    buf = torch.empty((nrep, ldf), dtype=dtype, device=dev)
+    aux = torch.zeros(2, dtype=torch.int64, device=dev)
+    status = aux[1:].view(torch.int32)
+    with torch.cuda.device(dev):
+        ws = _workspace(lib.txb_sampler_workspace_bytes(), dev)
+        st = lib.txb_sampler_freq(C.byref(state), ndat, nrep, nsamp, buf.data_ptr(), _FREQ_DTYPES[dtype], ldf,
+                                  aux.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_sampler_freq")
+    launch_count += 3
+    _sampler_flags(status[:1], "txb_sampler_freq")
+    pcg64_commit(rng, state, int(aux[0].item()))
+    return buf[:, :ndat]
+
+
+def sampler_resample(rng: np.random.Generator, x, u, nrep: int, order: int, w=None, x_is_u: bool = False,
+                     nsamp: int | None = None, sync_rng: bool = True) -> torch.Tensor:
+    """K2 fused with the generator (scalar x): bootstrap comoments for ``{"nrep": nrep, "rng": rng}``.
+
+    Neither the index nor the frequency table is materialised.  ``sync_rng=False`` skips the
+    device->host read of the consumed-draw count (the caller's ``rng`` is then left untouched).
+    """
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    if x_is_u:
+        x = None
+    x, u, w, ndat, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    if nchan != 1 or ldu != 0:
+        msg = "sampler_resample handles scalar x only; use sampler_freq + resample_vals"
+        raise ValueError(msg)
+    nsamp = ndat if nsamp is None else nsamp
+    state = pcg64_state(rng)
+    out = torch.empty((nrep, 1, 2, order + 1), dtype=torch.float64, device=dev)
+    aux = torch.zeros(2, dtype=torch.int64, device=dev)
+    status = aux[1:].view(torch.int32)
+    mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    with torch.cuda.device(dev):
+        ws = _workspace(lib.txb_sampler_resample_workspace_bytes(ndat, order, nrep), dev)
+        st = lib.txb_sampler_resample_f64(
+            C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, out.data_ptr(),
+            aux.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(),
+        )
+    check(st, "txb_sampler_resample_f64")
+    launch_count += 7
+    if sync_rng:
+        _sampler_flags(status[:1], "txb_sampler_resample_f64")
+        pcg64_commit(rng, state, int(aux[0].item()))
+    return out.reshape(nrep, *val_shape, 2, order + 1)
 
 
 def _tails(data, dev):

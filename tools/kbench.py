@@ -139,6 +139,21 @@ def gather():
         del x, u, idx
 
 
+def sampler():
+    import numpy as np
+    for n, order, nrep in [(10_000_000, 8, 64), (10_000_000, 8, 256), (1_000_000, 8, 256), (100_000_000, 6, 16)]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+        x = torch.randn(n, dtype=torch.float64, device="cuda")
+        rng = np.random.default_rng(0)
+        t, tm = timeit(lambda: K.sampler_resample(rng, x, u, nrep, order, sync_rng=False), warm=2, rep=3)
+        print(json.dumps({"sampler_fused": [n, order, nrep], "ms": t * 1e3, "ms_med": tm * 1e3, "draws_per_s": nrep * n / t, "reps_per_s": nrep / t}))
+        t, tm = timeit(lambda: K.sampler_indices(rng, nrep, n), warm=1, rep=3)
+        print(json.dumps({"sampler_fill": [n, nrep], "ms": t * 1e3, "draws_per_s": nrep * n / t, "GBs": 8 * nrep * n / t / 1e9}))
+        t, tm = timeit(lambda: K.sampler_freq(rng, nrep, n, dtype=torch.uint8), warm=1, rep=3)
+        print(json.dumps({"sampler_hist_u8": [n, nrep], "ms": t * 1e3, "draws_per_s": nrep * n / t}))
+        del x, u
+
+
 def hist():
     for nrep, n, dt in [(64, 10_000_000, torch.int64), (64, 10_000_000, torch.int32), (64, 10_000_000, torch.uint8)]:
         idx = torch.randint(0, n, (nrep, n), device="cuda", dtype=torch.int64)
