@@ -1,0 +1,366 @@
+"""Headline benchmark: BASELINE.json config 2 on N B200s (one process per GPU).
+
+workload ("step") = one pass of thermoextrap's hot path over one batch of synthetic samples:
+    K1  order-8 comoment reduction of 1e7 (x, u) samples      (DataCentralMomentsVals.from_vals)
+    K6  the reference sampler's index stream, nrep=1000        (numpy PCG64, regenerated on device)
+    K2  1000-replicate bootstrap of the comoments              (.resample(sampler={"nrep": 1000}))
+    K7  derivative expressions + Taylor predict per replicate  (beta.factory_extrapmodel().predict)
+
+metric: bootstrap replicates/s (whole job, all ranks).  ``value`` times K1+K6+K2 with samples
+resident in HBM; ``e2e`` times the public API call chain from pinned HOST arrays to HOST
+predictions (H2D + every kernel + K7 + D2H inside the timed region).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+``--impl reference`` times the reference's CPU implementation of the same path (numba port of
+cmomy's push algorithm + live numpy sampler, oracle/cmomy_port.py) on the host cores.
+"""
+
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "bootstrap_replicates_per_s"
+UNIT = "replicates/s"
+NSAMP, ORDER, NREP = 10_000_000, 8, 1000
+BETA0, BETAS = 1.0, [0.9, 0.95, 1.05, 1.1]
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nsamp", type=int, default=NSAMP, help=argparse.SUPPRESS)
+    ap.add_argument("--nrep", type=int, default=NREP, help=argparse.SUPPRESS)
+    ap.add_argument("--order", type=int, default=ORDER, help=argparse.SUPPRESS)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help=argparse.SUPPRESS)
+    return ap.parse_args()
+
+
+def workload_name(a) -> str:
+    return (f"C2: beta extrapolation order {a.order}, {a.nsamp:.0e} samples, scalar x, "
+            f"bootstrap nrep={a.nrep} with the reference sampler's (numpy PCG64) index stream")
+
+
+def make_samples(n: int, seed: int):
+    """u ~ N(175, 5.3^2), x = 1e-3 u + N(0, 0.02^2)  (notebook statistics)."""
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    u = rng.normal(175.0, 5.3, n)
+    x = 1e-3 * u + rng.normal(0.0, 0.02, n)
+    return x, u
+
+
+# --------------------------------------------------------------------------- CPU baseline
+def cpu_reference_rate(a, seconds: float):
+    """Reference path on the host cores, bounded sample: full-width samples, few replicates."""
+    import numba
+    import numpy as np
+
+    from oracle import cmomy_port as cp
+
+    x, u = make_samples(a.nsamp, 0)
+    cp.bootstrap_reference_path(x[:1000], u[:1000], a.order, 2, np.random.default_rng(0))  # JIT
+    cp.reduce_vals(x[:1000], u[:1000], a.order)
+    cores = numba.get_num_threads()
+    # calibrate: one replicate per thread, then size the sample for ~`seconds`
+    t0 = time.perf_counter()
+    cp.bootstrap_reference_path(x, u, a.order, cores, np.random.default_rng(1))
+    t1 = time.perf_counter() - t0
+    nrep = max(cores, int(seconds / t1) * cores)
+    nrep = min(nrep, a.nrep)
+
+    def step():
+        t0 = time.perf_counter()
+        cp.reduce_vals(x, u, a.order)
+        cp.bootstrap_reference_path(x, u, a.order, nrep, np.random.default_rng(1))
+        return time.perf_counter() - t0
+
+    return step, nrep, cores
+
+
+def run_reference(a) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    step, nrep, cores = cpu_reference_rate(a, a.cpu_seconds)
+    for _ in range(min(a.warmup, 1)):
+        step()
+    ts = [step() for _ in range(max(1, a.steps))]
+    t = sum(ts) / len(ts)
+    value = nrep / t
+    sample = (f"{a.nsamp} samples x {nrep} of {a.nrep} replicates per step: K1 push reduce + numpy "
+              f"choice table + indices_to_freq + K2 freq-weighted push (numba, prange over replicates)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+        "steps": len(ts), "warmup": min(a.warmup, 1), "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a), "order": a.order, "nsamp": a.nsamp, "nrep": a.nrep,
+                   "replicates_per_step": nrep},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.rows: list[list[str]] = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
+            )
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self) -> None:
+        for ln in self.proc.stdout:
+            self.rows.append([c.strip() for c in ln.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- B200 arm
+def run_b200(a) -> None:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from thermoextrap_b200 import _lib, backend
+    from thermoextrap_b200 import kernels as K
+    import thermoextrap_b200 as xt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    # replicates are independent: rank r bootstraps its own nrep replicates of its own
+    # sample set (weak scaling, no data-path collective)
+    x_np, u_np = make_samples(a.nsamp, seed=100 + rank)
+    xh = torch.from_numpy(x_np).pin_memory()
+    uh = torch.from_numpy(u_np).pin_memory()
+    xd, ud = xh.to(dev), uh.to(dev)
+    rng = np.random.default_rng(1 + rank)
+
+    def step_device():
+        c = K.reduce_vals(xd, ud, a.order)
+        b = K.sampler_resample(rng, xd, ud, a.nrep, a.order, sync_rng=False)
+        return c, b
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        step_device()
+    barrier()
+
+    clocks = ClockSampler(local) if rank == 0 else None
+    lib.txb_profile_begin(b"sampler_gather")
+    launches0 = K.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(a.steps):
+        step_device()
+    ev1.record()
+    barrier()
+    t_dev = ev0.elapsed_time(ev1) * 1e-3
+    launches = K.launch_count - launches0
+    k_ms, k_n = C.c_double(), C.c_int()
+    _lib.check(lib.txb_profile_end(C.byref(k_ms), C.byref(k_n)), "txb_profile_end")
+
+    # K1 alone (samples/s) and its kernel time, outside the headline region
+    lib.txb_profile_begin(b"reduce")
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    r0.record()
+    for _ in range(a.steps):
+        K.reduce_vals(xd, ud, a.order)
+    r1.record()
+    torch.cuda.synchronize()
+    t_red = r0.elapsed_time(r1) * 1e-3 / a.steps
+    red_ms, red_n = C.c_double(), C.c_int()
+    lib.txb_profile_end(C.byref(red_ms), C.byref(red_n))
+
+    # ---- end to end through the public API: pinned host arrays in, host predictions out
+    xv = xt.DataArray(xh.numpy(), dims=("rec",))
+    uv = xt.DataArray(uh.numpy(), dims=("rec",))
+
+    def step_e2e():
+        backend.clear_device_cache()  # every step uploads its own inputs
+        data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=a.order, central=True)
+        model = xt.beta.factory_extrapmodel(beta=BETA0, data=data)
+        boot = model.resample(sampler={"nrep": a.nrep, "rng": rng})
+        return model.predict(BETAS).values, boot.predict(BETAS).values
+
+    for _ in range(max(a.warmup, 3)):
+        pred, pred_boot = step_e2e()
+    barrier()
+    backend.transfer_bytes.update(h2d=0, d2h=0)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        pred, pred_boot = step_e2e()
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    h2d, d2h = backend.transfer_bytes["h2d"], backend.transfer_bytes["d2h"]
+    clock_info = clocks.stop() if clocks else None
+    assert pred_boot.shape[:2] == (len(BETAS), a.nrep) and np.isfinite(pred_boot).all()
+
+    times = torch.tensor([t_dev, t_e2e, t_red], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    t_dev, t_e2e, t_red = (float(v) for v in times.tolist())
+
+    if rank == 0:
+        emit(a, world, t_dev, t_e2e, t_red, k_ms.value, k_n.value, red_ms.value, red_n.value, launches,
+             h2d // a.steps, d2h // a.steps, clock_info)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def measured_peaks() -> tuple[float, str]:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except (KeyError, ValueError):
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def fp64_peak_tflops() -> float:
+    """DFMA micro-benchmark (MEASURED_PEAKS.json has no fp64 figure)."""
+    import torch
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    scratch = torch.zeros(8, dtype=torch.float64, device="cuda")
+    fl = C.c_double()
+    best = 0.0
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        lib.txb_fp64_peak_launch(20000, 8, scratch.data_ptr(), C.byref(fl), None)
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, fl.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
+
+
+def emit(a, world, t_dev, t_e2e, t_red, k_ms, k_n, red_ms, red_n, launches, h2d, d2h, clock_info) -> None:
+    import torch
+
+    peak, peak_src = measured_peaks()
+    draws = a.nrep * a.nsamp
+    k_s = k_ms * 1e-3 / max(k_n, 1)  # average duration of one k_sampler<GATHER> launch
+    alg_bytes = 16.0 * draws  # one (x - cx, u - cu) pair per bootstrap draw
+    achieved = alg_bytes / k_s / 1e9
+    flops = 4.0 * (a.order + 1) * draws  # 2 (k+1) FMA per draw, scalar x
+    fp64_peak = fp64_peak_tflops()
+    red_s = red_ms * 1e-3 / max(red_n, 1)
+    cpu = None
+    if world == 1:
+        step, nrep_cpu, cores = cpu_reference_rate(a, a.cpu_seconds)
+        t_cpu = step()
+        cpu = {
+            "value": nrep_cpu / t_cpu, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{a.nsamp} samples x {nrep_cpu} of {a.nrep} replicates, one pass "
+                      f"({t_cpu:.1f} s): numba port of cmomy push reduce + numpy choice + indices_to_freq + "
+                      "freq-weighted push, prange over replicates",
+        }
+    line = {
+        "metric": METRIC, "value": a.nrep * world * a.steps / t_dev, "unit": UNIT, "n_gpus": world,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": t_dev / a.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": workload_name(a), "order": a.order, "nsamp": a.nsamp, "nrep": a.nrep,
+            "sharding": "replicates (each rank: own samples, own nrep replicates; no data-path collective)",
+            "l2": "inputs larger than L2 (160 MB of samples per step; 1e10 regenerated draws)",
+            "step": "K1 reduce_vals + K6 device sampler + K2 bootstrap (+finalize), samples resident in HBM",
+        },
+        "e2e": {"value": a.nrep * world * a.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": t_e2e / a.steps * 1e3,
+                "path": "DataCentralMomentsVals.from_vals -> beta.factory_extrapmodel -> .resample({'nrep','rng'}) -> .predict"},
+        "gpu_launches": int(launches),
+        "roofline": {
+            "kernel": "k_sampler<MODE_GATHER> (fused PCG64 sampler + gather + power sums)",
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "peak_source": peak_src, "traffic": None, "launch_ms": k_s * 1e3, "launches_timed": k_n,
+            "share_of_step": k_ms * 1e-3 / t_dev,
+            "fp64": {"achieved_tflops": flops / k_s / 1e12, "peak_tflops": fp64_peak,
+                     "frac": flops / k_s / 1e12 / fp64_peak, "peak_source": "txb_fp64_peak_launch DFMA micro-benchmark, this run"},
+        },
+        "reduce": {"samples_per_s": a.nsamp * world / t_red, "kernel_ms": red_s * 1e3,
+                   "GBps": 16.0 * a.nsamp / red_s / 1e9, "frac_hbm": 16.0 * a.nsamp / red_s / 1e9 / peak},
+        "cpu_baseline": cpu,
+        "clocks": clock_info,
+        "gpu": torch.cuda.get_device_name(0),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main() -> None:
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

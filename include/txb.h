@@ -141,6 +141,9 @@ int txb_resample_indices_f64(const double* x, const double* u, const double* w, 
  * so the caller's numpy Generator continues exactly where numpy would have.
  * *status (device int, may be NULL): 2 = narrow table overflow, 4 = internal raw-range
  * estimate too short (never observed; > 12 sigma).
+ * txb_sampler_prepare runs the counting pass once (and reports raw_used) into the first
+ * txb_sampler_workspace_bytes() bytes of `workspace`; a later emit call given the SAME
+ * (rng, ndat, count) and that workspace with prepared != 0 skips the pass.
  *   txb_sampler_indices : indices[count] int64              (IndexSampler.indices)
  *   txb_sampler_freq    : freq[nrep, ldf] of freq_dtype     (IndexSampler.freq)
  *   txb_sampler_resample_f64 : K2 fused with the generator for scalar x -- neither
@@ -151,17 +154,20 @@ typedef struct txb_pcg64 {
 } txb_pcg64;
 size_t txb_sampler_workspace_bytes(void);
 int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used);
+int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
+                        int* status, void* workspace, size_t ws_bytes, void* stream);
 int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
-                        int64_t* raw_used, int* status, void* workspace, size_t ws_bytes,
-                        void* stream);
+                        int64_t* raw_used, int* status, int prepared, void* workspace,
+                        size_t ws_bytes, void* stream);
 int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp, void* freq,
-                     int freq_dtype, int64_t ldf, int64_t* raw_used, int* status, void* workspace,
-                     size_t ws_bytes, void* stream);
+                     int freq_dtype, int64_t ldf, int64_t* raw_used, int* status, int prepared,
+                     void* workspace, size_t ws_bytes, void* stream);
 size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep);
 int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                              const double* w, int64_t ndat, int64_t ldx, int order, int mode,
                              int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
-                             int* status, void* workspace, size_t ws_bytes, void* stream);
+                             int* status, int prepared, void* workspace, size_t ws_bytes,
+                             void* stream);
 
 /* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------
  * data[nblock, nval, 2, order+1] (cmomy layout).
@@ -204,6 +210,14 @@ int txb_poly_predict_f64(const double* coefs, int np1, int64_t nelem, const doub
 /* ---- measurement helper: fp64 FMA peak micro-benchmark (bench.py roofline) ---
  * scratch: >= 1 device double; *flops (HOST pointer) = flop count of the launch. */
 int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* flops, void* stream);
+
+/* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
+ * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",
+ * "sampler_count", "sampler_gather") is bracketed by CUDA events on its own stream;
+ * txb_profile_end synchronises on them and returns the summed duration and the number of
+ * launches.  No effect on results; not thread safe (measurement only).            */
+int txb_profile_begin(const char* tag);
+int txb_profile_end(double* total_ms, int* nlaunch);
 
 #ifdef __cplusplus
 }

@@ -108,3 +108,28 @@ def poly_predict(coefs, dalpha, mode=0):
     if mode == 1:
         return _t(np.cumsum(terms, axis=1))
     return _t(terms)
+
+
+class SamplerPlan:
+    """Stand-in for ``kernels.SamplerPlan``: live numpy draws the table (it IS the reference sampler)."""
+
+    def __init__(self, rng, nrep, nsamp, ndat=None):
+        self.nrep, self.nsamp = int(nrep), int(nsamp)
+        self.ndat = self.nsamp if ndat is None else int(ndat)
+        self._idx = rng.choice(self.ndat, size=(self.nrep, self.nsamp), replace=True)
+
+
+def sampler_indices(src, nrep=None, nsamp=None, ndat=None):
+    plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, nsamp, ndat)
+    return _t(plan._idx)
+
+
+def sampler_freq(src, nrep=None, nsamp=None, ndat=None, dtype=torch.uint8):
+    plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, nsamp, ndat)
+    return indices_to_freq(plan._idx, plan.ndat, dtype=dtype)
+
+
+def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, sync_rng=True):
+    n = _np(u).shape[0]
+    plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, n if nsamp is None else nsamp, n)
+    return resample_indices(x, u, plan._idx, order, w=w, x_is_u=x_is_u)

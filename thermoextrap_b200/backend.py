@@ -40,6 +40,9 @@ MISSING = _Missing()
 # ------------------------------------------------------------------ device cache
 _dev_cache: dict[tuple, tuple[Any, Any]] = {}
 
+#: bytes actually copied host->device / device->host by this module (bench.py reads these)
+transfer_bytes = {"h2d": 0, "d2h": 0}
+
 
 def to_device(arr: np.ndarray):
     """Upload a host array once; later calls with the same buffer reuse the device copy."""
@@ -52,13 +55,14 @@ def to_device(arr: np.ndarray):
         return hit[1]
     dev = K.device()
     host = np.ascontiguousarray(arr)
+    transfer_bytes["h2d"] += host.nbytes
     t = torch.from_numpy(host)
     if host.nbytes >= (1 << 20) and dev.type == "cuda":
         t = t.pin_memory()
     t = t.to(dev, non_blocking=True)
     try:
         base = arr if arr.base is None else arr
-        ref = weakref.ref(base, lambda _r, k=key: _dev_cache.pop(k, None))
+        ref = weakref.ref(base, lambda _r, k=key, c=_dev_cache: c.pop(k, None))
         _dev_cache[key] = (ref, t)
     except TypeError:
         pass
@@ -100,10 +104,11 @@ class IndexSampler:
     on the device (K6, bit-exact) when needed.
     """
 
-    def __init__(self, indices=None, freq=None, ndat: int | None = None) -> None:
-        if indices is None and freq is None:
+    def __init__(self, indices=None, freq=None, ndat: int | None = None, plan=None) -> None:
+        if indices is None and freq is None and plan is None:
             msg = "must specify indices or freq"
             raise ValueError(msg)
+        self._plan = plan  # kernels.SamplerPlan: the table exists only as generator state
         self._indices = None if indices is None else np.asarray(_values(indices), dtype=np.int64)
         self._freq = None if freq is None else np.asarray(_values(freq), dtype=np.int64)
         if self._indices is not None and self._indices.ndim != 2:
@@ -113,15 +118,27 @@ class IndexSampler:
             msg = "freq must be 2-D [nrep, ndat]"
             raise ValueError(msg)
         if ndat is None:
-            ndat = self._freq.shape[1] if self._freq is not None else self._indices.shape[1]
+            if plan is not None:
+                ndat = plan.ndat
+            else:
+                ndat = self._freq.shape[1] if self._freq is not None else self._indices.shape[1]
         self.ndat = int(ndat)
         self._freq_dev = None
 
     @property
+    def plan(self):
+        """Pending device-side table (``None`` once a host table was given or materialised)."""
+        return self._plan if self._indices is None and self._freq is None else None
+
+    @property
     def indices(self) -> np.ndarray:
         if self._indices is None:
-            # any index table with these frequencies (sorted expansion), as cmomy does
-            self._indices = np.stack([np.repeat(np.arange(self.ndat), f) for f in self._freq])
+            if self._plan is not None:
+                # materialise the (possibly huge) table only because somebody asked for it
+                self._indices = K.sampler_indices(self._plan).to("cpu").numpy()
+            else:
+                # any index table with these frequencies (sorted expansion), as cmomy does
+                self._indices = np.stack([np.repeat(np.arange(self.ndat), f) for f in self._freq])
         return self._indices
 
     @property
@@ -130,6 +147,8 @@ class IndexSampler:
 
     @property
     def nrep(self) -> int:
+        if self._indices is None and self._freq is None:
+            return self._plan.nrep
         return (self._indices if self._indices is not None else self._freq).shape[0]
 
     def freq_device(self, narrow: bool = True):
@@ -141,11 +160,13 @@ class IndexSampler:
         if self._freq is not None:
             self._freq_dev = to_device(self._freq)
             return self._freq_dev
-        idx = to_device(self._indices)
         out = None
         for dt in ((torch.uint8, torch.int32) if narrow else (torch.int64,)):
             try:
-                out = K.indices_to_freq(idx, self.ndat, dtype=dt)
+                if self._indices is None:
+                    out = K.sampler_freq(self._plan, dtype=dt)
+                else:
+                    out = K.indices_to_freq(to_device(self._indices), self.ndat, dtype=dt)
                 break
             except OverflowError:
                 continue
@@ -210,6 +231,10 @@ def factory_sampler(
         raise ValueError(msg)
     nsamp = ndat if nsamp is None else nsamp
     g = random.validate_rng(rng)
+    if replace and 2 <= ndat < 2**32 and type(g.bit_generator).__name__ == "PCG64":
+        # numpy's own stream, regenerated bit-exactly on the device; `g` is advanced now,
+        # exactly as the eager table would have advanced it
+        return IndexSampler(plan=K.SamplerPlan(g, nrep, nsamp, ndat), ndat=ndat)
     idx = g.choice(ndat, size=(nrep, nsamp), replace=replace)
     return IndexSampler(indices=idx, ndat=ndat)
 
@@ -222,6 +247,7 @@ def _mom_dims_tuple(mom_dims, mom_ndim):
 
 
 def _host(t) -> np.ndarray:
+    transfer_bytes["d2h"] += t.numel() * t.element_size()
     return t.to("cpu").numpy()
 
 
@@ -496,6 +522,8 @@ def wrap_resample_vals(
 def resample_device(xd, ud, wd, sampler: IndexSampler, order: int, x_is_u: bool = False):
     """Route one bootstrap to the best kernel: index gather (scalar x) or freq contraction."""
     scalar = x_is_u and ud.ndim == 1 or (xd is not None and xd.ndim == 1)
+    if scalar and sampler.plan is not None and sampler._freq_dev is None:
+        return K.sampler_resample(sampler.plan, xd, ud, order=order, w=wd, x_is_u=x_is_u)
     if scalar and sampler.has_indices and sampler._freq is None:
         return K.resample_indices(xd, ud, to_device(sampler.indices), order, w=wd, x_is_u=x_is_u)
     return K.resample_vals(xd, ud, sampler.freq_device(), order, w=wd, x_is_u=x_is_u)

@@ -7,6 +7,7 @@
 // (k+1 FMA per sample-channel), additive across threads / blocks / GPUs, and
 // a final O(k^2) binomial re-centring per channel (finalize.cu).
 #include <stdarg.h>
+#include <string.h>
 
 #include "txb_common.cuh"
 
@@ -19,6 +20,29 @@ void set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+// ---------------------------------------------------------------- profiling hook
+static char g_prof_tag[64] = "";
+static const int PROF_MAX = 1024;
+static cudaEvent_t g_prof_ev[2 * PROF_MAX];
+static int g_prof_made = 0, g_prof_used = 0;
+
+ProfScope::ProfScope(const char* tag, cudaStream_t st) : st_(st), slot_(-1) {
+    if (g_prof_tag[0] == 0 || strcmp(tag, g_prof_tag) != 0 || g_prof_used >= PROF_MAX) return;
+    while (g_prof_made <= g_prof_used) {
+        if (cudaEventCreate(&g_prof_ev[2 * g_prof_made]) != cudaSuccess ||
+            cudaEventCreate(&g_prof_ev[2 * g_prof_made + 1]) != cudaSuccess) {
+            cudaGetLastError();
+            return;
+        }
+        ++g_prof_made;
+    }
+    slot_ = g_prof_used++;
+    cudaEventRecord(g_prof_ev[2 * slot_], st_);
+}
+ProfScope::~ProfScope() {
+    if (slot_ >= 0) cudaEventRecord(g_prof_ev[2 * slot_ + 1], st_);
 }
 
 int sm_count() {
@@ -398,6 +422,8 @@ static int launch_scalar(const double* x, const double* u, const double* w, int6
     double* ws0 = ws;
     double* ws1 = ws + nb * (K + 1);
     const bool vec = aligned16(u) && (!x || aligned16(x)) && (!w || aligned16(w));
+    {
+    ProfScope prof("reduce", st);
 #define TXB_LAUNCH_SC(HX, HW, V) \
     k_reduce_scalar<K, HX, HW, V><<<(unsigned)nb, 256, 0, st>>>(x, u, w, nsamp, pivot, ws0, ws1)
     if (x) {
@@ -408,6 +434,7 @@ static int launch_scalar(const double* x, const double* u, const double* w, int6
         else   { if (vec) TXB_LAUNCH_SC(false, false, 2); else TXB_LAUNCH_SC(false, false, 1); }
     }
 #undef TXB_LAUNCH_SC
+    }
     TXB_CUDA_LAUNCH_CHECK("k_reduce_scalar");
     int rc = launch_sum_parts(ws0, nb, K + 1, S0, st);
     if (rc == TXB_OK && x) rc = launch_sum_parts(ws1, nb, K + 1, S1, st);
@@ -427,6 +454,8 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     double* ws0 = ws;
     double* ws1 = ws + (UPC ? p.nslabs * nchan * (K + 1) : 0);
     const dim3 grid((unsigned)p.nctiles, (unsigned)p.nslabs);
+    {
+    ProfScope prof("reduce", st);
     if (cpt == 4)
         k_reduce_wide<K, (HAS_X && UPC) ? 2 : 4, HAS_X, UPC>
             <<<grid, 256, 0, st>>>(x, u, w, nsamp, nchan, ldx, ldu, pivot, p.lanes_c, ws0, ws1);
@@ -436,6 +465,7 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     else
         k_reduce_wide<K, 1, HAS_X, UPC>
             <<<grid, 256, 0, st>>>(x, u, w, nsamp, nchan, ldx, ldu, pivot, p.lanes_c, ws0, ws1);
+    }
     TXB_CUDA_LAUNCH_CHECK("k_reduce_wide");
     int rc = TXB_OK;
     if (UPC) rc = launch_sum_parts(ws0, p.nslabs, nchan * (K + 1), S0, st);
@@ -545,4 +575,30 @@ extern "C" int txb_reduce_vals_f64(const double* x, const double* u, const doubl
                              stream);
     if (rc != TXB_OK) return rc;
     return txb_finalize_f64(S0, S1, pivot, 1, nchan, nu, order, mode, out, stream);
+}
+
+// ---------------------------------------------------------------- measurement hook (C ABI)
+extern "C" int txb_profile_begin(const char* tag) {
+    TXB_CHECK_ARG(tag && strlen(tag) < sizeof(txb::g_prof_tag), "txb_profile_begin: bad tag");
+    strcpy(txb::g_prof_tag, tag);
+    txb::g_prof_used = 0;
+    return TXB_OK;
+}
+
+extern "C" int txb_profile_end(double* total_ms, int* nlaunch) {
+    txb::g_prof_tag[0] = 0;
+    double tot = 0.0;
+    for (int i = 0; i < txb::g_prof_used; ++i) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(txb::g_prof_ev[2 * i + 1]) != cudaSuccess ||
+            cudaEventElapsedTime(&ms, txb::g_prof_ev[2 * i], txb::g_prof_ev[2 * i + 1]) != cudaSuccess) {
+            txb::set_error("txb_profile_end: %s", cudaGetErrorString(cudaGetLastError()));
+            return TXB_ERR_CUDA;
+        }
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (nlaunch) *nlaunch = txb::g_prof_used;
+    txb::g_prof_used = 0;
+    return TXB_OK;
 }

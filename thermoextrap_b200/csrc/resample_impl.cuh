@@ -58,7 +58,10 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
         attr_done = true;
     }
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
-    k_resample<K, MODE, NCG, FT><<<grid, 256, C::SMEM, st>>>(a);
+    {
+        ProfScope prof("resample", st);
+        k_resample<K, MODE, NCG, FT><<<grid, 256, C::SMEM, st>>>(a);
+    }
     TXB_CUDA_LAUNCH_CHECK("k_resample");
     int rc = TXB_OK;
     if (want0) rc = launch_sum_parts(a.ws0, p.nslab, n0, S0, st);

@@ -49,7 +49,7 @@ struct SamplerArgs {
     Affine pow2[SMP_NPOW];        // 2^i steps
 };
 
-enum { MODE_COUNT = 0, MODE_FILL = 1, MODE_HIST = 2, MODE_GATHER = 3 };
+enum { MODE_COUNT = 0, MODE_FILL = 1, MODE_HIST = 2, MODE_GATHER = 3, MODE_LOCATE = 4 };
 
 __device__ __forceinline__ void affine_apply(uint64_t& hi, uint64_t& lo, const Affine& f) {
     const uint64_t plo = f.a_lo * lo;
@@ -190,6 +190,8 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
     if (MODE != MODE_COUNT) {
         P = e.block_base[blockIdx.x];
         if (P >= a.count) return;
+        // LOCATE: only the block that emits output #count-1 walks its range (to report raw_used)
+        if (MODE == MODE_LOCATE && P + e.block_count[blockIdx.x] < a.count) return;
     }
     const int64_t q_block = (int64_t)blockIdx.x * a.steps_per_block;
     uint64_t hi = a.s_hi, lo = a.s_lo;
@@ -458,20 +460,33 @@ Head carve_head(void* ws, int nblocks) {
     return Head{p + 8, p + 8 + nblocks, p};
 }
 
-// pass A + scan; leaves e.block_base / e.raw_used ready for pass B
-int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status, cudaStream_t st) {
+// pass A + scan; leaves e.block_base / e.raw_used ready for pass B.  `prepared`: the head of
+// the workspace already holds the result of txb_sampler_prepare for the same (rng, ndat, count).
+int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status, cudaStream_t st,
+                   int prepared = 0) {
     Head h = carve_head(ws, p.nblocks);
     e.block_count = h.block_count;
     e.block_base = h.block_base;
     e.raw_used = raw_used ? raw_used : h.raw_used;
     e.status = status;
+    if (prepared) {
+        if (status && cudaMemsetAsync(status, 0, sizeof(int), st) != cudaSuccess) {
+            set_error("sampler: cudaMemsetAsync failed");
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        return TXB_OK;
+    }
     if (cudaMemsetAsync(e.raw_used, 0, sizeof(int64_t), st) != cudaSuccess ||
         (status && cudaMemsetAsync(status, 0, sizeof(int), st) != cudaSuccess)) {
         set_error("sampler: cudaMemsetAsync failed");
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
-    k_sampler<MODE_COUNT, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    {
+        ProfScope prof("sampler_count", st);
+        k_sampler<MODE_COUNT, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<count>");
     k_sampler_scan<<<1, 32, 0, st>>>(h.block_count, h.block_base, p.nblocks, p.a.count, status);
     TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
@@ -507,9 +522,28 @@ extern "C" int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used) {
     return TXB_OK;
 }
 
+extern "C" int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
+                                   int* status, void* workspace, size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(workspace, "txb_sampler_prepare: null pointer");
+    if (ws_bytes < SMP_WS_HEAD) {
+        set_error("txb_sampler_prepare: workspace too small");
+        return TXB_ERR_WORKSPACE;
+    }
+    Plan p;
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    EmitArgs e{};
+    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    if (rc != TXB_OK) return rc;
+    k_sampler<MODE_LOCATE, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<locate>");
+    return TXB_OK;
+}
+
 extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
-                                   int64_t* raw_used, int* status, void* workspace, size_t ws_bytes,
-                                   void* stream) {
+                                   int64_t* raw_used, int* status, int prepared, void* workspace,
+                                   size_t ws_bytes, void* stream) {
     TXB_CHECK_ARG(indices && workspace, "txb_sampler_indices: null pointer");
     if (ws_bytes < SMP_WS_HEAD) {
         set_error("txb_sampler_indices: workspace too small");
@@ -520,7 +554,7 @@ extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t c
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
     if (rc != TXB_OK) return rc;
     e.indices = indices;
     k_sampler<MODE_FILL, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
@@ -530,7 +564,7 @@ extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t c
 
 extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
                                 void* freq, int freq_dtype, int64_t ldf, int64_t* raw_used, int* status,
-                                void* workspace, size_t ws_bytes, void* stream) {
+                                int prepared, void* workspace, size_t ws_bytes, void* stream) {
     TXB_CHECK_ARG(freq && workspace, "txb_sampler_freq: null pointer");
     TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat, "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld",
                   (long long)nrep, (long long)ldf, (long long)ndat);
@@ -552,7 +586,7 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
         return TXB_ERR_CUDA;
     }
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
     if (rc != TXB_OK) return rc;
     e.freq = freq;
     e.ldf = ldf;
@@ -574,7 +608,8 @@ extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, 
 extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                                         const double* w, int64_t ndat, int64_t ldx, int order, int mode,
                                         int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
-                                        int* status, void* workspace, size_t ws_bytes, void* stream) {
+                                        int* status, int prepared, void* workspace, size_t ws_bytes,
+                                        void* stream) {
     TXB_CHECK_ARG(u && out && workspace, "txb_sampler_resample_f64: null pointer");
     TXB_CHECK_ARG(order >= 1 && nrep >= 1, "txb_sampler_resample_f64: order=%d nrep=%lld", order, (long long)nrep);
     TXB_CHECK_ARG(mode == TXB_MODE_COMOMENTS ? x != nullptr : (mode == TXB_MODE_X_IS_U && x == nullptr),
@@ -604,12 +639,14 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
         return TXB_ERR_CUDA;
     }
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st);
+    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
     if (rc != TXB_OK) return rc;
     e.packed = packed;
     e.w = w;
     e.S0 = S0;
     e.S1 = S1;
+    {
+    ProfScope prof("sampler_gather", st);
     TXB_DISPATCH_ORDER(ks, {
         if (x) {
             if (w) k_sampler<MODE_GATHER, K, true, true, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
@@ -619,6 +656,7 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             else   k_sampler<MODE_GATHER, K, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
         }
     });
+    }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<gather>");
     return txb_finalize_f64(S0, S1, pivot, nrep, 1, 1, order, mode, out, stream);
 }

@@ -14,6 +14,15 @@ namespace txb {
 void set_error(const char* fmt, ...);
 int  sm_count();
 
+// Measurement hook (txb_profile_begin / txb_profile_end in txb.h): while a tag is active,
+// launches wrapped in a ProfScope of that tag are bracketed by CUDA events on their stream.
+struct ProfScope {
+    ProfScope(const char* tag, cudaStream_t st);
+    ~ProfScope();
+    cudaStream_t st_;
+    int slot_;
+};
+
 #define TXB_CHECK_ARG(cond, ...)                  \
     do {                                          \
         if (!(cond)) {                            \

@@ -268,59 +268,98 @@ def _sampler_flags(status: torch.Tensor, what: str) -> None:
         raise _lib.TxbError(f"{what}: raw-draw range estimate too short (report this)")
 
 
-def sampler_indices(rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None) -> torch.Tensor:
-    """``rng.choice(ndat, (nrep, nsamp), replace=True)`` generated on the device, bit-exact (int64)."""
+class SamplerPlan:
+    """A pending ``rng.choice(ndat, (nrep, nsamp))`` table that lives only as generator state.
+
+    Creating the plan runs the device counting pass, learns how many raw draws the table
+    consumes and moves ``rng`` past them immediately -- exactly what numpy does when the
+    reference builds the table eagerly -- so later use of ``rng`` stays bit-identical.  The
+    table itself (80 GB at BASELINE config 2) is regenerated inside whichever kernel needs it.
+    """
+
+    def __init__(self, rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None) -> None:
+        global launch_count
+        lib = _lib.load()
+        dev = device()
+        self.nrep, self.nsamp = int(nrep), int(nsamp)
+        self.ndat = self.nsamp if ndat is None else int(ndat)
+        self.state = pcg64_state(rng)
+        self.head = torch.empty(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device=dev)
+        aux = torch.zeros(2, dtype=torch.int64, device=dev)
+        status = aux[1:].view(torch.int32)
+        with torch.cuda.device(dev):
+            st = lib.txb_sampler_prepare(C.byref(self.state), self.ndat, self.nrep * self.nsamp, aux.data_ptr(),
+                                         status.data_ptr(), self.head.data_ptr(), self.head.numel(), _stream_ptr())
+        check(st, "txb_sampler_prepare")
+        launch_count += 3
+        _sampler_flags(status[:1], "txb_sampler_prepare")
+        self.raw_used = int(aux[0].item())
+        after = _lib.Pcg64State.from_buffer_copy(self.state)
+        pcg64_commit(rng, after, self.raw_used)
+
+    def workspace(self, nbytes: int, dev) -> torch.Tensor:
+        ws = _workspace(max(nbytes, self.head.numel()), dev)
+        ws[: self.head.numel()].copy_(self.head)
+        return ws
+
+
+def _plan_of(src, nrep, nsamp, ndat) -> SamplerPlan:
+    if isinstance(src, SamplerPlan):
+        return src
+    return SamplerPlan(src, nrep, nsamp, ndat)
+
+
+def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None) -> torch.Tensor:
+    """``rng.choice(ndat, (nrep, nsamp), replace=True)`` generated on the device, bit-exact (int64).
+
+    ``src`` is a numpy ``Generator(PCG64)`` (advanced as numpy would) or a :class:`SamplerPlan`.
+    """
     global launch_count
     lib = _lib.load()
     dev = device()
-    ndat = nsamp if ndat is None else ndat
-    if ndat == 1:  # numpy draws nothing for a single-valued range
-        return torch.zeros((nrep, nsamp), dtype=torch.int64, device=dev)
-    state = pcg64_state(rng)
-    out = torch.empty((nrep, nsamp), dtype=torch.int64, device=dev)
-    aux = torch.zeros(2, dtype=torch.int64, device=dev)
-    status = aux[1:].view(torch.int32)
+    if not isinstance(src, SamplerPlan) and (nsamp if ndat is None else ndat) == 1:
+        return torch.zeros((nrep, nsamp), dtype=torch.int64, device=dev)  # numpy draws nothing here
+    plan = _plan_of(src, nrep, nsamp, ndat)
+    out = torch.empty((plan.nrep, plan.nsamp), dtype=torch.int64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        ws = _workspace(lib.txb_sampler_workspace_bytes(), dev)
-        st = lib.txb_sampler_indices(C.byref(state), ndat, nrep * nsamp, out.data_ptr(), aux.data_ptr(),
-                                     status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+        ws = plan.workspace(0, dev)
+        st = lib.txb_sampler_indices(C.byref(plan.state), plan.ndat, plan.nrep * plan.nsamp, out.data_ptr(), None,
+                                     status.data_ptr(), 1, ws.data_ptr(), ws.numel(), _stream_ptr())
     check(st, "txb_sampler_indices")
-    launch_count += 3
-    _sampler_flags(status[:1], "txb_sampler_indices")
-    pcg64_commit(rng, state, int(aux[0].item()))
+    launch_count += 1
     return out
 
 
-def sampler_freq(rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None,
+def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
                  dtype: torch.dtype = torch.uint8) -> torch.Tensor:
     """Frequency table of the same stream, histogrammed on the device without the index table."""
     global launch_count
     lib = _lib.load()
     dev = device()
-    ndat = nsamp if ndat is None else ndat
-    state = pcg64_state(rng)
+    plan = _plan_of(src, nrep, nsamp, ndat)
     esz = torch.empty((), dtype=dtype).element_size()
-    ldf = -(-ndat * esz // 4) * 4 // esz
-    buf = torch.empty((nrep, ldf), dtype=dtype, device=dev)
-    aux = torch.zeros(2, dtype=torch.int64, device=dev)
-    status = aux[1:].view(torch.int32)
+    ldf = -(-plan.ndat * esz // 4) * 4 // esz
+    buf = torch.empty((plan.nrep, ldf), dtype=dtype, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        ws = _workspace(lib.txb_sampler_workspace_bytes(), dev)
-        st = lib.txb_sampler_freq(C.byref(state), ndat, nrep, nsamp, buf.data_ptr(), _FREQ_DTYPES[dtype], ldf,
-                                  aux.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+        ws = plan.workspace(0, dev)
+        st = lib.txb_sampler_freq(C.byref(plan.state), plan.ndat, plan.nrep, plan.nsamp, buf.data_ptr(),
+                                  _FREQ_DTYPES[dtype], ldf, None, status.data_ptr(), 1, ws.data_ptr(), ws.numel(),
+                                  _stream_ptr())
     check(st, "txb_sampler_freq")
-    launch_count += 3
-    _sampler_flags(status[:1], "txb_sampler_freq")
-    pcg64_commit(rng, state, int(aux[0].item()))
-    return buf[:, :ndat]
+    launch_count += 2
+    _sampler_flags(status, "txb_sampler_freq")
+    return buf[:, : plan.ndat]
 
 
-def sampler_resample(rng: np.random.Generator, x, u, nrep: int, order: int, w=None, x_is_u: bool = False,
+def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
                      nsamp: int | None = None, sync_rng: bool = True) -> torch.Tensor:
     """K2 fused with the generator (scalar x): bootstrap comoments for ``{"nrep": nrep, "rng": rng}``.
 
-    Neither the index nor the frequency table is materialised.  ``sync_rng=False`` skips the
-    device->host read of the consumed-draw count (the caller's ``rng`` is then left untouched).
+    Neither the index nor the frequency table is materialised.  With a raw ``Generator`` and
+    ``sync_rng=False`` the counting pass runs inside the call and ``rng`` is left untouched
+    (no device->host read at all: the benchmark's steady-state form).
     """
     global launch_count
     lib = _lib.load()
@@ -332,22 +371,25 @@ def sampler_resample(rng: np.random.Generator, x, u, nrep: int, order: int, w=No
         msg = "sampler_resample handles scalar x only; use sampler_freq + resample_vals"
         raise ValueError(msg)
     nsamp = ndat if nsamp is None else nsamp
-    state = pcg64_state(rng)
+    if isinstance(src, SamplerPlan) or sync_rng:
+        plan = _plan_of(src, nrep, nsamp, ndat)
+        if plan.ndat != ndat:
+            msg = f"sampler ndat={plan.ndat} does not match {ndat} samples"
+            raise ValueError(msg)
+        state, nrep, nsamp, prepared = plan.state, plan.nrep, plan.nsamp, 1
+    else:
+        plan, state, prepared = None, pcg64_state(src), 0
     out = torch.empty((nrep, 1, 2, order + 1), dtype=torch.float64, device=dev)
-    aux = torch.zeros(2, dtype=torch.int64, device=dev)
-    status = aux[1:].view(torch.int32)
     mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
     with torch.cuda.device(dev):
-        ws = _workspace(lib.txb_sampler_resample_workspace_bytes(ndat, order, nrep), dev)
+        nb = lib.txb_sampler_resample_workspace_bytes(ndat, order, nrep)
+        ws = plan.workspace(nb, dev) if plan is not None else _workspace(nb, dev)
         st = lib.txb_sampler_resample_f64(
             C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, out.data_ptr(),
-            aux.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(),
+            None, None, prepared, ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_sampler_resample_f64")
-    launch_count += 7
-    if sync_rng:
-        _sampler_flags(status[:1], "txb_sampler_resample_f64")
-        pcg64_commit(rng, state, int(aux[0].item()))
+    launch_count += 5 if prepared else 7
     return out.reshape(nrep, *val_shape, 2, order + 1)
 
 

@@ -1,0 +1,29 @@
+"""Short launch sequence for `ncu --set full` captures of the hot kernels (development tool).
+
+usage: python tools/ncu_case.py [gather|reduce|resample]
+  gather  : count pass (k_sampler #0) then the fused sampler+bootstrap (k_sampler #1), C2 width, 64 replicates
+"""
+
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import numpy as np
+import torch
+
+from thermoextrap_b200 import kernels as K
+
+which = sys.argv[1] if len(sys.argv) > 1 else "gather"
+n = 10_000_000
+u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+x = 1e-3 * u + 0.02 * torch.randn(n, dtype=torch.float64, device="cuda")
+if which == "gather":
+    nrep = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+    K.sampler_resample(np.random.default_rng(1), x, u, nrep, 8, sync_rng=False)
+elif which == "reduce":
+    K.reduce_vals(x, u, 8)
+elif which == "resample":
+    f8 = K.sampler_freq(np.random.default_rng(1), 64, n, dtype=torch.uint8)
+    K.resample_vals(x, u, f8, 8)
+torch.cuda.synchronize()
