@@ -156,18 +156,32 @@ size_t txb_sampler_workspace_bytes(void);
 int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used);
 int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
                         int* status, void* workspace, size_t ws_bytes, void* stream);
-int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
-                        int64_t* raw_used, int* status, int prepared, void* workspace,
-                        size_t ws_bytes, void* stream);
-int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp, void* freq,
-                     int freq_dtype, int64_t ldf, int64_t* raw_used, int* status, int prepared,
-                     void* workspace, size_t ws_bytes, void* stream);
+/* Multi-GPU form of txb_sampler_prepare: the counting pass is split by thread block.  Rank g runs
+ * txb_sampler_count on blocks [block_lo, block_hi) of txb_sampler_nblocks(...) (entries outside
+ * the range are zeroed), the ranks SUM the int64 array block_count = ((int64_t*)workspace) + 8
+ * (nblocks entries; one small all-reduce), and txb_sampler_scan finishes the preparation.
+ * block_hi < 0 means "to the end".                                                        */
+int txb_sampler_nblocks(const txb_pcg64* rng, int64_t ndat, int64_t count);
+int txb_sampler_count(const txb_pcg64* rng, int64_t ndat, int64_t count, int block_lo, int block_hi,
+                      void* workspace, size_t ws_bytes, void* stream);
+int txb_sampler_scan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
+                     int* status, void* workspace, size_t ws_bytes, void* stream);
+/* Emit calls take a window so that ranks can own slices of ONE numpy table:
+ * positions [pos_lo, pos_hi) of the flattened table / replicates [rep_lo, rep_hi); outputs hold
+ * only the window (indices[pos_hi - pos_lo], freq[rep_hi - rep_lo, ldf], out[rep_hi - rep_lo, ...]). */
+int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t pos_lo,
+                        int64_t pos_hi, int64_t* indices, int64_t* raw_used, int* status,
+                        int prepared, void* workspace, size_t ws_bytes, void* stream);
+int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                     int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
+                     int64_t* raw_used, int* status, int prepared, void* workspace, size_t ws_bytes,
+                     void* stream);
 size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep);
 int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                              const double* w, int64_t ndat, int64_t ldx, int order, int mode,
-                             int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
-                             int* status, int prepared, void* workspace, size_t ws_bytes,
-                             void* stream);
+                             int64_t nrep, int64_t nsamp, int64_t rep_lo, int64_t rep_hi, double* out,
+                             int64_t* raw_used, int* status, int prepared, void* workspace,
+                             size_t ws_bytes, void* stream);
 
 /* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------
  * data[nblock, nval, 2, order+1] (cmomy layout).

@@ -113,23 +113,53 @@ def poly_predict(coefs, dalpha, mode=0):
 class SamplerPlan:
     """Stand-in for ``kernels.SamplerPlan``: live numpy draws the table (it IS the reference sampler)."""
 
-    def __init__(self, rng, nrep, nsamp, ndat=None):
+    def __init__(self, rng, nrep, nsamp, ndat=None, group=None):
         self.nrep, self.nsamp = int(nrep), int(nsamp)
         self.ndat = self.nsamp if ndat is None else int(ndat)
         self._idx = rng.choice(self.ndat, size=(self.nrep, self.nsamp), replace=True)
 
 
-def sampler_indices(src, nrep=None, nsamp=None, ndat=None):
+def _win(plan, reps):
+    return slice(None) if reps is None else slice(int(reps[0]), int(reps[1]))
+
+
+def sampler_indices(src, nrep=None, nsamp=None, ndat=None, reps=None):
     plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, nsamp, ndat)
-    return _t(plan._idx)
+    return _t(plan._idx[_win(plan, reps)])
 
 
-def sampler_freq(src, nrep=None, nsamp=None, ndat=None, dtype=torch.uint8):
+def sampler_freq(src, nrep=None, nsamp=None, ndat=None, dtype=torch.uint8, reps=None):
     plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, nsamp, ndat)
-    return indices_to_freq(plan._idx, plan.ndat, dtype=dtype)
+    return indices_to_freq(plan._idx[_win(plan, reps)], plan.ndat, dtype=dtype)
 
 
-def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, sync_rng=True):
+def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, sync_rng=True, reps=None):
     n = _np(u).shape[0]
     plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, n if nsamp is None else nsamp, n)
-    return resample_indices(x, u, plan._idx, order, w=w, x_is_u=x_is_u)
+    return resample_indices(x, u, plan._idx[_win(plan, reps)], order, w=w, x_is_u=x_is_u)
+
+
+def reduce_sums(x, u, order, w=None, pivot=None):
+    x, u = _np(x).astype(np.float64), _np(u).astype(np.float64)
+    val_shape = x.shape[1:]
+    x2 = x.reshape(x.shape[0], -1)
+    if pivot is None:
+        pivot = _t(np.concatenate([x2[:256].mean(0), [u[:256].mean()]]))
+    pv = _np(pivot)
+    dx, du = x2 - pv[:-1], u - pv[-1]
+    ww = np.ones_like(u) if w is None else _np(w)
+    pw = du[:, None] ** np.arange(order + 1)[None, :] * ww[:, None]
+    return pivot, _t(pw.sum(0)[None, :]), _t(dx.T @ pw), val_shape
+
+
+def finalize_sums(pivot, S0, S1, order, x_is_u=False, val_shape=()):
+    pv, s0, s1 = _np(pivot), _np(S0), _np(S1)
+    nchan = s1.shape[0]
+    raw = np.zeros((nchan, 2, order + 1))
+    raw[:, 0, :] = s0[0] / s0[0, 0]
+    raw[:, 1, :] = s1 / s0[0, 0]
+    raw[:, 0, 0] = s0[0, 0]
+    out = oc.raw_to_central(raw)
+    out[:, 1, 0] += pv[:-1]
+    out[:, 0, 1] += pv[-1]
+    return _t(out.reshape(*val_shape, 2, order + 1))

@@ -1,0 +1,76 @@
+"""World-size-2 runs of the multi-GPU host logic on CPU (gloo), kernels replaced by the oracle stand-in.
+
+What is under test: sharding arithmetic, the common-pivot broadcast, the all_reduce of additive
+sums, replicate windows and the all_gather of slabs (thermoextrap_b200/parallel.py) -- the same
+code that runs over NCCL on the GPUs.
+"""
+
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out_dir):
+    sys.path.insert(0, str(ROOT))
+    sys.path.insert(0, str(ROOT / "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import fake_kernels
+
+    import thermoextrap_b200.parallel as par
+
+    par.K = fake_kernels
+    from oracle import comoments as oc
+
+    rng = np.random.default_rng(0)
+    n, nv, order, nrep = 1001, 3, 5, 7
+    u = rng.normal(10.0, 2.0, n)
+    x = 0.3 * u[:, None] + rng.normal(0.0, 1.0, (n, nv))
+    lo, hi = par.shard_range(n, rank, world)
+    # samples sharded
+    red = par.reduce_vals_sharded(x[lo:hi], u[lo:hi], order).numpy()
+    ref = oc.comoments_two_pass(x, u, order)
+    assert np.all(np.abs(red - ref) <= 1e-9 * np.maximum(np.abs(ref), oc.tolerance_scale(x, u, order)))
+    # replicates sharded: one numpy table split over the ranks
+    g = np.random.default_rng(123)
+    boot = par.bootstrap_sharded(g, x[:, 0], u, nrep, order).numpy()
+    idx = np.random.default_rng(123).choice(n, (nrep, n))
+    bref = oc.resample_vals_gather(x[:, 0], u, order, idx)
+    assert boot.shape == bref.shape
+    assert np.all(np.abs(boot - bref) <= 1e-9 * np.maximum(np.abs(bref), oc.tolerance_scale(x[:, 0], u, order)))
+    slab = par.bootstrap_sharded(np.random.default_rng(123), x[:, 0], u, nrep, order, gather=False).numpy()
+    a, b = par.shard_range(nrep, rank, world)
+    assert np.allclose(slab, bref[a:b], rtol=1e-9, atol=1e-12)
+    (Path(out_dir) / f"ok{rank}").write_text("ok")
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_paths_gloo(tmp_path, world):
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert sorted(p.name for p in tmp_path.iterdir()) == [f"ok{r}" for r in range(world)]
+
+
+def test_shard_range_is_a_partition():
+    from thermoextrap_b200.parallel import shard_range
+
+    for n in (0, 1, 7, 1000):
+        for world in (1, 2, 3, 8):
+            cuts = [shard_range(n, r, world) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n
+            assert all(cuts[i][1] == cuts[i + 1][0] for i in range(world - 1))
+            assert max(b - a for a, b in cuts) - min(b - a for a, b in cuts) <= 1

@@ -132,3 +132,74 @@ def test_full_size_properties(K):
     freq = K.indices_to_freq(idx, n, dtype=torch.uint8)
     via_freq = K.resample_vals(x, u, freq, order)
     assert torch.allclose(fused, via_freq, rtol=1e-9, atol=0)
+
+
+# ------------------------------------------------------------------ windows / split counting (multi-GPU form)
+def test_replicate_windows_tile_the_table(K):
+    import torch
+
+    nrep, n, order = 11, 50_000, 6
+    rng = np.random.default_rng(3)
+    u = rng.normal(0.0, 1.0, n)
+    x = u + rng.normal(0.0, 1.0, n)
+    ref_idx = np.random.default_rng(9).choice(n, (nrep, n))
+    plan = K.SamplerPlan(np.random.default_rng(9), nrep, n)
+    whole = K.sampler_resample(plan, x, u, order=order)
+    cuts = [(0, 4), (4, 5), (5, 11)]
+    parts = [K.sampler_resample(plan, x, u, order=order, reps=c) for c in cuts]
+    assert torch.allclose(torch.cat(parts), whole, rtol=1e-12, atol=0)
+    for a, b in cuts:
+        assert np.array_equal(K.sampler_indices(plan, reps=(a, b)).cpu().numpy(), ref_idx[a:b])
+        f = K.sampler_freq(plan, dtype=torch.int32, reps=(a, b)).cpu().numpy()
+        assert np.array_equal(f.astype(np.int64), oc.indices_to_freq(ref_idx[a:b], n))
+    with pytest.raises(ValueError):
+        K.sampler_indices(plan, reps=(5, 12))
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_split_count_equals_prepare(K, world):
+    """Ranks counting disjoint block ranges + integer SUM == the single-GPU preparation."""
+    import ctypes as C
+
+    import torch
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    nrep, n = 5, 3_000_000
+    plan = K.SamplerPlan(np.random.default_rng(4), nrep, n)
+    state = K.pcg64_state(np.random.default_rng(4))
+    nb = lib.txb_sampler_nblocks(C.byref(state), n, nrep * n)
+    assert nb > 0
+    heads = []
+    for r in range(world):
+        h = torch.zeros(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device="cuda")
+        lo, hi = nb * r // world, nb * (r + 1) // world
+        assert lib.txb_sampler_count(C.byref(state), n, nrep * n, lo, hi, h.data_ptr(), h.numel(), None) == 0
+        heads.append(h.view(torch.int64))
+    total = heads[0].clone()
+    for h in heads[1:]:
+        total[8 : 8 + nb] += h[8 : 8 + nb]
+    aux = torch.zeros(2, dtype=torch.int64, device="cuda")
+    assert lib.txb_sampler_scan(C.byref(state), n, nrep * n, aux.data_ptr(), aux[1:].data_ptr(), total.data_ptr(),
+                                total.numel() * 8, None) == 0
+    ref = plan.head.view(torch.int64)
+    assert torch.equal(total[8 : 8 + 2 * nb], ref[8 : 8 + 2 * nb])
+    assert int(aux[0]) == plan.raw_used
+
+
+def test_sums_are_additive_across_shards(K):
+    import torch
+
+    x, u, _ = (lambda r: (r.normal(1.0, 2.0, (9000, 4)), r.normal(175.0, 5.3, 9000), None))(np.random.default_rng(0))
+    order = 6
+    pivot, _, _, _ = K.reduce_sums(x[:1024], u[:1024], 1)
+    tot0 = tot1 = None
+    for lo, hi in [(0, 1000), (1000, 1001), (1001, 9000)]:
+        _, s0, s1, vs = K.reduce_sums(x[lo:hi], u[lo:hi], order, pivot=pivot)
+        tot0 = s0 if tot0 is None else tot0 + s0
+        tot1 = s1 if tot1 is None else tot1 + s1
+    out = K.finalize_sums(pivot, tot0, tot1, order, val_shape=vs).cpu().numpy()
+    ref = oc.comoments_two_pass(x, u, order)
+    assert float((np.abs(out - ref) / np.maximum(np.abs(ref), oc.tolerance_scale(x, u, order))).max()) < TOL
+    assert torch.allclose(torch.from_numpy(out), K.reduce_vals(x, u, order).cpu(), rtol=1e-11, atol=1e-13)

@@ -53,12 +53,15 @@ SIGNATURES = {
     "txb_sampler_workspace_bytes": (_sz, []),
     "txb_pcg64_advance": (_int, [_p, _i64]),
     "txb_sampler_prepare": (_int, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
-    "txb_sampler_indices": (_int, [_p, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p]),
-    "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _int, _p, _sz, _p]),
+    "txb_sampler_nblocks": (_int, [_p, _i64, _i64]),
+    "txb_sampler_count": (_int, [_p, _i64, _i64, _int, _int, _p, _sz, _p]),
+    "txb_sampler_scan": (_int, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "txb_sampler_indices": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p]),
+    "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _int, _p, _sz, _p]),
     "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64]),
     "txb_sampler_resample_f64": (
         _int,
-        [_p, _p, _p, _p, _i64, _i64, _int, _int, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p],
+        [_p, _p, _p, _p, _i64, _i64, _int, _int, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p],
     ),
     "txb_reduce_data_f64": (_int, [_p, _i64, _i64, _int, _p, _p]),
     "txb_resample_data_f64": (_int, [_p, _p, _i64, _i64, _i64, _int, _p, _p]),

@@ -106,6 +106,9 @@ struct EmitArgs {
     const double* w;
     double* S0;                 // [nrep, K+1]  (zeroed by the host wrapper)
     double* S1;
+    int64_t pos_lo, pos_hi;     // only outputs with pos_lo <= position < pos_hi are consumed (rank window)
+    int64_t rep_lo;             // first replicate of the window: output rows are relative to it
+    int block_offset;           // COUNT: first block of this launch (ranks count disjoint block ranges)
 };
 
 template <typename FT>
@@ -186,14 +189,17 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
     __shared__ uint32_t sm_val[MODE == MODE_COUNT ? 1 : STAGE];
     __shared__ double sm_red[MODE == MODE_GATHER ? SMP_THREADS / 32 : 1][2 * (K + 1)];
 
+    const int bid = blockIdx.x + (MODE == MODE_COUNT ? e.block_offset : 0);
     int64_t P = 0;
     if (MODE != MODE_COUNT) {
-        P = e.block_base[blockIdx.x];
+        P = e.block_base[bid];
         if (P >= a.count) return;
+        const int64_t P_end = P + e.block_count[bid];
         // LOCATE: only the block that emits output #count-1 walks its range (to report raw_used)
-        if (MODE == MODE_LOCATE && P + e.block_count[blockIdx.x] < a.count) return;
+        if (MODE == MODE_LOCATE && P_end < a.count) return;
+        if (MODE != MODE_LOCATE && (P >= e.pos_hi || P_end <= e.pos_lo)) return;  // outside the window
     }
-    const int64_t q_block = (int64_t)blockIdx.x * a.steps_per_block;
+    const int64_t q_block = (int64_t)bid * a.steps_per_block;
     uint64_t hi = a.s_hi, lo = a.s_lo;
     {
         uint64_t q = (uint64_t)q_block + (uint64_t)threadIdx.x * T;
@@ -228,7 +234,7 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
             if ((uint32_t)m0 >= thresh) mask |= 1u << (2 * k);
             if ((uint32_t)m1 >= thresh) mask |= 1u << (2 * k + 1);
         }
-        const bool pre = it == 0 && blockIdx.x == 0 && threadIdx.x == 0 && a.pre_valid != 0;
+        const bool pre = it == 0 && bid == 0 && threadIdx.x == 0 && a.pre_valid != 0;
         uint32_t pre_val = 0;
         bool pre_acc = false;
         if (pre) {
@@ -262,25 +268,29 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
             }
         }
         __syncthreads();
-        const int64_t limit = a.count - P;  // entries >= limit are past the requested count
-        const int nvalid = (int64_t)total < limit ? total : (int)limit;
+        // entries [nlow, nvalid) of this iteration lie inside [pos_lo, min(pos_hi, count))
+        const int64_t limit = (e.pos_hi < a.count ? e.pos_hi : a.count) - P;
+        const int nvalid = limit <= 0 ? 0 : ((int64_t)total < limit ? total : (int)limit);
+        const int64_t below = e.pos_lo - P;
+        const int nlow = below <= 0 ? 0 : (below < (int64_t)nvalid ? (int)below : nvalid);
 
         if (MODE == MODE_FILL) {
-            for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS) e.indices[P + i] = (int64_t)sm_val[i];
+            for (int i = nlow + threadIdx.x; i < nvalid; i += SMP_THREADS)
+                e.indices[P + i - e.pos_lo] = (int64_t)sm_val[i];
         } else if (MODE == MODE_HIST) {
             FT* freq = reinterpret_cast<FT*>(e.freq);
             if (P + nvalid <= next_boundary) {
-                const int64_t row = cur_rep * e.ldf;
-                for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS) freq_bump<FT>(freq, row + sm_val[i], bad);
+                const int64_t row = (cur_rep - e.rep_lo) * e.ldf;
+                for (int i = nlow + threadIdx.x; i < nvalid; i += SMP_THREADS) freq_bump<FT>(freq, row + sm_val[i], bad);
             } else {
-                for (int i = threadIdx.x; i < nvalid; i += SMP_THREADS)
-                    freq_bump<FT>(freq, ((P + i) / a.nsamp) * e.ldf + sm_val[i], bad);
+                for (int i = nlow + threadIdx.x; i < nvalid; i += SMP_THREADS)
+                    freq_bump<FT>(freq, ((P + i) / a.nsamp - e.rep_lo) * e.ldf + sm_val[i], bad);
             }
         } else if (MODE == MODE_GATHER) {
             if (P + nvalid <= next_boundary) {
                 // fast path: every draw of this iteration belongs to replicate cur_rep
                 constexpr int G = 8;
-                for (int i0 = threadIdx.x; i0 < nvalid; i0 += G * SMP_THREADS) {
+                for (int i0 = nlow + threadIdx.x; i0 < nvalid; i0 += G * SMP_THREADS) {
                     double2 v[G];
                     double pw[G];
 #pragma unroll
@@ -294,23 +304,23 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
 #pragma unroll
                     for (int g = 0; g < G; ++g) acc.push(v[g], pw[g]);
                 }
-                dirty = true;
+                dirty = dirty || nvalid > nlow;
             } else {
                 // replicate boundary inside this iteration: thread-local tagged accumulation
                 if (dirty) {
-                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep - e.rep_lo);
                     acc.zero();
                     dirty = false;
                 }
-                const int per = (nvalid + SMP_THREADS - 1) / SMP_THREADS;
-                const int i_lo = threadIdx.x * per;
+                const int per = (nvalid - nlow + SMP_THREADS - 1) / SMP_THREADS;
+                const int i_lo = nlow + threadIdx.x * per;
                 const int i_hi = min(nvalid, i_lo + per);
                 int64_t tag = -1;
                 for (int i = i_lo; i < i_hi; ++i) {
                     const int64_t rep = (P + i) / a.nsamp;
                     if (rep != tag) {
                         if (tag >= 0) {
-                            acc.flush_thread(e.S0, e.S1, tag);
+                            acc.flush_thread(e.S0, e.S1, tag - e.rep_lo);
                             acc.zero();
                         }
                         tag = rep;
@@ -319,18 +329,18 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
                     acc.push(__ldg(e.packed + s), HAS_W ? __ldg(e.w + s) : 1.0);
                 }
                 if (tag >= 0) {
-                    acc.flush_thread(e.S0, e.S1, tag);
+                    acc.flush_thread(e.S0, e.S1, tag - e.rep_lo);
                     acc.zero();
                 }
             }
         }
 
         P += total;
-        if (P >= a.count) break;
+        if (P >= a.count || (MODE != MODE_LOCATE && P >= e.pos_hi)) break;
         if (MODE == MODE_HIST || MODE == MODE_GATHER) {
             if (P >= next_boundary) {
                 if (MODE == MODE_GATHER && dirty) {
-                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+                    acc.flush_block(sm_red, e.S0, e.S1, cur_rep - e.rep_lo);
                     acc.zero();
                     dirty = false;
                 }
@@ -350,10 +360,10 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
         if (threadIdx.x == 0) {
             long long t = 0;
             for (int k = 0; k < SMP_THREADS / 32; ++k) t += sm_cnt[k];
-            e.block_count[blockIdx.x] = t;
+            e.block_count[bid] = t;
         }
     }
-    if (MODE == MODE_GATHER && dirty) acc.flush_block(sm_red, e.S0, e.S1, cur_rep);
+    if (MODE == MODE_GATHER && dirty) acc.flush_block(sm_red, e.S0, e.S1, cur_rep - e.rep_lo);
     if (MODE == MODE_HIST && bad && e.status) atomicOr(e.status, bad);
 }
 
@@ -460,15 +470,59 @@ Head carve_head(void* ws, int nblocks) {
     return Head{p + 8, p + 8 + nblocks, p};
 }
 
-// pass A + scan; leaves e.block_base / e.raw_used ready for pass B.  `prepared`: the head of
-// the workspace already holds the result of txb_sampler_prepare for the same (rng, ndat, count).
-int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status, cudaStream_t st,
-                   int prepared = 0) {
+// Workspace head (first txb_sampler_workspace_bytes() bytes), all int64:
+//   [0] raw_used scratch   [1..7] reserved   [8 .. 8+nblocks) block_count   [8+nblocks .. 8+2 nblocks) block_base
+void bind_head(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status) {
     Head h = carve_head(ws, p.nblocks);
     e.block_count = h.block_count;
     e.block_base = h.block_base;
     e.raw_used = raw_used ? raw_used : h.raw_used;
     e.status = status;
+    e.pos_lo = 0;
+    e.pos_hi = p.a.count;
+    e.rep_lo = 0;
+    e.block_offset = 0;
+}
+
+// pass A over blocks [block_lo, block_hi); the other entries of block_count are zeroed so that
+// ranks counting disjoint ranges can combine their heads with a plain integer SUM
+int run_count(const Plan& p, EmitArgs& e, int block_lo, int block_hi, cudaStream_t st) {
+    if (cudaMemsetAsync(e.block_count, 0, sizeof(int64_t) * p.nblocks, st) != cudaSuccess) {
+        set_error("sampler: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    if (block_hi <= block_lo) return TXB_OK;
+    e.block_offset = block_lo;
+    {
+        ProfScope prof("sampler_count", st);
+        k_sampler<MODE_COUNT, 1, false, false, int64_t><<<block_hi - block_lo, SMP_THREADS, 0, st>>>(p.a, e);
+    }
+    e.block_offset = 0;
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<count>");
+    return TXB_OK;
+}
+
+// scan of block_count -> block_base, then find the raw position of output #count-1
+int run_scan(const Plan& p, EmitArgs& e, cudaStream_t st) {
+    if (cudaMemsetAsync(e.raw_used, 0, sizeof(int64_t), st) != cudaSuccess ||
+        (e.status && cudaMemsetAsync(e.status, 0, sizeof(int), st) != cudaSuccess)) {
+        set_error("sampler: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    k_sampler_scan<<<1, 32, 0, st>>>(e.block_count, const_cast<int64_t*>(e.block_base), p.nblocks, p.a.count,
+                                     e.status);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
+    k_sampler<MODE_LOCATE, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<locate>");
+    return TXB_OK;
+}
+
+// everything an emit call needs before its pass B
+int begin_emit(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status, int prepared,
+               cudaStream_t st) {
+    bind_head(p, e, ws, raw_used, status);
     if (prepared) {
         if (status && cudaMemsetAsync(status, 0, sizeof(int), st) != cudaSuccess) {
             set_error("sampler: cudaMemsetAsync failed");
@@ -477,19 +531,17 @@ int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int*
         }
         return TXB_OK;
     }
-    if (cudaMemsetAsync(e.raw_used, 0, sizeof(int64_t), st) != cudaSuccess ||
-        (status && cudaMemsetAsync(status, 0, sizeof(int), st) != cudaSuccess)) {
-        set_error("sampler: cudaMemsetAsync failed");
-        cudaGetLastError();
-        return TXB_ERR_CUDA;
+    int rc = run_count(p, e, 0, p.nblocks, st);
+    if (rc != TXB_OK) return rc;
+    return run_scan(p, e, st);
+}
+
+int check_head(const char* what, void* workspace, size_t ws_bytes) {
+    TXB_CHECK_ARG(workspace != nullptr, "%s: null workspace", what);
+    if (ws_bytes < SMP_WS_HEAD) {
+        set_error("%s: workspace too small", what);
+        return TXB_ERR_WORKSPACE;
     }
-    {
-        ProfScope prof("sampler_count", st);
-        k_sampler<MODE_COUNT, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
-    }
-    TXB_CUDA_LAUNCH_CHECK("k_sampler<count>");
-    k_sampler_scan<<<1, 32, 0, st>>>(h.block_count, h.block_base, p.nblocks, p.a.count, status);
-    TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
     return TXB_OK;
 }
 
@@ -497,6 +549,47 @@ int count_and_scan(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int*
 
 extern "C" size_t txb_sampler_workspace_bytes(void) { return SMP_WS_HEAD; }
 
+extern "C" int txb_sampler_nblocks(const txb_pcg64* rng, int64_t ndat, int64_t count) {
+    Plan p;
+    return make_plan(rng, ndat, count, count, p) == TXB_OK ? p.nblocks : -1;
+}
+
+extern "C" int txb_sampler_count(const txb_pcg64* rng, int64_t ndat, int64_t count, int block_lo,
+                                 int block_hi, void* workspace, size_t ws_bytes, void* stream) {
+    int rc = check_head("txb_sampler_count", workspace, ws_bytes);
+    if (rc != TXB_OK) return rc;
+    Plan p;
+    rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    if (block_hi < 0 || block_hi > p.nblocks) block_hi = p.nblocks;
+    TXB_CHECK_ARG(block_lo >= 0 && block_lo <= block_hi, "txb_sampler_count: bad block range");
+    EmitArgs e{};
+    bind_head(p, e, workspace, nullptr, nullptr);
+    return run_count(p, e, block_lo, block_hi, (cudaStream_t)stream);
+}
+
+extern "C" int txb_sampler_scan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
+                                int* status, void* workspace, size_t ws_bytes, void* stream) {
+    int rc = check_head("txb_sampler_scan", workspace, ws_bytes);
+    if (rc != TXB_OK) return rc;
+    Plan p;
+    rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    EmitArgs e{};
+    bind_head(p, e, workspace, raw_used, status);
+    return run_scan(p, e, (cudaStream_t)stream);
+}
+
+extern "C" int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
+                                   int* status, void* workspace, size_t ws_bytes, void* stream) {
+    int rc = check_head("txb_sampler_prepare", workspace, ws_bytes);
+    if (rc != TXB_OK) return rc;
+    Plan p;
+    rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    EmitArgs e{};
+    return begin_emit(p, e, workspace, raw_used, status, 0, (cudaStream_t)stream);
+}
 extern "C" int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used) {
     TXB_CHECK_ARG(rng && raw_used >= 0, "txb_pcg64_advance: bad argument");
     int64_t r = raw_used;
@@ -522,74 +615,61 @@ extern "C" int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used) {
     return TXB_OK;
 }
 
-extern "C" int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
-                                   int* status, void* workspace, size_t ws_bytes, void* stream) {
-    TXB_CHECK_ARG(workspace, "txb_sampler_prepare: null pointer");
-    if (ws_bytes < SMP_WS_HEAD) {
-        set_error("txb_sampler_prepare: workspace too small");
-        return TXB_ERR_WORKSPACE;
-    }
+extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t pos_lo,
+                                   int64_t pos_hi, int64_t* indices, int64_t* raw_used, int* status,
+                                   int prepared, void* workspace, size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(indices != nullptr, "txb_sampler_indices: null pointer");
+    TXB_CHECK_ARG(0 <= pos_lo && pos_lo < pos_hi && pos_hi <= count,
+                  "txb_sampler_indices: bad window [%lld, %lld) of %lld", (long long)pos_lo, (long long)pos_hi,
+                  (long long)count);
+    int rc = check_head("txb_sampler_indices", workspace, ws_bytes);
+    if (rc != TXB_OK) return rc;
     Plan p;
-    int rc = make_plan(rng, ndat, count, count, p);
+    rc = make_plan(rng, ndat, count, count, p);
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st);
-    if (rc != TXB_OK) return rc;
-    k_sampler<MODE_LOCATE, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
-    TXB_CUDA_LAUNCH_CHECK("k_sampler<locate>");
-    return TXB_OK;
-}
-
-extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* indices,
-                                   int64_t* raw_used, int* status, int prepared, void* workspace,
-                                   size_t ws_bytes, void* stream) {
-    TXB_CHECK_ARG(indices && workspace, "txb_sampler_indices: null pointer");
-    if (ws_bytes < SMP_WS_HEAD) {
-        set_error("txb_sampler_indices: workspace too small");
-        return TXB_ERR_WORKSPACE;
-    }
-    Plan p;
-    int rc = make_plan(rng, ndat, count, count, p);
-    if (rc != TXB_OK) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
-    EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
+    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
     if (rc != TXB_OK) return rc;
     e.indices = indices;
+    e.pos_lo = pos_lo;
+    e.pos_hi = pos_hi;
     k_sampler<MODE_FILL, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
     TXB_CUDA_LAUNCH_CHECK("k_sampler<fill>");
     return TXB_OK;
 }
 
 extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
-                                void* freq, int freq_dtype, int64_t ldf, int64_t* raw_used, int* status,
-                                int prepared, void* workspace, size_t ws_bytes, void* stream) {
-    TXB_CHECK_ARG(freq && workspace, "txb_sampler_freq: null pointer");
-    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat, "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld",
-                  (long long)nrep, (long long)ldf, (long long)ndat);
+                                int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
+                                int64_t* raw_used, int* status, int prepared, void* workspace,
+                                size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(freq != nullptr, "txb_sampler_freq: null pointer");
+    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
+                  "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld window [%lld, %lld)", (long long)nrep,
+                  (long long)ldf, (long long)ndat, (long long)rep_lo, (long long)rep_hi);
     TXB_CHECK_ARG(freq_dtype >= 0 && freq_dtype <= 3, "txb_sampler_freq: bad freq_dtype %d", freq_dtype);
     static const size_t esz[4] = {8, 4, 2, 1};
     TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
                   "txb_sampler_freq: narrow table rows must be 4-byte aligned");
-    if (ws_bytes < SMP_WS_HEAD) {
-        set_error("txb_sampler_freq: workspace too small");
-        return TXB_ERR_WORKSPACE;
-    }
+    int rc = check_head("txb_sampler_freq", workspace, ws_bytes);
+    if (rc != TXB_OK) return rc;
     Plan p;
-    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemsetAsync(freq, 0, (size_t)nrep * ldf * esz[freq_dtype], st) != cudaSuccess) {
+    if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
         set_error("txb_sampler_freq: cudaMemsetAsync failed");
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
+    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
     if (rc != TXB_OK) return rc;
     e.freq = freq;
     e.ldf = ldf;
+    e.rep_lo = rep_lo;
+    e.pos_lo = rep_lo * nsamp;
+    e.pos_hi = rep_hi * nsamp;
     switch (freq_dtype) {
         case TXB_I64: k_sampler<MODE_HIST, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
         case TXB_I32: k_sampler<MODE_HIST, 1, false, false, int32_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
@@ -607,14 +687,17 @@ extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, 
 
 extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                                         const double* w, int64_t ndat, int64_t ldx, int order, int mode,
-                                        int64_t nrep, int64_t nsamp, double* out, int64_t* raw_used,
-                                        int* status, int prepared, void* workspace, size_t ws_bytes,
-                                        void* stream) {
+                                        int64_t nrep, int64_t nsamp, int64_t rep_lo, int64_t rep_hi,
+                                        double* out, int64_t* raw_used, int* status, int prepared,
+                                        void* workspace, size_t ws_bytes, void* stream) {
     TXB_CHECK_ARG(u && out && workspace, "txb_sampler_resample_f64: null pointer");
-    TXB_CHECK_ARG(order >= 1 && nrep >= 1, "txb_sampler_resample_f64: order=%d nrep=%lld", order, (long long)nrep);
+    TXB_CHECK_ARG(order >= 1 && nrep >= 1 && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
+                  "txb_sampler_resample_f64: order=%d nrep=%lld window [%lld, %lld)", order, (long long)nrep,
+                  (long long)rep_lo, (long long)rep_hi);
     TXB_CHECK_ARG(mode == TXB_MODE_COMOMENTS ? x != nullptr : (mode == TXB_MODE_X_IS_U && x == nullptr),
                   "txb_sampler_resample_f64: mode COMOMENTS needs x, mode X_IS_U needs x == NULL");
-    if (ws_bytes < txb_sampler_resample_workspace_bytes(ndat, order, nrep)) {
+    const int64_t nwin = rep_hi - rep_lo;
+    if (ws_bytes < txb_sampler_resample_workspace_bytes(ndat, order, nwin)) {
         set_error("txb_sampler_resample_f64: workspace too small");
         return TXB_ERR_WORKSPACE;
     }
@@ -628,23 +711,26 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
     double2* packed = reinterpret_cast<double2*>(base);
     double* pivot = reinterpret_cast<double*>(packed + ndat);
     double* S0 = pivot + 4;
-    double* S1 = S0 + nrep * (order + 2);
+    double* S1 = S0 + nwin * (order + 2);
     rc = txb_pivot_f64(x, u, ndat, 1, x ? ldx : 1, 0, pivot, stream);
     if (rc != TXB_OK) return rc;
     rc = launch_pack_shifted(x, x ? ldx : 0, u, ndat, pivot, packed, st);
     if (rc != TXB_OK) return rc;
-    if (cudaMemsetAsync(S0, 0, sizeof(double) * 2 * nrep * (order + 2), st) != cudaSuccess) {
+    if (cudaMemsetAsync(S0, 0, sizeof(double) * 2 * nwin * (order + 2), st) != cudaSuccess) {
         set_error("txb_sampler_resample_f64: cudaMemsetAsync failed");
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
     EmitArgs e{};
-    rc = count_and_scan(p, e, workspace, raw_used, status, st, prepared);
+    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
     if (rc != TXB_OK) return rc;
     e.packed = packed;
     e.w = w;
     e.S0 = S0;
     e.S1 = S1;
+    e.rep_lo = rep_lo;
+    e.pos_lo = rep_lo * nsamp;
+    e.pos_hi = rep_hi * nsamp;
     {
     ProfScope prof("sampler_gather", st);
     TXB_DISPATCH_ORDER(ks, {
@@ -658,5 +744,5 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
     });
     }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<gather>");
-    return txb_finalize_f64(S0, S1, pivot, nrep, 1, 1, order, mode, out, stream);
+    return txb_finalize_f64(S0, S1, pivot, nwin, 1, 1, order, mode, out, stream);
 }

@@ -123,6 +123,51 @@ def reduce_vals(x, u, order: int, w=None, x_is_u: bool = False) -> torch.Tensor:
     return out.reshape(*val_shape, 2, order + 1)
 
 
+def reduce_sums(x, u, order: int, w=None, pivot=None):
+    """K1 without the final re-centring: additive pivot sums ``(pivot, S0[nu, order+1], S1[nchan, order+1])``.
+
+    Sums about a COMMON ``pivot`` (``[cx[nchan], cu[nu]]``) add across sample shards -- streamed
+    chunks or GPUs (``all_reduce(SUM)``) -- and :func:`finalize_sums` turns the total into comoments.
+    ``pivot=None`` estimates one from this shard (txb_pivot_f64).  Also returns ``val_shape``.
+    """
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    nu = nchan if ldu else 1
+    ncx = nchan if x is not None else 0
+    with torch.cuda.device(dev):
+        if pivot is None:
+            pivot = torch.empty(ncx + nu, dtype=torch.float64, device=dev)
+            check(lib.txb_pivot_f64(_ptr(x), _ptr(u), nsamp, nchan, nchan, ldu, pivot.data_ptr(), _stream_ptr()),
+                  "txb_pivot_f64")
+        S0 = torch.empty((nu, order + 1), dtype=torch.float64, device=dev)
+        S1 = torch.empty((nchan, order + 1), dtype=torch.float64, device=dev) if x is not None else None
+        ws = _workspace(lib.txb_reduce_workspace_bytes(nsamp, nchan, order), dev)
+        st = lib.txb_reduce_sums_f64(_ptr(x), _ptr(u), _ptr(w), nsamp, nchan, nchan, ldu, order, pivot.data_ptr(),
+                                     S0.data_ptr(), _ptr(S1), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_reduce_sums_f64")
+    launch_count += 1
+    return pivot, S0, S1, val_shape
+
+
+def finalize_sums(pivot, S0, S1, order: int, x_is_u: bool = False, val_shape=()) -> torch.Tensor:
+    """Pivot sums -> comoments ``[*val, 2, order+1]`` (``S0`` carries order+1 powers when ``x_is_u``)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    nu = S0.shape[-2]
+    nchan = S1.shape[-2] if S1 is not None else nu
+    out = torch.empty((nchan, 2, order + 1), dtype=torch.float64, device=dev)
+    mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    with torch.cuda.device(dev):
+        st = lib.txb_finalize_f64(S0.data_ptr(), _ptr(S1), pivot.data_ptr(), 1, nchan, nu, order, mode,
+                                  out.data_ptr(), _stream_ptr())
+    check(st, "txb_finalize_f64")
+    launch_count += 1
+    return out.reshape(*val_shape, 2, order + 1)
+
+
 def indices_to_freq(indices, ndat: int | None = None, dtype: torch.dtype = torch.int64) -> torch.Tensor:
     """K6.  ``freq[r, i] = #{j: indices[r, j] == i}`` on the device (bit-exact integers)."""
     global launch_count
@@ -277,20 +322,40 @@ class SamplerPlan:
     table itself (80 GB at BASELINE config 2) is regenerated inside whichever kernel needs it.
     """
 
-    def __init__(self, rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None) -> None:
+    def __init__(self, rng: np.random.Generator, nrep: int, nsamp: int, ndat: int | None = None, group=None) -> None:
+        """``group``: a ``torch.distributed`` process group whose ranks all build the SAME plan (same
+        ``rng`` state); the counting pass is then split across them and combined with one small
+        all-reduce of the per-block counts."""
         global launch_count
         lib = _lib.load()
         dev = device()
         self.nrep, self.nsamp = int(nrep), int(nsamp)
         self.ndat = self.nsamp if ndat is None else int(ndat)
         self.state = pcg64_state(rng)
-        self.head = torch.empty(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device=dev)
+        self.head = torch.zeros(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device=dev)
         aux = torch.zeros(2, dtype=torch.int64, device=dev)
         status = aux[1:].view(torch.int32)
+        count = self.nrep * self.nsamp
+        args = (C.byref(self.state), self.ndat, count)
         with torch.cuda.device(dev):
-            st = lib.txb_sampler_prepare(C.byref(self.state), self.ndat, self.nrep * self.nsamp, aux.data_ptr(),
-                                         status.data_ptr(), self.head.data_ptr(), self.head.numel(), _stream_ptr())
-        check(st, "txb_sampler_prepare")
+            if group is None:
+                st = lib.txb_sampler_prepare(*args, aux.data_ptr(), status.data_ptr(), self.head.data_ptr(),
+                                             self.head.numel(), _stream_ptr())
+                check(st, "txb_sampler_prepare")
+            else:
+                import torch.distributed as dist
+
+                world, rank = dist.get_world_size(group), dist.get_rank(group)
+                nb = lib.txb_sampler_nblocks(*args)
+                if nb < 0:
+                    check(1, "txb_sampler_nblocks")
+                lo, hi = nb * rank // world, nb * (rank + 1) // world
+                check(lib.txb_sampler_count(*args, lo, hi, self.head.data_ptr(), self.head.numel(), _stream_ptr()),
+                      "txb_sampler_count")
+                counts = self.head.view(torch.int64)[8 : 8 + nb]
+                dist.all_reduce(counts, group=group)  # ranks counted disjoint block ranges
+                check(lib.txb_sampler_scan(*args, aux.data_ptr(), status.data_ptr(), self.head.data_ptr(),
+                                           self.head.numel(), _stream_ptr()), "txb_sampler_scan")
         launch_count += 3
         _sampler_flags(status[:1], "txb_sampler_prepare")
         self.raw_used = int(aux[0].item())
@@ -309,7 +374,16 @@ def _plan_of(src, nrep, nsamp, ndat) -> SamplerPlan:
     return SamplerPlan(src, nrep, nsamp, ndat)
 
 
-def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None) -> torch.Tensor:
+def _window(plan: SamplerPlan, reps) -> tuple[int, int]:
+    lo, hi = (0, plan.nrep) if reps is None else (int(reps[0]), int(reps[1]))
+    if not 0 <= lo < hi <= plan.nrep:
+        msg = f"replicate window [{lo}, {hi}) outside [0, {plan.nrep})"
+        raise ValueError(msg)
+    return lo, hi
+
+
+def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
+                    reps=None) -> torch.Tensor:
     """``rng.choice(ndat, (nrep, nsamp), replace=True)`` generated on the device, bit-exact (int64).
 
     ``src`` is a numpy ``Generator(PCG64)`` (advanced as numpy would) or a :class:`SamplerPlan`.
@@ -320,19 +394,21 @@ def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat
     if not isinstance(src, SamplerPlan) and (nsamp if ndat is None else ndat) == 1:
         return torch.zeros((nrep, nsamp), dtype=torch.int64, device=dev)  # numpy draws nothing here
     plan = _plan_of(src, nrep, nsamp, ndat)
-    out = torch.empty((plan.nrep, plan.nsamp), dtype=torch.int64, device=dev)
+    lo, hi = _window(plan, reps)
+    out = torch.empty((hi - lo, plan.nsamp), dtype=torch.int64, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         ws = plan.workspace(0, dev)
-        st = lib.txb_sampler_indices(C.byref(plan.state), plan.ndat, plan.nrep * plan.nsamp, out.data_ptr(), None,
-                                     status.data_ptr(), 1, ws.data_ptr(), ws.numel(), _stream_ptr())
+        st = lib.txb_sampler_indices(C.byref(plan.state), plan.ndat, plan.nrep * plan.nsamp, lo * plan.nsamp,
+                                     hi * plan.nsamp, out.data_ptr(), None, status.data_ptr(), 1, ws.data_ptr(),
+                                     ws.numel(), _stream_ptr())
     check(st, "txb_sampler_indices")
     launch_count += 1
     return out
 
 
 def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
-                 dtype: torch.dtype = torch.uint8) -> torch.Tensor:
+                 dtype: torch.dtype = torch.uint8, reps=None) -> torch.Tensor:
     """Frequency table of the same stream, histogrammed on the device without the index table."""
     global launch_count
     lib = _lib.load()
@@ -340,11 +416,12 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     plan = _plan_of(src, nrep, nsamp, ndat)
     esz = torch.empty((), dtype=dtype).element_size()
     ldf = -(-plan.ndat * esz // 4) * 4 // esz
-    buf = torch.empty((plan.nrep, ldf), dtype=dtype, device=dev)
+    lo, hi = _window(plan, reps)
+    buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         ws = plan.workspace(0, dev)
-        st = lib.txb_sampler_freq(C.byref(plan.state), plan.ndat, plan.nrep, plan.nsamp, buf.data_ptr(),
+        st = lib.txb_sampler_freq(C.byref(plan.state), plan.ndat, plan.nrep, plan.nsamp, lo, hi, buf.data_ptr(),
                                   _FREQ_DTYPES[dtype], ldf, None, status.data_ptr(), 1, ws.data_ptr(), ws.numel(),
                                   _stream_ptr())
     check(st, "txb_sampler_freq")
@@ -354,7 +431,7 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
 
 
 def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
-                     nsamp: int | None = None, sync_rng: bool = True) -> torch.Tensor:
+                     nsamp: int | None = None, sync_rng: bool = True, reps=None) -> torch.Tensor:
     """K2 fused with the generator (scalar x): bootstrap comoments for ``{"nrep": nrep, "rng": rng}``.
 
     Neither the index nor the frequency table is materialised.  With a raw ``Generator`` and
@@ -379,18 +456,22 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
         state, nrep, nsamp, prepared = plan.state, plan.nrep, plan.nsamp, 1
     else:
         plan, state, prepared = None, pcg64_state(src), 0
-    out = torch.empty((nrep, 1, 2, order + 1), dtype=torch.float64, device=dev)
+    lo, hi = (0, nrep) if reps is None else (int(reps[0]), int(reps[1]))
+    if not 0 <= lo < hi <= nrep:
+        msg = f"replicate window [{lo}, {hi}) outside [0, {nrep})"
+        raise ValueError(msg)
+    out = torch.empty((hi - lo, 1, 2, order + 1), dtype=torch.float64, device=dev)
     mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
     with torch.cuda.device(dev):
-        nb = lib.txb_sampler_resample_workspace_bytes(ndat, order, nrep)
+        nb = lib.txb_sampler_resample_workspace_bytes(ndat, order, hi - lo)
         ws = plan.workspace(nb, dev) if plan is not None else _workspace(nb, dev)
         st = lib.txb_sampler_resample_f64(
-            C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, out.data_ptr(),
+            C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, lo, hi, out.data_ptr(),
             None, None, prepared, ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_sampler_resample_f64")
-    launch_count += 5 if prepared else 7
-    return out.reshape(nrep, *val_shape, 2, order + 1)
+    launch_count += 5 if prepared else 8
+    return out.reshape(hi - lo, *val_shape, 2, order + 1)
 
 
 def _tails(data, dev):

@@ -225,6 +225,9 @@ class ExprProgram:
                     raise NotImplementedError(msg)
                 nf = 0
                 for f in factors:
+                    if f.is_number:  # e.g. Float factors, which as_coeff_mul leaves in place
+                        coef = coef * f
+                        continue
                     base, exp = f.as_base_exp()
                     if isinstance(base, sp.log):
                         if exp != 1:
