@@ -210,7 +210,6 @@ def run_b200(a) -> None:
     barrier()
 
     clocks = ClockSampler(local) if rank == 0 else None
-    lib.txb_profile_begin(b"sampler_gather")
     launches0 = K.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -221,8 +220,17 @@ def run_b200(a) -> None:
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
     launches = K.launch_count - launches0
-    k_ms, k_n = C.c_double(), C.c_int()
-    _lib.check(lib.txb_profile_end(C.byref(k_ms), C.byref(k_n)), "txb_profile_end")
+    # per-kernel device time of the bootstrap's kernels: same loop again, one family bracketed at a time
+    # (events on the launching stream; the profile hook adds two event records per launch)
+    kernels = {}
+    for tag in ("sampler_count", "bucket_scatter", "bucket_consume", "sampler_gather"):
+        lib.txb_profile_begin(tag.encode())
+        for _ in range(a.steps):
+            step_device()
+        ms, nl = C.c_double(), C.c_int()
+        _lib.check(lib.txb_profile_end(C.byref(ms), C.byref(nl)), "txb_profile_end")
+        if nl.value:
+            kernels[tag] = {"ms_per_step": ms.value / a.steps, "launches_per_step": nl.value / a.steps}
 
     # K1 alone (samples/s) and its kernel time, outside the headline region
     lib.txb_profile_begin(b"reduce")
@@ -266,7 +274,7 @@ def run_b200(a) -> None:
     t_dev, t_e2e, t_red = (float(v) for v in times.tolist())
 
     if rank == 0:
-        emit(a, world, t_dev, t_e2e, t_red, k_ms.value, k_n.value, red_ms.value, red_n.value, launches,
+        emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms.value, red_n.value, launches,
              h2d // a.steps, d2h // a.steps, clock_info)
     if world > 1:
         dist.destroy_process_group()
@@ -302,16 +310,29 @@ def fp64_peak_tflops() -> float:
     return best
 
 
-def emit(a, world, t_dev, t_e2e, t_red, k_ms, k_n, red_ms, red_n, launches, h2d, d2h, clock_info) -> None:
+#: algorithmic HBM bytes per bootstrap draw of each kernel family
+ALG_BYTES_PER_DRAW = {"sampler_gather": 16.0, "bucket_scatter": 2.0, "bucket_consume": 2.0, "sampler_count": 0.0}
+KERNEL_NAMES = {
+    "sampler_gather": "k_sampler<MODE_GATHER> (fused PCG64 sampler + HBM gather + power sums)",
+    "bucket_scatter": "k_bucket_scatter (PCG64 sampler + shared-memory write-combining partition by sample bucket)",
+    "bucket_consume": "k_bucket_consume (per-bucket shared-memory gather + fp64 power sums)",
+    "sampler_count": "k_sampler_count (PCG64 sampler, accepted draws per iteration)",
+}
+
+
+def emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms, red_n, launches, h2d, d2h, clock_info) -> None:
     import torch
 
     peak, peak_src = measured_peaks()
     draws = a.nrep * a.nsamp
-    k_s = k_ms * 1e-3 / max(k_n, 1)  # average duration of one k_sampler<GATHER> launch
-    alg_bytes = 16.0 * draws  # one (x - cx, u - cu) pair per bootstrap draw
-    achieved = alg_bytes / k_s / 1e9
+    step_ms = t_dev / a.steps * 1e3
+    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])  # dominant kernel of the step
+    k_s = kernels[top]["ms_per_step"] * 1e-3 / kernels[top]["launches_per_step"]
+    draws_per_launch = draws / kernels[top]["launches_per_step"]
+    achieved = ALG_BYTES_PER_DRAW[top] * draws_per_launch / k_s / 1e9
     flops = 4.0 * (a.order + 1) * draws  # 2 (k+1) FMA per draw, scalar x
     fp64_peak = fp64_peak_tflops()
+    fp64_ms = kernels.get("bucket_consume", kernels.get("sampler_gather"))["ms_per_step"]
     red_s = red_ms * 1e-3 / max(red_n, 1)
     cpu = None
     if world == 1:
@@ -338,12 +359,18 @@ def emit(a, world, t_dev, t_e2e, t_red, k_ms, k_n, red_ms, red_n, launches, h2d,
                 "path": "DataCentralMomentsVals.from_vals -> beta.factory_extrapmodel -> .resample({'nrep','rng'}) -> .predict"},
         "gpu_launches": int(launches),
         "roofline": {
-            "kernel": "k_sampler<MODE_GATHER> (fused PCG64 sampler + gather + power sums)",
+            "kernel": KERNEL_NAMES[top],
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "peak_source": peak_src, "traffic": None, "launch_ms": k_s * 1e3, "launches_timed": k_n,
-            "share_of_step": k_ms * 1e-3 / t_dev,
-            "fp64": {"achieved_tflops": flops / k_s / 1e12, "peak_tflops": fp64_peak,
-                     "frac": flops / k_s / 1e12 / fp64_peak, "peak_source": "txb_fp64_peak_launch DFMA micro-benchmark, this run"},
+            "peak_source": peak_src, "traffic": None, "launch_ms": k_s * 1e3,
+            "launches_per_step": kernels[top]["launches_per_step"],
+            "share_of_step": kernels[top]["ms_per_step"] / step_ms,
+            "note": "the partition kernel is instruction-issue bound (integer PCG64 + shared-memory atomics), "
+                    "not HBM bound; its HBM roofline is reported because the contract asks for the dominant kernel",
+            "kernels": {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kernels.items()},
+            "fp64": {"kernel": "bucket_consume" if "bucket_consume" in kernels else "sampler_gather",
+                     "achieved_tflops": flops / (fp64_ms * 1e-3) / 1e12, "peak_tflops": fp64_peak,
+                     "frac": flops / (fp64_ms * 1e-3) / 1e12 / fp64_peak,
+                     "peak_source": "txb_fp64_peak_launch DFMA micro-benchmark, this run"},
         },
         "reduce": {"samples_per_s": a.nsamp * world / t_red, "kernel_ms": red_s * 1e3,
                    "GBps": 16.0 * a.nsamp / red_s / 1e9, "frac_hbm": 16.0 * a.nsamp / red_s / 1e9 / peak},

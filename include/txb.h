@@ -142,7 +142,7 @@ int txb_resample_indices_f64(const double* x, const double* u, const double* w, 
  * *status (device int, may be NULL): 2 = narrow table overflow, 4 = internal raw-range
  * estimate too short (never observed; > 12 sigma).
  * txb_sampler_prepare runs the counting pass once (and reports raw_used) into the first
- * txb_sampler_workspace_bytes() bytes of `workspace`; a later emit call given the SAME
+ * txb_sampler_workspace_bytes(ndat, count) bytes of `workspace`; a later emit call given the SAME
  * (rng, ndat, count) and that workspace with prepared != 0 skips the pass.
  *   txb_sampler_indices : indices[count] int64              (IndexSampler.indices)
  *   txb_sampler_freq    : freq[nrep, ldf] of freq_dtype     (IndexSampler.freq)
@@ -152,14 +152,19 @@ typedef struct txb_pcg64 {
     uint64_t state_hi, state_lo, inc_hi, inc_lo;
     uint32_t has_uint32, uinteger;
 } txb_pcg64;
-size_t txb_sampler_workspace_bytes(void);
+/* head of every sampler workspace: block counts / offsets and the per-iteration position table */
+size_t txb_sampler_workspace_bytes(int64_t ndat, int64_t count);
+/* out[0] = entries of block_count (int64 at byte 64), out[1] = entries of iter_count (int32),
+ * out[2] = byte offset of iter_count, out[3] = txb_sampler_workspace_bytes(ndat, count)      */
+int txb_sampler_layout(int64_t ndat, int64_t count, int64_t* out);
 int txb_pcg64_advance(txb_pcg64* rng, int64_t raw_used);
 int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
                         int* status, void* workspace, size_t ws_bytes, void* stream);
 /* Multi-GPU form of txb_sampler_prepare: the counting pass is split by thread block.  Rank g runs
  * txb_sampler_count on blocks [block_lo, block_hi) of txb_sampler_nblocks(...) (entries outside
- * the range are zeroed), the ranks SUM the int64 array block_count = ((int64_t*)workspace) + 8
- * (nblocks entries; one small all-reduce), and txb_sampler_scan finishes the preparation.
+ * the range are zeroed), the ranks SUM the two count arrays of the head (block_count, int64, and
+ * iter_count, int32: see txb_sampler_layout; one small all-reduce each), and txb_sampler_scan
+ * finishes the preparation.
  * block_hi < 0 means "to the end".                                                        */
 int txb_sampler_nblocks(const txb_pcg64* rng, int64_t ndat, int64_t count);
 int txb_sampler_count(const txb_pcg64* rng, int64_t ndat, int64_t count, int block_lo, int block_hi,
@@ -176,11 +181,24 @@ int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t n
                      int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
                      int64_t* raw_used, int* status, int prepared, void* workspace, size_t ws_bytes,
                      void* stream);
-size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep);
+/* txb_sampler_resample_f64 `flags`: TXB_SAMPLER_PREPARED = the workspace head holds the result of
+ * txb_sampler_prepare (or count + scan) for the same (rng, ndat, nrep * nsamp);
+ * TXB_SAMPLER_NO_BUCKETS = always use the gather kernel.  With the minimum workspace
+ * (txb_sampler_resample_workspace_bytes) the bootstrap gathers (x, u) pairs from HBM; given
+ * txb_sampler_resample_fast_workspace_bytes (or as much of it as the caller can spare -- replicates
+ * are processed in as many windows as needed) draws are first partitioned by sample bucket and
+ * consumed from shared memory (sampler_bucket.cuh), which is ~2.5x faster on tables beyond L2.
+ * *status |= 8 if a bucket list overflowed its > 10 sigma capacity, |= 16 if a shared-memory ring
+ * wrapped (> 6 sigma); neither has been observed: rerun with NO_BUCKETS.                    */
+enum { TXB_SAMPLER_PREPARED = 1, TXB_SAMPLER_NO_BUCKETS = 2 };
+size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t nsamp,
+                                            int64_t nrep_out);
+size_t txb_sampler_resample_fast_workspace_bytes(int64_t ndat, int order, int mode, int64_t nrep,
+                                                 int64_t nsamp, int64_t nrep_out);
 int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                              const double* w, int64_t ndat, int64_t ldx, int order, int mode,
                              int64_t nrep, int64_t nsamp, int64_t rep_lo, int64_t rep_hi, double* out,
-                             int64_t* raw_used, int* status, int prepared, void* workspace,
+                             int64_t* raw_used, int* status, int flags, void* workspace,
                              size_t ws_bytes, void* stream);
 
 /* ---- K3 / K4: merge pre-reduced blocks (Chan/Pebay) -----------------------

@@ -133,7 +133,8 @@ def sampler_freq(src, nrep=None, nsamp=None, ndat=None, dtype=torch.uint8, reps=
     return indices_to_freq(plan._idx[_win(plan, reps)], plan.ndat, dtype=dtype)
 
 
-def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, sync_rng=True, reps=None):
+def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, sync_rng=True, reps=None,
+                     buckets=True):
     n = _np(u).shape[0]
     plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, n if nsamp is None else nsamp, n)
     return resample_indices(x, u, plan._idx[_win(plan, reps)], order, w=w, x_is_u=x_is_u)

@@ -171,21 +171,26 @@ def test_split_count_equals_prepare(K, world):
     state = K.pcg64_state(np.random.default_rng(4))
     nb = lib.txb_sampler_nblocks(C.byref(state), n, nrep * n)
     assert nb > 0
+    lay = (C.c_int64 * 4)()
+    assert lib.txb_sampler_layout(n, nrep * n, lay) == 0
+    assert lay[0] == nb and lay[3] == lib.txb_sampler_workspace_bytes(n, nrep * n) == plan.head.numel()
     heads = []
     for r in range(world):
-        h = torch.zeros(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device="cuda")
+        h = torch.zeros(lay[3], dtype=torch.uint8, device="cuda")
         lo, hi = nb * r // world, nb * (r + 1) // world
         assert lib.txb_sampler_count(C.byref(state), n, nrep * n, lo, hi, h.data_ptr(), h.numel(), None) == 0
-        heads.append(h.view(torch.int64))
+        heads.append(h)
     total = heads[0].clone()
     for h in heads[1:]:
-        total[8 : 8 + nb] += h[8 : 8 + nb]
+        total.view(torch.int64)[8 : 8 + nb] += h.view(torch.int64)[8 : 8 + nb]
+        total[lay[2] : lay[2] + 4 * lay[1]].view(torch.int32).add_(h[lay[2] : lay[2] + 4 * lay[1]].view(torch.int32))
     aux = torch.zeros(2, dtype=torch.int64, device="cuda")
     assert lib.txb_sampler_scan(C.byref(state), n, nrep * n, aux.data_ptr(), aux[1:].data_ptr(), total.data_ptr(),
-                                total.numel() * 8, None) == 0
-    ref = plan.head.view(torch.int64)
-    assert torch.equal(total[8 : 8 + 2 * nb], ref[8 : 8 + 2 * nb])
+                                total.numel(), None) == 0
+    assert torch.equal(total[64:], plan.head[64:])
     assert int(aux[0]) == plan.raw_used
+    it = plan.head[lay[2] : lay[2] + 4 * lay[1]].view(torch.int32)
+    assert int(it.sum()) >= nrep * n  # the counted raw range covers the requested draws
 
 
 def test_sums_are_additive_across_shards(K):
@@ -203,3 +208,44 @@ def test_sums_are_additive_across_shards(K):
     ref = oc.comoments_two_pass(x, u, order)
     assert float((np.abs(out - ref) / np.maximum(np.abs(ref), oc.tolerance_scale(x, u, order))).max()) < TOL
     assert torch.allclose(torch.from_numpy(out), K.reduce_vals(x, u, order).cpu(), rtol=1e-11, atol=1e-13)
+
+
+# ------------------------------------------------------------------ bucketed (shared-memory) bootstrap
+@pytest.mark.parametrize("n,nrep,order", [(4_200_000, 3, 8), (5_000_003, 2, 6), (6_300_000, 2, 2)])
+def test_bucketed_equals_gather_and_oracle(K, n, nrep, order):
+    import torch
+
+    rng = np.random.default_rng(5)
+    u = rng.normal(175.0, 5.3, n)
+    x = 1e-3 * u + rng.normal(0.0, 0.02, n)
+    w = rng.random(n)
+    idx = np.random.default_rng(31).choice(n, (nrep, n))
+    scale = oc.tolerance_scale(x, u, order)
+    for wt in (None, w):
+        a = K.sampler_resample(np.random.default_rng(31), x, u, nrep, order, w=wt, buckets=True)
+        b = K.sampler_resample(np.random.default_rng(31), x, u, nrep, order, w=wt, buckets=False)
+        assert torch.allclose(a, b, rtol=1e-10, atol=1e-300)
+        if wt is None:
+            ref = oc.resample_vals_gather(x, u, order, idx[:1], w=wt)
+            assert float((np.abs(a[:1].cpu().numpy() - ref) / np.maximum(np.abs(ref), scale)).max()) < TOL
+    a = K.sampler_resample(np.random.default_rng(31), None, u, nrep, order, x_is_u=True, buckets=True)
+    b = K.sampler_resample(np.random.default_rng(31), None, u, nrep, order, x_is_u=True, buckets=False)
+    assert torch.allclose(a, b, rtol=1e-10, atol=1e-300)
+
+
+def test_bucketed_windows_when_scratch_is_small(K):
+    import torch
+
+    n, nrep, order = 4_200_000, 70, 4
+    rng = np.random.default_rng(6)
+    u = rng.normal(0.0, 1.0, n)
+    x = u + rng.normal(0.0, 1.0, n)
+    full = K.sampler_resample(np.random.default_rng(2), x, u, nrep, order, buckets=False)
+    # scratch for ~33 of the 70 replicates: the library must loop over replicate windows
+    per_rep = 513 * (4 + 2 * 8 * (order + 1) + 300 * 64)
+    part = K.sampler_resample(np.random.default_rng(2), x, u, nrep, order, scratch_bytes=33 * per_rep)
+    assert torch.allclose(part, full, rtol=1e-10, atol=1e-300)
+    # and replicate windows requested by the caller
+    plan = K.SamplerPlan(np.random.default_rng(2), nrep, n)
+    mid = K.sampler_resample(plan, x, u, order=order, reps=(17, 60))
+    assert torch.allclose(mid, full[17:60], rtol=1e-10, atol=1e-300)

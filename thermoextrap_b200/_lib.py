@@ -15,6 +15,7 @@ _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libtxb.so"
 TXB_OK = 0
 TXB_I64, TXB_I32, TXB_U16, TXB_U8 = 0, 1, 2, 3
 MODE_COMOMENTS, MODE_X_IS_U = 0, 1
+SAMPLER_PREPARED, SAMPLER_NO_BUCKETS = 1, 2
 
 _p = C.c_void_p
 _i64 = C.c_int64
@@ -50,7 +51,8 @@ SIGNATURES = {
         _int,
         [_p, _p, _p, _i64, _i64, _int, _int, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p],
     ),
-    "txb_sampler_workspace_bytes": (_sz, []),
+    "txb_sampler_workspace_bytes": (_sz, [_i64, _i64]),
+    "txb_sampler_layout": (_int, [_i64, _i64, _p]),
     "txb_pcg64_advance": (_int, [_p, _i64]),
     "txb_sampler_prepare": (_int, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
     "txb_sampler_nblocks": (_int, [_p, _i64, _i64]),
@@ -58,7 +60,8 @@ SIGNATURES = {
     "txb_sampler_scan": (_int, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
     "txb_sampler_indices": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p]),
     "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _int, _p, _sz, _p]),
-    "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64]),
+    "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64, _i64, _i64]),
+    "txb_sampler_resample_fast_workspace_bytes": (_sz, [_i64, _int, _int, _i64, _i64, _i64]),
     "txb_sampler_resample_f64": (
         _int,
         [_p, _p, _p, _p, _i64, _i64, _int, _int, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p],

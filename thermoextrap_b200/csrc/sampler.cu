@@ -27,6 +27,7 @@ namespace txb {
 
 int launch_pack_shifted(const double* x, int64_t ldx, const double* u, int64_t nsamp,
                         const double* pivot, double2* packed, cudaStream_t st);
+int launch_sum_parts(const double* ws, int64_t nparts, int64_t n, double* out, cudaStream_t st);
 
 constexpr uint64_t PCG_MULT_HI = 0x2360ED051FC65DA4ull;
 constexpr uint64_t PCG_MULT_LO = 0x4385DF649FCCF645ull;
@@ -44,8 +45,10 @@ struct SamplerArgs {
     uint32_t n, thresh;           // ndat, 2^32 mod ndat
     int64_t count;                // accepted draws wanted (nrep * nsamp)
     int64_t nsamp;                // draws per replicate
-    int64_t steps_per_block;      // multiple of SMP_THREADS * SMP_T
+    int64_t steps_per_block;      // multiple of 512 * SMP_T (both thread geometries tile it)
     Affine iter_jump;             // (SMP_THREADS - 1) * SMP_T steps
+    Affine iter_jump2;            // (BK_THREADS - 1) * SMP_T steps (512-thread kernels)
+    Affine step_k[SMP_T];         // k + 1 steps: the SMP_T states of an iteration, independently from the first
     Affine pow2[SMP_NPOW];        // 2^i steps
 };
 
@@ -69,6 +72,28 @@ __device__ __forceinline__ uint64_t pcg_step_out(uint64_t& hi, uint64_t& lo, uin
     const uint64_t x = hi ^ lo;
     const unsigned rot = (unsigned)(hi >> 58);
     return (x >> rot) | (x << ((64u - rot) & 63u));
+}
+
+__device__ __forceinline__ uint64_t pcg_out(uint64_t hi, uint64_t lo) {
+    const uint64_t x = hi ^ lo;
+    const unsigned rot = (unsigned)(hi >> 58);
+    return (x >> rot) | (x << ((64u - rot) & 63u));
+}
+
+// the SMP_T outputs of one thread-iteration, each state computed independently from the current
+// one (instruction-level parallelism instead of a serial multiply chain); advances (hi, lo) by SMP_T
+__device__ __forceinline__ void pcg_block_out(uint64_t& hi, uint64_t& lo, const SamplerArgs& a,
+                                              uint64_t (&out)[SMP_T]) {
+    uint64_t h_last = hi, l_last = lo;
+#pragma unroll
+    for (int k = 0; k < SMP_T; ++k) {
+        uint64_t h = hi, l = lo;
+        affine_apply(h, l, a.step_k[k]);
+        out[k] = pcg_out(h, l);
+        if (k == SMP_T - 1) h_last = h, l_last = l;
+    }
+    hi = h_last;
+    lo = l_last;
 }
 
 // exclusive block scan of one int per thread (256 threads); returns the block total in `total`
@@ -106,6 +131,8 @@ struct EmitArgs {
     const double* w;
     double* S0;                 // [nrep, K+1]  (zeroed by the host wrapper)
     double* S1;
+    int64_t* iter_base;         // per-iteration output positions (512 * SMP_T steps each)
+    int* iter_count;
     int64_t pos_lo, pos_hi;     // only outputs with pos_lo <= position < pos_hi are consumed (rank window)
     int64_t rep_lo;             // first replicate of the window: output rows are relative to it
     int block_offset;           // COUNT: first block of this launch (ranks count disjoint block ranges)
@@ -367,6 +394,73 @@ __global__ void __launch_bounds__(SMP_THREADS, 2)
     if (MODE == MODE_HIST && bad && e.status) atomicOr(e.status, bad);
 }
 
+// pass A (512 threads): accepted draws per iteration (512 * SMP_T LCG steps) and per block
+__global__ void __launch_bounds__(512, 2)
+    k_sampler_count(const __grid_constant__ SamplerArgs a, int block_offset, int64_t* __restrict__ block_count,
+                    int* __restrict__ iter_count) {
+    constexpr int T = SMP_T;
+    constexpr int NT = 512;
+    __shared__ int sm_c[2][NT / 32];
+    const int bid = blockIdx.x + block_offset;
+    const int64_t q_block = (int64_t)bid * a.steps_per_block;
+    uint64_t hi = a.s_hi, lo = a.s_lo;
+    {
+        uint64_t q = (uint64_t)q_block + (uint64_t)threadIdx.x * T;
+        for (int i = 0; q != 0 && i < SMP_NPOW; ++i, q >>= 1)
+            if (q & 1) affine_apply(hi, lo, a.pow2[i]);
+    }
+    const int64_t niter = a.steps_per_block / (NT * T);
+    const uint32_t n = a.n, thresh = a.thresh;
+    long long total = 0;
+    for (int64_t it = 0; it < niter; ++it) {
+        int c = 0;
+        uint64_t outs[T];
+        pcg_block_out(hi, lo, a, outs);
+#pragma unroll
+        for (int k = 0; k < T; ++k) {
+            const uint64_t o = outs[k];
+            c += (uint32_t)((uint64_t)(uint32_t)o * n) >= thresh ? 1 : 0;
+            c += (uint32_t)((o >> 32) * (uint64_t)n) >= thresh ? 1 : 0;
+        }
+        if (it == 0 && bid == 0 && threadIdx.x == 0 && a.pre_valid != 0)
+            c += (uint32_t)((uint64_t)a.pre_u32 * n) >= thresh ? 1 : 0;
+        c = __reduce_add_sync(0xffffffffu, c);
+        int* buf = sm_c[it & 1];
+        if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+#pragma unroll
+            for (int k = 0; k < NT / 32; ++k) t += buf[k];
+            iter_count[(int64_t)bid * niter + it] = t;
+            total += t;
+        }
+        affine_apply(hi, lo, a.iter_jump2);
+    }
+    if (threadIdx.x == 0) block_count[bid] = total;
+}
+
+// iter_base[j] = output position of the first draw of iteration j (one warp per block)
+__global__ void k_sampler_iter_scan(const int64_t* __restrict__ block_base, const int* __restrict__ iter_count,
+                                    int64_t* __restrict__ iter_base, int nblocks, int64_t niter) {
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= nblocks) return;
+    int64_t run = block_base[b];
+    for (int64_t i0 = 0; i0 < niter; i0 += 32) {
+        const int64_t i = i0 + lane;
+        const int v = i < niter ? iter_count[(int64_t)b * niter + i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (i < niter) iter_base[(int64_t)b * niter + i] = run + inc - v;
+        run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
 // exclusive scan of the per-block counts (a few thousand entries); flags a short raw range
 __global__ void k_sampler_scan(const int64_t* __restrict__ cnt, int64_t* __restrict__ base, int nblocks,
                                int64_t count, int* __restrict__ status) {
@@ -381,6 +475,8 @@ __global__ void k_sampler_scan(const int64_t* __restrict__ cnt, int64_t* __restr
 }
 
 }  // namespace txb
+
+#include "sampler_bucket.cuh"
 
 // ------------------------------------------------------------------ host side
 using namespace txb;
@@ -398,6 +494,8 @@ inline Affine mk_affine(u128 a, u128 c) {
 struct Plan {
     SamplerArgs a;
     int nblocks;
+    int64_t ipb;        // iterations (512 * SMP_T steps) per block
+    size_t head_bytes;  // scalars | block_count | block_base | iter_base | iter_count
 };
 
 // (a, c) of `delta` LCG steps
@@ -437,7 +535,7 @@ int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, 
     TXB_CHECK_ARG(want < 1.0e14, "sampler: %lld draws is beyond the jump table", (long long)count);
     const int64_t raw = (int64_t)want + 1;
     const int64_t steps = (raw + 1) / 2;
-    const int64_t per_iter = (int64_t)SMP_THREADS * SMP_T;
+    const int64_t per_iter = (int64_t)BK_THREADS * SMP_T;
     const int64_t iters = (steps + per_iter - 1) / per_iter;
     int64_t nb = (int64_t)sm_count() * 8;
     if (nb > iters) nb = iters;
@@ -449,6 +547,12 @@ int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, 
     u128 ja, jc;
     lcg_jump(inc, (uint64_t)(SMP_THREADS - 1) * SMP_T, ja, jc);
     a.iter_jump = mk_affine(ja, jc);
+    lcg_jump(inc, (uint64_t)(BK_THREADS - 1) * SMP_T, ja, jc);
+    a.iter_jump2 = mk_affine(ja, jc);
+    for (int k = 0; k < SMP_T; ++k) {
+        lcg_jump(inc, (uint64_t)(k + 1), ja, jc);
+        a.step_k[k] = mk_affine(ja, jc);
+    }
     u128 ca = mk128(PCG_MULT_HI, PCG_MULT_LO), cc = inc;
     for (int i = 0; i < SMP_NPOW; ++i) {
         a.pow2[i] = mk_affine(ca, cc);
@@ -456,6 +560,8 @@ int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, 
         ca = ca * ca;
     }
     TXB_CHECK_ARG((size_t)p.nblocks * 16 + 64 <= SMP_WS_HEAD, "sampler: too many blocks");
+    p.ipb = ipb;
+    p.head_bytes = align_up(SMP_WS_HEAD + (size_t)(nb * ipb) * 12 + 64, 256);
     return TXB_OK;
 }
 
@@ -463,19 +569,25 @@ struct Head {
     int64_t* block_count;
     int64_t* block_base;
     int64_t* raw_used;
+    int64_t* iter_base;
+    int* iter_count;
 };
 
-Head carve_head(void* ws, int nblocks) {
+Head carve_head(void* ws, const Plan& pl) {
     int64_t* p = reinterpret_cast<int64_t*>(ws);
-    return Head{p + 8, p + 8 + nblocks, p};
+    int64_t* ib = reinterpret_cast<int64_t*>(reinterpret_cast<char*>(ws) + SMP_WS_HEAD);
+    return Head{p + 8, p + 8 + pl.nblocks, p, ib, reinterpret_cast<int*>(ib + (int64_t)pl.nblocks * pl.ipb)};
 }
 
-// Workspace head (first txb_sampler_workspace_bytes() bytes), all int64:
-//   [0] raw_used scratch   [1..7] reserved   [8 .. 8+nblocks) block_count   [8+nblocks .. 8+2 nblocks) block_base
+// Workspace head (first txb_sampler_workspace_bytes(...) bytes):
+//   int64 [0] raw_used scratch, [1..7] reserved, [8 .. 8+nblocks) block_count, [8+nblocks .. 8+2 nblocks) block_base
+//   at byte 65536: int64 iter_base[nblocks * ipb], then int32 iter_count[nblocks * ipb]
 void bind_head(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* status) {
-    Head h = carve_head(ws, p.nblocks);
+    Head h = carve_head(ws, p);
     e.block_count = h.block_count;
     e.block_base = h.block_base;
+    e.iter_base = h.iter_base;
+    e.iter_count = h.iter_count;
     e.raw_used = raw_used ? raw_used : h.raw_used;
     e.status = status;
     e.pos_lo = 0;
@@ -487,19 +599,18 @@ void bind_head(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* sta
 // pass A over blocks [block_lo, block_hi); the other entries of block_count are zeroed so that
 // ranks counting disjoint ranges can combine their heads with a plain integer SUM
 int run_count(const Plan& p, EmitArgs& e, int block_lo, int block_hi, cudaStream_t st) {
-    if (cudaMemsetAsync(e.block_count, 0, sizeof(int64_t) * p.nblocks, st) != cudaSuccess) {
+    if (cudaMemsetAsync(e.block_count, 0, sizeof(int64_t) * p.nblocks, st) != cudaSuccess ||
+        cudaMemsetAsync(e.iter_count, 0, sizeof(int) * (size_t)p.nblocks * p.ipb, st) != cudaSuccess) {
         set_error("sampler: cudaMemsetAsync failed");
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
     if (block_hi <= block_lo) return TXB_OK;
-    e.block_offset = block_lo;
     {
         ProfScope prof("sampler_count", st);
-        k_sampler<MODE_COUNT, 1, false, false, int64_t><<<block_hi - block_lo, SMP_THREADS, 0, st>>>(p.a, e);
+        k_sampler_count<<<block_hi - block_lo, 512, 0, st>>>(p.a, block_lo, e.block_count, e.iter_count);
     }
-    e.block_offset = 0;
-    TXB_CUDA_LAUNCH_CHECK("k_sampler<count>");
+    TXB_CUDA_LAUNCH_CHECK("k_sampler_count");
     return TXB_OK;
 }
 
@@ -514,6 +625,8 @@ int run_scan(const Plan& p, EmitArgs& e, cudaStream_t st) {
     k_sampler_scan<<<1, 32, 0, st>>>(e.block_count, const_cast<int64_t*>(e.block_base), p.nblocks, p.a.count,
                                      e.status);
     TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
+    k_sampler_iter_scan<<<(p.nblocks + 7) / 8, 256, 0, st>>>(e.block_base, e.iter_count, e.iter_base, p.nblocks, p.ipb);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler_iter_scan");
     k_sampler<MODE_LOCATE, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
     TXB_CUDA_LAUNCH_CHECK("k_sampler<locate>");
     return TXB_OK;
@@ -536,9 +649,9 @@ int begin_emit(const Plan& p, EmitArgs& e, void* ws, int64_t* raw_used, int* sta
     return run_scan(p, e, st);
 }
 
-int check_head(const char* what, void* workspace, size_t ws_bytes) {
+int check_head(const char* what, void* workspace, size_t ws_bytes, const Plan& p) {
     TXB_CHECK_ARG(workspace != nullptr, "%s: null workspace", what);
-    if (ws_bytes < SMP_WS_HEAD) {
+    if (ws_bytes < p.head_bytes) {
         set_error("%s: workspace too small", what);
         return TXB_ERR_WORKSPACE;
     }
@@ -547,7 +660,26 @@ int check_head(const char* what, void* workspace, size_t ws_bytes) {
 
 }  // namespace
 
-extern "C" size_t txb_sampler_workspace_bytes(void) { return SMP_WS_HEAD; }
+static size_t head_bytes_for(int64_t ndat, int64_t count) {
+    const txb_pcg64 dummy = {0, 0, 0, 1, 0, 0};
+    Plan p;
+    return make_plan(&dummy, ndat, count, count, p) == TXB_OK ? p.head_bytes : 0;
+}
+
+extern "C" size_t txb_sampler_workspace_bytes(int64_t ndat, int64_t count) { return head_bytes_for(ndat, count); }
+
+extern "C" int txb_sampler_layout(int64_t ndat, int64_t count, int64_t* out) {
+    const txb_pcg64 dummy = {0, 0, 0, 1, 0, 0};
+    Plan p;
+    int rc = make_plan(&dummy, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    TXB_CHECK_ARG(out != nullptr, "txb_sampler_layout: null pointer");
+    out[0] = p.nblocks;                      // entries of block_count (int64, byte offset 64)
+    out[1] = (int64_t)p.nblocks * p.ipb;     // entries of iter_count (int32)
+    out[2] = (int64_t)SMP_WS_HEAD + 8 * out[1];  // byte offset of iter_count
+    out[3] = (int64_t)p.head_bytes;
+    return TXB_OK;
+}
 
 extern "C" int txb_sampler_nblocks(const txb_pcg64* rng, int64_t ndat, int64_t count) {
     Plan p;
@@ -556,10 +688,10 @@ extern "C" int txb_sampler_nblocks(const txb_pcg64* rng, int64_t ndat, int64_t c
 
 extern "C" int txb_sampler_count(const txb_pcg64* rng, int64_t ndat, int64_t count, int block_lo,
                                  int block_hi, void* workspace, size_t ws_bytes, void* stream) {
-    int rc = check_head("txb_sampler_count", workspace, ws_bytes);
-    if (rc != TXB_OK) return rc;
     Plan p;
-    rc = make_plan(rng, ndat, count, count, p);
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_count", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     if (block_hi < 0 || block_hi > p.nblocks) block_hi = p.nblocks;
     TXB_CHECK_ARG(block_lo >= 0 && block_lo <= block_hi, "txb_sampler_count: bad block range");
@@ -570,10 +702,10 @@ extern "C" int txb_sampler_count(const txb_pcg64* rng, int64_t ndat, int64_t cou
 
 extern "C" int txb_sampler_scan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
                                 int* status, void* workspace, size_t ws_bytes, void* stream) {
-    int rc = check_head("txb_sampler_scan", workspace, ws_bytes);
-    if (rc != TXB_OK) return rc;
     Plan p;
-    rc = make_plan(rng, ndat, count, count, p);
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_scan", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     EmitArgs e{};
     bind_head(p, e, workspace, raw_used, status);
@@ -582,10 +714,10 @@ extern "C" int txb_sampler_scan(const txb_pcg64* rng, int64_t ndat, int64_t coun
 
 extern "C" int txb_sampler_prepare(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t* raw_used,
                                    int* status, void* workspace, size_t ws_bytes, void* stream) {
-    int rc = check_head("txb_sampler_prepare", workspace, ws_bytes);
-    if (rc != TXB_OK) return rc;
     Plan p;
-    rc = make_plan(rng, ndat, count, count, p);
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_prepare", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     EmitArgs e{};
     return begin_emit(p, e, workspace, raw_used, status, 0, (cudaStream_t)stream);
@@ -622,10 +754,10 @@ extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t c
     TXB_CHECK_ARG(0 <= pos_lo && pos_lo < pos_hi && pos_hi <= count,
                   "txb_sampler_indices: bad window [%lld, %lld) of %lld", (long long)pos_lo, (long long)pos_hi,
                   (long long)count);
-    int rc = check_head("txb_sampler_indices", workspace, ws_bytes);
-    if (rc != TXB_OK) return rc;
     Plan p;
-    rc = make_plan(rng, ndat, count, count, p);
+    int rc = make_plan(rng, ndat, count, count, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_indices", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     EmitArgs e{};
@@ -651,10 +783,10 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
     static const size_t esz[4] = {8, 4, 2, 1};
     TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
                   "txb_sampler_freq: narrow table rows must be 4-byte aligned");
-    int rc = check_head("txb_sampler_freq", workspace, ws_bytes);
-    if (rc != TXB_OK) return rc;
     Plan p;
-    rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_freq", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
@@ -680,15 +812,108 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
     return TXB_OK;
 }
 
-extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep) {
-    const size_t dbl = (size_t)(2 * ndat) + (size_t)(2 * nrep * (order + 2)) + 16;
-    return align_up(SMP_WS_HEAD + dbl * sizeof(double) + 512, 256);
+namespace {
+
+// geometry of the bucketed path for one call
+struct BucketPlan {
+    bool ok;
+    int nb, cap;
+    double m;              // expected entries of one (replicate, bucket) list
+    size_t fixed_bytes;    // everything except the per-replicate part
+};
+
+// segments per replicate, draws per segment and list capacity for a window of `nwin` replicates
+struct SegPlan {
+    int nseg, cap_lines;
+    int64_t seg_len;
+    size_t per_rep_bytes;  // line counts + partials + lists for one replicate
+};
+
+SegPlan seg_plan(const BucketPlan& b, int64_t nsamp, int ks, int64_t nwin) {
+    SegPlan s{};
+    int64_t nseg = (4 * (int64_t)sm_count() + nwin - 1) / nwin;  // >= 4 CTAs per SM in flight overall
+    const int64_t max_seg = (int64_t)(b.m / (8.0 * BK_LINE));     // keep lists mostly full lines
+    if (nseg > max_seg) nseg = max_seg;
+    if (nseg < 1) nseg = 1;
+    s.nseg = (int)nseg;
+    s.seg_len = (nsamp + nseg - 1) / nseg;
+    const double ms = b.m * (double)s.seg_len / (double)nsamp;
+    s.cap_lines = (int)((ms + 10.0 * sqrt(ms) + 32.0) / BK_LINE) + 3;
+    s.per_rep_bytes = (size_t)b.nb * (sizeof(unsigned) * s.nseg + 2 * sizeof(double) * (ks + 1) +
+                                      (size_t)s.nseg * s.cap_lines * BK_LINE * 2) + 64;
+    return s;
+}
+
+BucketPlan bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp, int64_t nrep_out, int order) {
+    BucketPlan b{};
+    b.nb = (int)((ndat + BK_SIZE - 1) / BK_SIZE);
+    b.m = ndat <= BK_SIZE ? (double)nsamp : (double)nsamp * BK_SIZE / (double)ndat;
+    // ring: 31 pending + one iteration's arrivals (Poisson, mean 8192 / nb) with a 6 sigma margin
+    const double arrivals = (double)(BK_THREADS * 2 * SMP_T) / b.nb;
+    b.cap = BK_MINCAP;
+    while (b.cap < 32.0 + arrivals + 6.0 * sqrt(arrivals)) b.cap *= 2;
+    // worth it only for tables too big for L2-resident gathers, with mostly full lines
+    b.ok = ndat >= (int64_t)4 << 20 && b.nb <= BK_MAXNB && b.m >= 8.0 * BK_LINE &&
+           (size_t)b.nb * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
+    b.fixed_bytes = p.head_bytes + 256 + sizeof(double2) * (size_t)ndat +
+                    sizeof(double) * (8 + 2 * (size_t)nrep_out * (order + 2));
+    return b;
+}
+
+template <int K>
+int launch_consume(const ConsumeArgs& c, bool has_x, bool has_w, int gy, cudaStream_t st) {
+    const size_t smem = sizeof(double2) * BK_SIZE + (has_w ? sizeof(double) * BK_SIZE : 0);
+    const dim3 grid((unsigned)c.nb, (unsigned)gy);
+#define TXB_CONSUME(HX, HW)                                                                                  \
+    {                                                                                                        \
+        static bool done = false;                                                                            \
+        if (!done) {                                                                                         \
+            if (cudaFuncSetAttribute(k_bucket_consume<K, HX, HW>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                     (int)(sizeof(double2) * BK_SIZE + sizeof(double) * BK_SIZE)) != cudaSuccess) { \
+                set_error("k_bucket_consume: shared memory opt-in failed");                                  \
+                cudaGetLastError();                                                                          \
+                return TXB_ERR_CUDA;                                                                         \
+            }                                                                                                \
+            done = true;                                                                                     \
+        }                                                                                                    \
+        k_bucket_consume<K, HX, HW><<<grid, BK_THREADS, smem, st>>>(c);                                      \
+    }
+    if (has_x) {
+        if (has_w) TXB_CONSUME(true, true) else TXB_CONSUME(true, false)
+    } else {
+        if (has_w) TXB_CONSUME(false, true) else TXB_CONSUME(false, false)
+    }
+#undef TXB_CONSUME
+    TXB_CUDA_LAUNCH_CHECK("k_bucket_consume");
+    return TXB_OK;
+}
+
+}  // namespace
+
+extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t nsamp,
+                                                       int64_t nrep_out) {
+    const size_t head = head_bytes_for(ndat, nrep * nsamp);
+    if (head == 0) return 0;
+    const size_t dbl = (size_t)(2 * ndat) + (size_t)(2 * nrep_out * (order + 2)) + 16;
+    return align_up(head + dbl * sizeof(double) + 512, 256);
+}
+
+extern "C" size_t txb_sampler_resample_fast_workspace_bytes(int64_t ndat, int order, int mode, int64_t nrep,
+                                                            int64_t nsamp, int64_t nrep_out) {
+    const txb_pcg64 dummy = {0, 0, 0, 1, 0, 0};
+    Plan p;
+    if (make_plan(&dummy, ndat, nrep * nsamp, nsamp, p) != TXB_OK) return 0;
+    const int ks = mode == TXB_MODE_X_IS_U ? order + 1 : order;
+    const BucketPlan b = bucket_plan(p, ndat, nsamp, nrep_out, order);
+    if (!b.ok) return txb_sampler_resample_workspace_bytes(ndat, order, nrep, nsamp, nrep_out);
+    const SegPlan sp = seg_plan(b, nsamp, ks, nrep_out);
+    return align_up(b.fixed_bytes + sp.per_rep_bytes * (size_t)nrep_out + 4096, 256);
 }
 
 extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, const double* u,
                                         const double* w, int64_t ndat, int64_t ldx, int order, int mode,
                                         int64_t nrep, int64_t nsamp, int64_t rep_lo, int64_t rep_hi,
-                                        double* out, int64_t* raw_used, int* status, int prepared,
+                                        double* out, int64_t* raw_used, int* status, int flags,
                                         void* workspace, size_t ws_bytes, void* stream) {
     TXB_CHECK_ARG(u && out && workspace, "txb_sampler_resample_f64: null pointer");
     TXB_CHECK_ARG(order >= 1 && nrep >= 1 && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
@@ -696,34 +921,122 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
                   (long long)rep_lo, (long long)rep_hi);
     TXB_CHECK_ARG(mode == TXB_MODE_COMOMENTS ? x != nullptr : (mode == TXB_MODE_X_IS_U && x == nullptr),
                   "txb_sampler_resample_f64: mode COMOMENTS needs x, mode X_IS_U needs x == NULL");
+    const int prepared = flags & TXB_SAMPLER_PREPARED;
     const int64_t nwin = rep_hi - rep_lo;
-    if (ws_bytes < txb_sampler_resample_workspace_bytes(ndat, order, nwin)) {
-        set_error("txb_sampler_resample_f64: workspace too small");
-        return TXB_ERR_WORKSPACE;
-    }
     Plan p;
     int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
     if (rc != TXB_OK) return rc;
+    if (ws_bytes < txb_sampler_resample_workspace_bytes(ndat, order, nrep, nsamp, nwin)) {
+        set_error("txb_sampler_resample_f64: workspace too small");
+        return TXB_ERR_WORKSPACE;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     const int ks = mode == TXB_MODE_X_IS_U ? order + 1 : order;
-    char* base = reinterpret_cast<char*>(workspace) + SMP_WS_HEAD;
+    TXB_CHECK_ARG(ks <= TXB_MAXK, "txb_sampler_resample_f64: order %d not supported", order);
+    char* base = reinterpret_cast<char*>(workspace) + p.head_bytes;
     base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(base) + 15) & ~(uintptr_t)15);
     double2* packed = reinterpret_cast<double2*>(base);
     double* pivot = reinterpret_cast<double*>(packed + ndat);
     double* S0 = pivot + 4;
     double* S1 = S0 + nwin * (order + 2);
+    char* dyn = reinterpret_cast<char*>(S1 + nwin * (order + 2));
+    dyn = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(dyn) + 63) & ~(uintptr_t)63);
     rc = txb_pivot_f64(x, u, ndat, 1, x ? ldx : 1, 0, pivot, stream);
     if (rc != TXB_OK) return rc;
     rc = launch_pack_shifted(x, x ? ldx : 0, u, ndat, pivot, packed, st);
     if (rc != TXB_OK) return rc;
+    EmitArgs e{};
+    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
+    if (rc != TXB_OK) return rc;
+
+    // ---- bucketed path when the table is too big for L2-resident gathers and scratch allows it
+    const BucketPlan bp = bucket_plan(p, ndat, nsamp, nwin, order);
+    const size_t used = (size_t)(dyn - reinterpret_cast<char*>(workspace));
+    const size_t avail = ws_bytes > used + 4096 ? ws_bytes - used - 4096 : 0;
+    int64_t wrep = 0;
+    SegPlan sp{};
+    if (bp.ok && !(flags & TXB_SAMPLER_NO_BUCKETS)) {
+        wrep = nwin;
+        sp = seg_plan(bp, nsamp, ks, wrep);
+        while (wrep > 0 && sp.per_rep_bytes * (size_t)wrep > avail) {  // fewer replicates per window
+            const int64_t fit = (int64_t)(avail / sp.per_rep_bytes);
+            wrep = fit < wrep ? fit : wrep - 1;
+            if (wrep > 0) sp = seg_plan(bp, nsamp, ks, wrep);
+        }
+        if (wrep < 32 && wrep < nwin) wrep = 0;  // too little scratch to be worth it
+    }
+    if (wrep > 0) {
+        unsigned* nlines = reinterpret_cast<unsigned*>(dyn);
+        double* ws0 = reinterpret_cast<double*>(dyn + align_up(sizeof(unsigned) * (size_t)wrep * bp.nb * sp.nseg, 64));
+        double* ws1 = ws0 + (size_t)bp.nb * wrep * (ks + 1);
+        uint16_t* lists = reinterpret_cast<uint16_t*>(ws1 + (size_t)bp.nb * wrep * (ks + 1));
+        lists = reinterpret_cast<uint16_t*>((reinterpret_cast<uintptr_t>(lists) + 63) & ~(uintptr_t)63);
+        static bool attr_done = false;
+        if (!attr_done) {
+            if (cudaFuncSetAttribute(k_bucket_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess) {
+                set_error("k_bucket_scatter: shared memory opt-in failed");
+                cudaGetLastError();
+                return TXB_ERR_CUDA;
+            }
+            attr_done = true;
+        }
+        const size_t sc_smem = (size_t)bp.nb * (bp.cap * 2 + 12);
+        for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
+            const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
+            const int64_t nw = r1 - r0;
+            BucketArgs ba{};
+            ba.iter_base = e.iter_base;
+            ba.iter_count = e.iter_count;
+            ba.niter = (int64_t)p.nblocks * p.ipb;
+            ba.status = status;
+            ba.lists = lists;
+            ba.nlines = nlines;
+            ba.nb = bp.nb;
+            ba.cap = bp.cap;
+            ba.cap_lines = sp.cap_lines;
+            ba.nseg = sp.nseg;
+            ba.seg_len = sp.seg_len;
+            ba.rep_lo = r0;
+            {
+                ProfScope prof("bucket_scatter", st);
+                k_bucket_scatter<<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
+            }
+            TXB_CUDA_LAUNCH_CHECK("k_bucket_scatter");
+            ConsumeArgs c{};
+            c.packed = packed;
+            c.w = w;
+            c.ndat = ndat;
+            c.lists = lists;
+            c.nlines = nlines;
+            c.nb = bp.nb;
+            c.cap_lines = sp.cap_lines;
+            c.nseg = sp.nseg;
+            c.nwin = nw;
+            c.ws0 = ws0;
+            c.ws1 = ws1;
+            int gy = (2 * sm_count() + bp.nb - 1) / bp.nb;
+            const int gy_max = (int)((nw + BK_THREADS / 32 - 1) / (BK_THREADS / 32));
+            if (gy > gy_max) gy = gy_max;
+            if (gy < 1) gy = 1;
+            {
+                ProfScope prof("bucket_consume", st);
+                TXB_DISPATCH_ORDER(ks, { rc = launch_consume<K>(c, x != nullptr, w != nullptr, gy, st); });
+            }
+            if (rc != TXB_OK) return rc;
+            rc = launch_sum_parts(ws0, bp.nb, nw * (ks + 1), S0 + (r0 - rep_lo) * (ks + 1), st);
+            if (rc == TXB_OK && x) rc = launch_sum_parts(ws1, bp.nb, nw * (ks + 1), S1 + (r0 - rep_lo) * (ks + 1), st);
+            if (rc != TXB_OK) return rc;
+        }
+        return txb_finalize_f64(S0, S1, pivot, nwin, 1, 1, order, mode, out, stream);
+    }
+
+    // ---- gather path
     if (cudaMemsetAsync(S0, 0, sizeof(double) * 2 * nwin * (order + 2), st) != cudaSuccess) {
         set_error("txb_sampler_resample_f64: cudaMemsetAsync failed");
         cudaGetLastError();
         return TXB_ERR_CUDA;
     }
-    EmitArgs e{};
-    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
-    if (rc != TXB_OK) return rc;
     e.packed = packed;
     e.w = w;
     e.S0 = S0;

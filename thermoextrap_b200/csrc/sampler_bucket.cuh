@@ -1,0 +1,312 @@
+// K6 + K2 for scalar x without random HBM gathers: "bucketed" bootstrap.  Included by sampler.cu.
+//
+// The fused gather kernel (k_sampler<GATHER>) is bound by random 64-byte DRAM bursts: 60 B of
+// traffic per 16-byte draw on a table that cannot stay in L2 (profiles/r01_gather_ncu_full.txt).
+// Here the draws are first partitioned by sample bucket (8192 consecutive samples) with software
+// write-combining through shared memory, then every bucket is consumed from a shared-memory copy
+// of its samples:
+//
+//   k_bucket_scatter  regenerates the sampler's stream (same blocks / offsets as every other
+//                     pass-B kernel), appends each draw's 13-bit local index to a 64-entry ring
+//                     per bucket in shared memory, and writes full 32-entry lines (64 B) to the
+//                     (replicate, bucket) list in HBM.  Rings are drained (padded lines) at every
+//                     replicate boundary and at the end of the block.
+//   k_bucket_consume  one CTA per bucket: stages the bucket's (dx, du[, w]) in shared memory, then
+//                     each warp walks the lists of its replicates with coalesced 16-byte loads and
+//                     gathers from shared memory; per-(replicate, bucket) power sums are reduced
+//                     with shuffles and written as partials (summed by k_sum_parts).
+//
+// HBM traffic: 2 bytes per draw written + read, streaming, instead of a random 64-byte burst.
+#pragma once
+
+namespace txb {
+
+constexpr int BK_LOG = 13;
+constexpr int BK_SIZE = 1 << BK_LOG;     // samples per bucket
+constexpr int BK_MINCAP = 64;            // smallest ring (entries per bucket, uint16); rings are a power of two
+constexpr int BK_LINE = 32;              // entries per flushed line (64 bytes)
+constexpr int BK_MAXNB = 1536;           // buckets a producer CTA can hold rings for
+constexpr int BK_THREADS = 512;
+constexpr uint16_t BK_EMPTY = 0xFFFFu;
+
+struct BucketArgs {
+    const int64_t* iter_base;   // [niter] output position of the first draw of each iteration
+    const int* iter_count;      // [niter]
+    int64_t niter;
+    int* status;          // |= 8 when a list overflows its capacity
+    uint16_t* lists;      // [nwin][nb][nseg][cap_lines][BK_LINE]
+    unsigned* nlines;     // [nwin][nb][nseg] lines written
+    int nb;               // buckets
+    int cap;              // ring entries per bucket (power of two >= BK_MINCAP)
+    int cap_lines;        // per segment list
+    int nseg;
+    int64_t seg_len;      // draws per segment
+    int64_t rep_lo;       // first replicate of the window
+};
+
+// exclusive block scan for BK_THREADS threads
+__device__ __forceinline__ int bk_block_scan(int v, int* sm_warp, int& total) {
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();
+    if (lane == 31) sm_warp[wrp] = inc;
+    __syncthreads();
+    int base = 0, tot = 0;
+#pragma unroll
+    for (int k = 0; k < BK_THREADS / 32; ++k) {
+        const int w = sm_warp[k];
+        if (k < wrp) base += w;
+        tot += w;
+    }
+    total = tot;
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(BK_THREADS, 1)
+    k_bucket_scatter(const __grid_constant__ SamplerArgs a, const BucketArgs e) {
+    constexpr int T = SMP_T;
+    constexpr int NSLOT = 2 * T;
+    extern __shared__ __align__(16) unsigned char bk_smem[];
+    const int nb = e.nb;
+    const unsigned cap = (unsigned)e.cap;
+    uint16_t* rings = reinterpret_cast<uint16_t*>(bk_smem);                        // [nb][cap]
+    unsigned* tail = reinterpret_cast<unsigned*>(bk_smem + (size_t)nb * cap * 2);  // [nb]
+    unsigned* head = tail + nb;                                                    // [nb]
+    unsigned* lines = head + nb;                                                   // [nb] lines written
+    __shared__ int sm_warp[BK_THREADS / 32];
+    __shared__ long long sm_j0;
+
+    const int seg = blockIdx.x;
+    const int64_t r = blockIdx.y;  // window-relative replicate
+    const int64_t rep_begin = (e.rep_lo + r) * a.nsamp;
+    const int64_t A = rep_begin + (int64_t)seg * e.seg_len;
+    int64_t B = A + e.seg_len;
+    if (B > rep_begin + a.nsamp) B = rep_begin + a.nsamp;
+    const int64_t list0 = (r * nb) * e.nseg + seg;  // + b * nseg
+
+    for (int b = threadIdx.x; b < nb; b += BK_THREADS) tail[b] = 0u, head[b] = 0u, lines[b] = 0u;
+    if (threadIdx.x == 0) {
+        // last iteration whose first output position is <= A
+        int64_t lo = 0, hi = e.niter - 1;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi + 1) >> 1;
+            if (e.iter_base[mid] <= A) lo = mid; else hi = mid - 1;
+        }
+        sm_j0 = lo;
+    }
+    __syncthreads();
+    if (A >= B) {  // empty segment
+        for (int b = threadIdx.x; b < nb; b += BK_THREADS) e.nlines[list0 + (int64_t)b * e.nseg] = 0u;
+        return;
+    }
+    const int64_t j0 = sm_j0;
+    uint64_t hi = a.s_hi, lo = a.s_lo;
+    {
+        uint64_t q = ((uint64_t)j0 * BK_THREADS + threadIdx.x) * T;
+        for (int i = 0; q != 0 && i < SMP_NPOW; ++i, q >>= 1)
+            if (q & 1) affine_apply(hi, lo, a.pow2[i]);
+    }
+    const uint32_t n = a.n, thresh = a.thresh;
+
+    auto write_line = [&](int b, unsigned h, int cnt) {
+        const unsigned line = lines[b];
+        lines[b] = line + 1;
+        if (line >= (unsigned)e.cap_lines) {
+            if (e.status) atomicOr(e.status, 8);
+            return;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(e.lists + ((list0 + (int64_t)b * e.nseg) * e.cap_lines + line) * BK_LINE);
+        const uint16_t* src = rings + (size_t)b * cap + (h & (cap - 1));  // h is a multiple of BK_LINE
+        if (cnt == BK_LINE) {
+            const uint4* s4 = reinterpret_cast<const uint4*>(src);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) __stcs(dst + q, s4[q]);
+        } else {
+            uint16_t tmp[BK_LINE];
+#pragma unroll
+            for (int q = 0; q < BK_LINE; ++q) tmp[q] = q < cnt ? src[q] : BK_EMPTY;
+            const uint4* t4 = reinterpret_cast<const uint4*>(tmp);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) __stcs(dst + q, t4[q]);
+        }
+    };
+    // every bucket ring is drained by one fixed thread: full lines always, the remainder when `all`
+    auto drain = [&](bool all) {
+        for (int b = threadIdx.x; b < nb; b += BK_THREADS) {
+            unsigned t = tail[b], h = head[b];
+            if (t - h > cap) {
+                // more arrivals than the ring holds (> 6 sigma).  The checked append writes those as
+                // one-entry lines; the fast append has wrapped over unread entries: flag it, the
+                // caller redoes the call on the gather path.
+                if (e.status) atomicOr(e.status, 16);
+                t = h + cap;
+            }
+            while (t - h >= (unsigned)BK_LINE) {
+                write_line(b, h, BK_LINE);
+                h += BK_LINE;
+            }
+            if (all) {
+                if (t != h) write_line(b, h, (int)(t - h));
+                t = h = 0u;
+            }
+            tail[b] = t;
+            head[b] = h;
+        }
+    };
+    auto append = [&](uint32_t v) {
+        const int b = (int)(v >> BK_LOG);
+        const uint16_t loc = (uint16_t)(v & (BK_SIZE - 1));
+        const unsigned slot = atomicAdd(tail + b, 1u);
+        if (slot - head[b] < cap) {
+            rings[(size_t)b * cap + (slot & (cap - 1))] = loc;
+        } else {  // ring full (> 6 sigma): a one-entry line, slot taken with a shared-memory atomic
+            const unsigned line = atomicAdd(lines + b, 1u);
+            if (line >= (unsigned)e.cap_lines) {
+                if (e.status) atomicOr(e.status, 8);
+            } else {
+                uint16_t* dst = e.lists + ((list0 + (int64_t)b * e.nseg) * e.cap_lines + line) * BK_LINE;
+                dst[0] = loc;
+                for (int q = 1; q < BK_LINE; ++q) dst[q] = BK_EMPTY;
+            }
+        }
+    };
+
+    for (int64_t j = j0; j < e.niter; ++j) {
+        const int64_t P = e.iter_base[j];
+        if (P >= B) break;
+        const int total = e.iter_count[j];
+        uint32_t val[NSLOT];
+        uint32_t mask = 0;
+        uint64_t outs[T];
+        pcg_block_out(hi, lo, a, outs);
+#pragma unroll
+        for (int k = 0; k < T; ++k) {
+            const uint64_t o = outs[k];
+            const uint64_t m0 = (uint64_t)(uint32_t)o * n;
+            const uint64_t m1 = (o >> 32) * (uint64_t)n;
+            val[2 * k] = (uint32_t)(m0 >> 32);
+            val[2 * k + 1] = (uint32_t)(m1 >> 32);
+            if ((uint32_t)m0 >= thresh) mask |= 1u << (2 * k);
+            if ((uint32_t)m1 >= thresh) mask |= 1u << (2 * k + 1);
+        }
+        const bool pre = j == 0 && threadIdx.x == 0 && a.pre_valid != 0;
+        uint32_t pre_val = 0;
+        bool pre_acc = false;
+        if (pre) {
+            const uint64_t m = (uint64_t)a.pre_u32 * n;
+            pre_val = (uint32_t)(m >> 32);
+            pre_acc = (uint32_t)m >= thresh;
+        }
+        if (P >= A && P + total <= B) {  // block-uniform: the whole iteration belongs to this segment
+            if (pre_acc) append(pre_val);
+            // all slot reservations first (independent shared-memory atomics), then the stores
+            unsigned slot[NSLOT];
+#pragma unroll
+            for (int k = 0; k < NSLOT; ++k)
+                if (mask & (1u << k)) slot[k] = atomicAdd(tail + (val[k] >> BK_LOG), 1u);
+#pragma unroll
+            for (int k = 0; k < NSLOT; ++k)
+                if (mask & (1u << k))
+                    rings[(val[k] >> BK_LOG) * cap + (slot[k] & (cap - 1))] = (uint16_t)(val[k] & (BK_SIZE - 1));
+        } else {
+            int tot;
+            const int c = __popc(mask) + (pre_acc ? 1 : 0);
+            int64_t pos = P + bk_block_scan(c, sm_warp, tot);
+            if (pre_acc) {
+                if (pos >= A && pos < B) append(pre_val);
+                ++pos;
+            }
+#pragma unroll
+            for (int k = 0; k < NSLOT; ++k) {
+                if (mask & (1u << k)) {
+                    if (pos >= A && pos < B) append(val[k]);
+                    ++pos;
+                }
+            }
+        }
+        __syncthreads();
+        drain(false);
+        __syncthreads();
+        affine_apply(hi, lo, a.iter_jump2);
+    }
+    drain(true);
+    for (int b = threadIdx.x; b < nb; b += BK_THREADS) {
+        const unsigned nl = lines[b];
+        e.nlines[list0 + (int64_t)b * e.nseg] = nl < (unsigned)e.cap_lines ? nl : (unsigned)e.cap_lines;
+    }
+}
+
+struct ConsumeArgs {
+    const double2* packed;   // [ndat] (x - cx, u - cu)
+    const double* w;         // [ndat] or NULL
+    int64_t ndat;
+    const uint16_t* lists;
+    const unsigned* nlines;
+    int nb, cap_lines, nseg;
+    int64_t nwin;            // replicates in this window
+    double* ws0;             // [nb][nwin][K+1] partial sums per bucket
+    double* ws1;
+};
+
+// one CTA per bucket; warps take replicates round-robin
+template <int K, bool HAS_X, bool HAS_W>
+__global__ void __launch_bounds__(BK_THREADS, 1) k_bucket_consume(const ConsumeArgs c) {
+    extern __shared__ __align__(16) unsigned char bk_smem[];
+    double2* tile = reinterpret_cast<double2*>(bk_smem);                                  // [BK_SIZE]
+    double* wt = reinterpret_cast<double*>(bk_smem + sizeof(double2) * BK_SIZE);          // [BK_SIZE] if HAS_W
+    const int b = blockIdx.x;
+    const int64_t s0 = (int64_t)b * BK_SIZE;
+    for (int i = threadIdx.x; i < BK_SIZE; i += BK_THREADS) {
+        const int64_t s = s0 + i;
+        tile[i] = s < c.ndat ? c.packed[s] : make_double2(0.0, 0.0);
+        if (HAS_W) wt[i] = s < c.ndat ? c.w[s] : 0.0;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    constexpr int NW = BK_THREADS / 32;
+    for (int64_t r = blockIdx.y * NW + wrp; r < c.nwin; r += (int64_t)gridDim.y * NW) {
+        Acc<K, HAS_X> acc;
+        acc.zero();
+        for (int seg = 0; seg < c.nseg; ++seg) {
+            const int64_t list = (r * c.nb + b) * c.nseg + seg;
+            const uint4* L = reinterpret_cast<const uint4*>(c.lists + list * c.cap_lines * BK_LINE);
+            const int nq = (int)c.nlines[list] * 4;  // 16-byte chunks (8 entries each)
+            uint4 q = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+            if (lane < nq) q = __ldcs(L + lane);
+            for (int i = lane; i < nq; i += 32) {
+                const uint4 cur = q;
+                if (i + 32 < nq) q = __ldcs(L + i + 32);  // prefetch the next chunk
+                const uint32_t wds[4] = {cur.x, cur.y, cur.z, cur.w};
+                double2 v[8];
+                double pw[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const uint32_t loc = (wds[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+                    const bool ok = loc != BK_EMPTY;
+                    const uint32_t li = ok ? loc : 0u;
+                    v[t] = tile[li];
+                    pw[t] = ok ? (HAS_W ? wt[li] : 1.0) : 0.0;
+                }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) acc.push(v[t], pw[t]);
+            }
+        }
+        const int64_t o = ((int64_t)b * c.nwin + r) * (K + 1);
+#pragma unroll
+        for (int j = 0; j <= K; ++j) {
+            const double a0 = warp_sum(acc.s0[j]);
+            if (lane == 0) c.ws0[o + j] = a0;
+            if (HAS_X) {
+                const double a1 = warp_sum(acc.s1[j]);
+                if (lane == 0) c.ws1[o + j] = a1;
+            }
+        }
+    }
+}
+
+}  // namespace txb

@@ -332,10 +332,13 @@ class SamplerPlan:
         self.nrep, self.nsamp = int(nrep), int(nsamp)
         self.ndat = self.nsamp if ndat is None else int(ndat)
         self.state = pcg64_state(rng)
-        self.head = torch.zeros(lib.txb_sampler_workspace_bytes(), dtype=torch.uint8, device=dev)
+        count = self.nrep * self.nsamp
+        nhead = lib.txb_sampler_workspace_bytes(self.ndat, count)
+        if nhead == 0:
+            check(1, "txb_sampler_workspace_bytes")
+        self.head = torch.zeros(nhead, dtype=torch.uint8, device=dev)
         aux = torch.zeros(2, dtype=torch.int64, device=dev)
         status = aux[1:].view(torch.int32)
-        count = self.nrep * self.nsamp
         args = (C.byref(self.state), self.ndat, count)
         with torch.cuda.device(dev):
             if group is None:
@@ -352,8 +355,11 @@ class SamplerPlan:
                 lo, hi = nb * rank // world, nb * (rank + 1) // world
                 check(lib.txb_sampler_count(*args, lo, hi, self.head.data_ptr(), self.head.numel(), _stream_ptr()),
                       "txb_sampler_count")
-                counts = self.head.view(torch.int64)[8 : 8 + nb]
-                dist.all_reduce(counts, group=group)  # ranks counted disjoint block ranges
+                lay = (C.c_int64 * 4)()
+                check(lib.txb_sampler_layout(self.ndat, count, lay), "txb_sampler_layout")
+                # ranks counted disjoint block ranges: integer SUM of the two count arrays
+                dist.all_reduce(self.head.view(torch.int64)[8 : 8 + lay[0]], group=group)
+                dist.all_reduce(self.head[lay[2] : lay[2] + 4 * lay[1]].view(torch.int32), group=group)
                 check(lib.txb_sampler_scan(*args, aux.data_ptr(), status.data_ptr(), self.head.data_ptr(),
                                            self.head.numel(), _stream_ptr()), "txb_sampler_scan")
         launch_count += 3
@@ -431,7 +437,8 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
 
 
 def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
-                     nsamp: int | None = None, sync_rng: bool = True, reps=None) -> torch.Tensor:
+                     nsamp: int | None = None, sync_rng: bool = True, reps=None, buckets: bool = True,
+                     scratch_bytes: int | None = None) -> torch.Tensor:
     """K2 fused with the generator (scalar x): bootstrap comoments for ``{"nrep": nrep, "rng": rng}``.
 
     Neither the index nor the frequency table is materialised.  With a raw ``Generator`` and
@@ -462,15 +469,29 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
         raise ValueError(msg)
     out = torch.empty((hi - lo, 1, 2, order + 1), dtype=torch.float64, device=dev)
     mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    flags = (_lib.SAMPLER_PREPARED if prepared else 0) | (0 if buckets else _lib.SAMPLER_NO_BUCKETS)
     with torch.cuda.device(dev):
-        nb = lib.txb_sampler_resample_workspace_bytes(ndat, order, hi - lo)
+        nb = lib.txb_sampler_resample_workspace_bytes(ndat, order, nrep, nsamp, hi - lo)
+        if nb == 0:
+            check(1, "txb_sampler_resample_workspace_bytes")
+        if buckets:
+            # scratch for the bucketed path: all replicates in one window if memory allows,
+            # otherwise as many as fit in a third of what is free (the library windows the rest)
+            fast = lib.txb_sampler_resample_fast_workspace_bytes(ndat, order, mode, nrep, nsamp, hi - lo)
+            held = _workspaces.get((dev.index or 0, torch.cuda.current_stream().cuda_stream))
+            free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
+            nb = max(nb, min(fast, free // 3 if scratch_bytes is None else nb + scratch_bytes))
         ws = plan.workspace(nb, dev) if plan is not None else _workspace(nb, dev)
         st = lib.txb_sampler_resample_f64(
             C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, lo, hi, out.data_ptr(),
-            None, None, prepared, ws.data_ptr(), ws.numel(), _stream_ptr(),
+            None, status.data_ptr(), flags, ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_sampler_resample_f64")
     launch_count += 5 if prepared else 8
+    if buckets and int(status.item()) & 24:  # a bucket list / ring overflowed its margin: redo by gathering
+        return sampler_resample(src if plan is None else plan, x, u, nrep, order, w=w, x_is_u=x_is_u, nsamp=nsamp,
+                                sync_rng=False, reps=reps, buckets=False)
     return out.reshape(hi - lo, *val_shape, 2, order + 1)
 
 

@@ -147,6 +147,16 @@ def sampler():
         rng = np.random.default_rng(0)
         t, tm = timeit(lambda: K.sampler_resample(rng, x, u, nrep, order, sync_rng=False), warm=2, rep=3)
         print(json.dumps({"sampler_fused": [n, order, nrep], "ms": t * 1e3, "ms_med": tm * 1e3, "draws_per_s": nrep * n / t, "reps_per_s": nrep / t}))
+        lib = _lib.load()
+        for tag in (b"sampler_count", b"bucket_scatter", b"bucket_consume"):
+            lib.txb_profile_begin(tag)
+            for _ in range(3):
+                K.sampler_resample(rng, x, u, nrep, order, sync_rng=False)
+            ms, nl = C.c_double(), C.c_int()
+            lib.txb_profile_end(C.byref(ms), C.byref(nl))
+            print(json.dumps({"kernel": tag.decode(), "ms": ms.value / max(nl.value, 1), "launches": nl.value}))
+        t, tm = timeit(lambda: K.sampler_resample(rng, x, u, nrep, order, sync_rng=False, buckets=False), warm=2, rep=3)
+        print(json.dumps({"sampler_gather": [n, order, nrep], "ms": t * 1e3, "draws_per_s": nrep * n / t}))
         t, tm = timeit(lambda: K.sampler_indices(rng, nrep, n), warm=1, rep=3)
         print(json.dumps({"sampler_fill": [n, nrep], "ms": t * 1e3, "draws_per_s": nrep * n / t, "GBs": 8 * nrep * n / t / 1e9}))
         t, tm = timeit(lambda: K.sampler_freq(rng, nrep, n, dtype=torch.uint8), warm=1, rep=3)
