@@ -61,7 +61,7 @@ def to_device(arr: np.ndarray):
         t = t.pin_memory()
     t = t.to(dev, non_blocking=True)
     try:
-        base = arr if arr.base is None else arr
+        base = arr if arr.base is None else arr.base  # the owner outlives temporary views of it
         ref = weakref.ref(base, lambda _r, k=key, c=_dev_cache: c.pop(k, None))
         _dev_cache[key] = (ref, t)
     except TypeError:
@@ -150,6 +150,15 @@ class IndexSampler:
         if self._indices is None and self._freq is None:
             return self._plan.nrep
         return (self._indices if self._indices is not None else self._freq).shape[0]
+
+    @property
+    def nsamp(self) -> int:
+        """Draws per replicate."""
+        if self._indices is not None:
+            return self._indices.shape[1]
+        if self._freq is not None:
+            return int(self._freq[0].sum())
+        return self._plan.nsamp
 
     def freq_device(self, narrow: bool = True):
         """Frequency table as a CUDA tensor (uint8 when it cannot overflow, else int32/int64)."""

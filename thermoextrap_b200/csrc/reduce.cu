@@ -122,13 +122,18 @@ __global__ void __launch_bounds__(256)
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     constexpr int UNR = 4;
     if (VEC == 2) {
-        for (; i + (UNR - 1) * stride < nvec; i += UNR * stride) {
+        // block-contiguous tiles (UNR * 256 double2 = 16 KB per array), grid-strided: neighbouring
+        // blocks stream neighbouring DRAM pages
+        constexpr int TILE = UNR * 256;
+        const int64_t ntile = nvec / TILE;
+        for (int64_t t = blockIdx.x; t < ntile; t += gridDim.x) {
+            const int64_t base = t * TILE + threadIdx.x;
             double2 xv[UNR], uv[UNR], wv[UNR];
 #pragma unroll
             for (int q = 0; q < UNR; ++q) {
-                uv[q] = ldg_stream2(u + 2 * (i + q * stride));
-                if (HAS_X) xv[q] = ldg_stream2(x + 2 * (i + q * stride));
-                if (HAS_W) wv[q] = ldg_stream2(w + 2 * (i + q * stride));
+                uv[q] = ldg_stream2(u + 2 * (base + q * 256));
+                if (HAS_X) xv[q] = ldg_stream2(x + 2 * (base + q * 256));
+                if (HAS_W) wv[q] = ldg_stream2(w + 2 * (base + q * 256));
             }
 #pragma unroll
             for (int q = 0; q < UNR; ++q) {
@@ -136,7 +141,7 @@ __global__ void __launch_bounds__(256)
                 body(HAS_X ? xv[q].y : 0.0, uv[q].y, HAS_W ? wv[q].y : 1.0);
             }
         }
-        for (; i < nvec; i += stride) {
+        for (i = ntile * TILE + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
             const double2 uv = ldg_stream2(u + 2 * i);
             double2 xv = make_double2(0, 0), wv = make_double2(1, 1);
             if (HAS_X) xv = ldg_stream2(x + 2 * i);

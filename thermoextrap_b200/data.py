@@ -166,11 +166,12 @@ class _LazyGather:
     kernels and the gathered samples are built on demand.
     """
 
-    def __init__(self, base: DataArray, indices: np.ndarray, rec_dim: str, rep_dim: str) -> None:
-        self.base, self.indices, self.rec_dim, self.rep_dim = base, indices, rec_dim, rep_dim
+    def __init__(self, base: DataArray, sampler, rec_dim: str, rep_dim: str) -> None:
+        self.base, self.sampler, self.rec_dim, self.rep_dim = base, sampler, rec_dim, rep_dim
 
     def compute(self) -> DataArray:
-        idx = DataArray(self.indices, dims=(self.rep_dim, self.rec_dim))
+        # only here is the sampler's index table itself needed (a device-side plan stays a plan until now)
+        idx = DataArray(self.sampler.indices, dims=(self.rep_dim, self.rec_dim))
         return self.base.isel({self.rec_dim: idx})
 
 
@@ -234,16 +235,15 @@ class DataValuesBase(AbstractData):
             msg = "object is already resampled"
             raise ValueError(msg)
         sampler = cm.factory_sampler(sampler, data=self._xv, dim=self.rec_dim)
-        indices = sampler.indices
-        if indices.shape[1] != len(self):
-            msg = f"indices.sizes[{self.rec_dim}]={indices.shape[1]} must equal {len(self)=}"
+        if sampler.nsamp != len(self):
+            msg = f"indices.sizes[{self.rec_dim}]={sampler.nsamp} must equal {len(self)=}"
             raise ValueError(msg)
         meta = self.meta.resample(
             data=self, meta_kws={} if meta_kws is None else meta_kws, sampler=sampler, rep_dim=rep_dim
         )
         return type(self)(
-            uv=_LazyGather(self._uv, indices, self.rec_dim, rep_dim),
-            xv=_LazyGather(self._xv, indices, self.rec_dim, rep_dim),
+            uv=_LazyGather(self._uv, sampler, self.rec_dim, rep_dim),
+            xv=_LazyGather(self._xv, sampler, self.rec_dim, rep_dim),
             order=self.order, rec_dim=self.rec_dim, umom_dim=self.umom_dim, deriv_dim=self.deriv_dim,
             meta=meta, x_is_u=self.x_is_u, boot=(self, sampler, rep_dim),
         )
