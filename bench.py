@@ -185,6 +185,7 @@ def run_b200(a) -> None:
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
+    clocks = ClockSampler(local) if rank == 0 else None
 
     # replicates are independent: rank r bootstraps its own nrep replicates of its own
     # sample set (weak scaling, no data-path collective)
@@ -209,7 +210,11 @@ def run_b200(a) -> None:
         step_device()
     barrier()
 
-    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks is not None:  # NVML start-up perturbs the GPU: wait until samples are flowing
+        t_wait = time.perf_counter()
+        while not clocks.rows and time.perf_counter() - t_wait < 5.0:
+            time.sleep(0.05)
+        clocks.rows.clear()
     launches0 = K.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
