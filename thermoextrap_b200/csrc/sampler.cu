@@ -48,7 +48,6 @@ struct SamplerArgs {
     int64_t steps_per_block;      // multiple of 512 * SMP_T (both thread geometries tile it)
     Affine iter_jump;             // (SMP_THREADS - 1) * SMP_T steps
     Affine iter_jump2;            // (BK_THREADS - 1) * SMP_T steps (512-thread kernels)
-    Affine step_k[SMP_T];         // k + 1 steps: the SMP_T states of an iteration, independently from the first
     Affine pow2[SMP_NPOW];        // 2^i steps
 };
 
@@ -78,22 +77,6 @@ __device__ __forceinline__ uint64_t pcg_out(uint64_t hi, uint64_t lo) {
     const uint64_t x = hi ^ lo;
     const unsigned rot = (unsigned)(hi >> 58);
     return (x >> rot) | (x << ((64u - rot) & 63u));
-}
-
-// the SMP_T outputs of one thread-iteration, each state computed independently from the current
-// one (instruction-level parallelism instead of a serial multiply chain); advances (hi, lo) by SMP_T
-__device__ __forceinline__ void pcg_block_out(uint64_t& hi, uint64_t& lo, const SamplerArgs& a,
-                                              uint64_t (&out)[SMP_T]) {
-    uint64_t h_last = hi, l_last = lo;
-#pragma unroll
-    for (int k = 0; k < SMP_T; ++k) {
-        uint64_t h = hi, l = lo;
-        affine_apply(h, l, a.step_k[k]);
-        out[k] = pcg_out(h, l);
-        if (k == SMP_T - 1) h_last = h, l_last = l;
-    }
-    hi = h_last;
-    lo = l_last;
 }
 
 // exclusive block scan of one int per thread (256 threads); returns the block total in `total`
@@ -414,11 +397,9 @@ __global__ void __launch_bounds__(512, 2)
     long long total = 0;
     for (int64_t it = 0; it < niter; ++it) {
         int c = 0;
-        uint64_t outs[T];
-        pcg_block_out(hi, lo, a, outs);
 #pragma unroll
         for (int k = 0; k < T; ++k) {
-            const uint64_t o = outs[k];
+            const uint64_t o = pcg_step_out(hi, lo, a.inc_hi, a.inc_lo);
             c += (uint32_t)((uint64_t)(uint32_t)o * n) >= thresh ? 1 : 0;
             c += (uint32_t)((o >> 32) * (uint64_t)n) >= thresh ? 1 : 0;
         }
@@ -549,10 +530,6 @@ int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, 
     a.iter_jump = mk_affine(ja, jc);
     lcg_jump(inc, (uint64_t)(BK_THREADS - 1) * SMP_T, ja, jc);
     a.iter_jump2 = mk_affine(ja, jc);
-    for (int k = 0; k < SMP_T; ++k) {
-        lcg_jump(inc, (uint64_t)(k + 1), ja, jc);
-        a.step_k[k] = mk_affine(ja, jc);
-    }
     u128 ca = mk128(PCG_MULT_HI, PCG_MULT_LO), cc = inc;
     for (int i = 0; i < SMP_NPOW; ++i) {
         a.pow2[i] = mk_affine(ca, cc);
@@ -848,11 +825,21 @@ BucketPlan bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp, int64_t nrep_
     BucketPlan b{};
     b.nb = (int)((ndat + BK_SIZE - 1) / BK_SIZE);
     b.m = ndat <= BK_SIZE ? (double)nsamp : (double)nsamp * BK_SIZE / (double)ndat;
-    // ring: 31 pending + one iteration's arrivals (Poisson, mean 8192 / nb) with a 6 sigma margin
+    // ring: up to 31 pending entries + one iteration's arrivals (Poisson, mean 8192 / nb).  The fast
+    // append wraps (and flags the call for a redo on the gather path) when arrivals > cap - pending:
+    // choose the power of two that makes this a < 1e-12 event per bucket and iteration.
     const double arrivals = (double)(BK_THREADS * 2 * SMP_T) / b.nb;
     b.cap = BK_MINCAP;
-    while (b.cap < 32.0 + arrivals + 6.0 * sqrt(arrivals)) b.cap *= 2;
-    // worth it only for tables too big for L2-resident gathers, with mostly full lines
+    for (;; b.cap *= 2) {
+        double term = exp(-arrivals), cdf = 0.0;  // P(X <= cap - 31)
+        for (int k = 0; k <= b.cap - 31; ++k) {
+            cdf += term;
+            term *= arrivals / (k + 1);
+        }
+        if (1.0 - cdf < 1e-12 || b.cap >= 4096) break;
+    }
+    // worth it only for tables too big for L2-resident gathers, with mostly full lines, and when the
+    // rings fit in shared memory (a window of bucket counts around 800-1170 does not: gather path)
     b.ok = ndat >= (int64_t)4 << 20 && b.nb <= BK_MAXNB && b.m >= 8.0 * BK_LINE &&
            (size_t)b.nb * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
     b.fixed_bytes = p.head_bytes + 256 + sizeof(double2) * (size_t)ndat +

@@ -182,11 +182,9 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         const int total = e.iter_count[j];
         uint32_t val[NSLOT];
         uint32_t mask = 0;
-        uint64_t outs[T];
-        pcg_block_out(hi, lo, a, outs);
 #pragma unroll
         for (int k = 0; k < T; ++k) {
-            const uint64_t o = outs[k];
+            const uint64_t o = pcg_step_out(hi, lo, a.inc_hi, a.inc_lo);
             const uint64_t m0 = (uint64_t)(uint32_t)o * n;
             const uint64_t m1 = (o >> 32) * (uint64_t)n;
             val[2 * k] = (uint32_t)(m0 >> 32);
