@@ -42,7 +42,7 @@ BETA0, BETAS = 1.0, [0.9, 0.95, 1.05, 1.1]
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nsamp", type=int, default=NSAMP, help=argparse.SUPPRESS)
@@ -122,47 +122,55 @@ def run_reference(a) -> None:
 
 # --------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed region (NVML in a thread: the same counters
+    `nvidia-smi --query-gpu=clocks.sm,clocks_event_reasons.*` prints, without a second process)."""
 
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index: int) -> None:
-        self.rows: list[list[str]] = []
-        self.proc = None
+    def __init__(self, index: int, period: float = 0.2) -> None:
+        self.rows: list[tuple[int, int]] = []
+        self.ok = False
+        self._stop = threading.Event()
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
-            )
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except OSError:
-            self.proc = None
+            import pynvml
 
-    def _read(self) -> None:
-        for ln in self.proc.stdout:
-            self.rows.append([c.strip() for c in ln.split(",")])
+            pynvml.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [v for v in vis.split(",") if v.strip().isdigit()]
+            phys = int(ids[index]) if index < len(ids) else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as exc:  # noqa: BLE001
+            self.err = repr(exc)
+            return
+        self.period = period
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def _run(self) -> None:
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                why = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((mhz, why))
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(self.period)
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"NVML unavailable: {self.err}"]}
+        self._stop.set()
         self.thread.join(timeout=2)
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for nm, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        sm = [r[0] for r in self.rows]
+        reasons = sorted({name for _, why in self.rows for bit, name in self.REASONS.items() if why & bit})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+                "reasons": reasons}
 
 
 # --------------------------------------------------------------------------- B200 arm
@@ -265,10 +273,15 @@ def run_b200(a) -> None:
     barrier()
     backend.transfer_bytes.update(h2d=0, d2h=0)
     t0 = time.perf_counter()
+    e2e_steps = []
     for _ in range(a.steps):
+        ts = time.perf_counter()
         pred, pred_boot = step_e2e()
+        e2e_steps.append(time.perf_counter() - ts)
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
+    if rank == 0:
+        print("e2e ms per step: " + " ".join(f"{1e3 * t:.1f}" for t in e2e_steps), file=sys.stderr)
     h2d, d2h = backend.transfer_bytes["h2d"], backend.transfer_bytes["d2h"]
     clock_info = clocks.stop() if clocks else None
     assert pred_boot.shape[:2] == (len(BETAS), a.nrep) and np.isfinite(pred_boot).all()

@@ -189,7 +189,8 @@ int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t n
  * are processed in as many windows as needed) draws are first partitioned by sample bucket and
  * consumed from shared memory (sampler_bucket.cuh), which is ~2.5x faster on tables beyond L2.
  * *status |= 8 if a bucket list overflowed its > 10 sigma capacity, |= 16 if a shared-memory ring
- * wrapped (> 6 sigma); neither has been observed: rerun with NO_BUCKETS.                    */
+ * wrapped (< 1e-12 per bucket and iteration): rerun with NO_BUCKETS.  |= 32 (informational) when
+ * the bucketed path ran.                                                                   */
 enum { TXB_SAMPLER_PREPARED = 1, TXB_SAMPLER_NO_BUCKETS = 2 };
 size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t nsamp,
                                             int64_t nrep_out);

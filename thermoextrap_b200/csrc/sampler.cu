@@ -455,6 +455,8 @@ __global__ void k_sampler_scan(const int64_t* __restrict__ cnt, int64_t* __restr
     if (run < count && status) atomicOr(status, 4);
 }
 
+__global__ void k_status_or(int* status, int bits) { atomicOr(status, bits); }
+
 }  // namespace txb
 
 #include "sampler_bucket.cuh"
@@ -1015,7 +1017,12 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             if (rc == TXB_OK && x) rc = launch_sum_parts(ws1, bp.nb, nw * (ks + 1), S1 + (r0 - rep_lo) * (ks + 1), st);
             if (rc != TXB_OK) return rc;
         }
-        return txb_finalize_f64(S0, S1, pivot, nwin, 1, 1, order, mode, out, stream);
+        rc = txb_finalize_f64(S0, S1, pivot, nwin, 1, 1, order, mode, out, stream);
+        if (rc == TXB_OK && status) {  // tell the caller which path ran (bit 32)
+            k_status_or<<<1, 1, 0, st>>>(status, 32);
+            TXB_CUDA_LAUNCH_CHECK("k_status_or");
+        }
+        return rc;
     }
 
     // ---- gather path

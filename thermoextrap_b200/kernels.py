@@ -119,7 +119,7 @@ def reduce_vals(x, u, order: int, w=None, x_is_u: bool = False) -> torch.Tensor:
             out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_reduce_vals_f64")
-    launch_count += 1
+    launch_count += 6  # pivot x2, sums, sum_parts x2, finalize (scalar x; wide x adds one u-only sum)
     return out.reshape(*val_shape, 2, order + 1)
 
 
@@ -488,8 +488,11 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
             None, status.data_ptr(), flags, ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_sampler_resample_f64")
-    launch_count += 5 if prepared else 8
-    if buckets and int(status.item()) & 24:  # a bucket list / ring overflowed its margin: redo by gathering
+    flag = int(status.item())
+    # kernels launched: pivot x2, pack, [count, scan, iter_scan, locate], then
+    # gather + finalize, or scatter + consume + sum_parts x2 + finalize + status note (per window)
+    launch_count += 3 + (0 if prepared else 4) + (6 if flag & 32 else 2)
+    if buckets and flag & 24:  # a bucket list / ring overflowed its margin: redo by gathering
         return sampler_resample(src if plan is None else plan, x, u, nrep, order, w=w, x_is_u=x_is_u, nsamp=nsamp,
                                 sync_rng=False, reps=reps, buckets=False)
     return out.reshape(hi - lo, *val_shape, 2, order + 1)
