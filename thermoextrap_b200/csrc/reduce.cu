@@ -9,7 +9,10 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "txb_common.cuh"
+#include "reduce_tma.cuh"
 
 namespace txb {
 
@@ -446,6 +449,114 @@ static int launch_scalar(const double* x, const double* u, const double* w, int6
     return rc;
 }
 
+// Ring geometry of the bulk-copy kernel: tiles of (256 / lanes_c) * WT_UNR rows x lanes_c * cpt
+// channels; as many stages as fit ~100 KB so that two CTAs share an SM.
+struct TmaPlan {
+    bool ok;
+    bool use_map;
+    int cpt, lanes_c, nstage;
+    int64_t nctiles, nslabs;
+    size_t smem;
+};
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                      CUtensorMapFloatOOBfill);
+static TensorMapEncodeFn tensor_map_encoder() {
+    static TensorMapEncodeFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (TensorMapEncodeFn)p;
+        cudaGetLastError();
+    }
+    return fn;
+}
+
+static int wide_tma_mode() {
+    // TXB_WIDE_TMA: 0 = register-staged kernel only, 1 (default) = bulk-copy ring for contiguous tiles,
+    // 2 = also tensor-map tiles for strided rows (measured no faster than the register-staged kernel)
+    const char* e = getenv("TXB_WIDE_TMA");
+    return e ? atoi(e) : 1;
+}
+
+// contig: every tile is one contiguous run (single channel tile, rows packed) -> 1-D bulk copies;
+// otherwise the rows are strided and the tile comes through a tensor map.
+static TmaPlan plan_wide_tma(int64_t nsamp, int64_t nchan, int cpt, int narr, bool contig) {
+    TmaPlan t{};
+    if (cpt < 2 || !wide_tma_mode()) return t;
+    const WidePlan p = plan_wide(nsamp, nchan, cpt);
+    t.cpt = cpt;
+    t.lanes_c = p.lanes_c;
+    t.nctiles = p.nctiles;
+    const int R = (256 / p.lanes_c) * WT_UNR;
+    t.use_map = !contig;
+    if (t.use_map && (wide_tma_mode() < 2 || R > 256 || nsamp >= (int64_t)1 << 31 || !tensor_map_encoder())) return t;
+    const size_t stage = (size_t)R * p.lanes_c * cpt * sizeof(double) * narr;
+    int ns = (int)((100u << 10) / stage);
+    if (ns > WT_MAXSTAGE) ns = WT_MAXSTAGE;
+    if (ns < 2) return t;
+    t.nstage = ns;
+    t.smem = stage * ns;
+    int64_t nslabs = ((int64_t)sm_count() * 2 + p.nctiles - 1) / p.nctiles;
+    const int64_t max_slabs = nsamp / ((int64_t)R * 2);  // at least two tiles per CTA
+    if (nslabs > max_slabs) nslabs = max_slabs;
+    if (nslabs < 1 || nslabs > p.nslabs) return t;  // tiny inputs / workspace sized by plan_wide
+    t.nslabs = nslabs;
+    t.ok = true;
+    return t;
+}
+
+static CUtensorMapL2promotion l2_promotion() {
+    const char* e = getenv("TXB_TMAP_L2");
+    return e ? (CUtensorMapL2promotion)atoi(e) : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+}
+
+// [nsamp, nchan] fp64 matrix with row pitch ld, boxes of R rows x W channels
+static bool make_tensor_map(CUtensorMap* m, const double* a, int64_t nsamp, int64_t nchan, int64_t ld,
+                            int R, int W) {
+    const cuuint64_t dims[2] = {(cuuint64_t)nchan, (cuuint64_t)nsamp};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(double)};
+    const cuuint32_t box[2] = {(cuuint32_t)W, (cuuint32_t)R};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = tensor_map_encoder()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a), dims,
+                                            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                            CU_TENSOR_MAP_SWIZZLE_NONE, l2_promotion(),
+                                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) set_error("cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return r == CUDA_SUCCESS;
+}
+
+template <int K, int CPT, bool HAS_X, bool UPC>
+static int launch_wide_tma_k(const TmaPlan& t, const double* x, const double* u, const double* w,
+                             int64_t nsamp, int64_t nchan, int64_t ldx, int64_t ldu,
+                             const double* pivot, double* ws0, double* ws1, cudaStream_t st) {
+    auto kern = k_reduce_wide_tma<K, CPT, HAS_X, UPC>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 << 10) != cudaSuccess) {
+            TXB_CUDA_LAUNCH_CHECK("k_reduce_wide_tma attribute");
+        }
+        attr_set = true;
+    }
+    CUtensorMap mx{}, mu{};
+    if (t.use_map) {
+        const int R = (256 / t.lanes_c) * WT_UNR, W = t.lanes_c * CPT;
+        if (HAS_X && !make_tensor_map(&mx, x, nsamp, nchan, ldx, R, W)) return TXB_ERR_CUDA;
+        if (UPC && !make_tensor_map(&mu, u, nsamp, nchan, ldu, R, W)) return TXB_ERR_CUDA;
+    }
+    const dim3 grid((unsigned)t.nctiles, (unsigned)t.nslabs);
+    kern<<<grid, 256, t.smem, st>>>(x, u, w, nsamp, nchan, ldx, ldu, pivot, t.lanes_c, t.nstage, ws0, ws1,
+                                    t.use_map ? 1 : 0, mx, mu);
+    return TXB_OK;
+}
+
 template <int K, bool HAS_X, bool UPC>
 static int launch_wide(const double* x, const double* u, const double* w, int64_t nsamp,
                        int64_t nchan, int64_t ldx, int64_t ldu, const double* pivot, double* S0,
@@ -455,13 +566,25 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     const bool ua = !UPC || (aligned16(u) && ldu % 2 == 0);
     if (xa && ua && nchan % 2 == 0) cpt = 2;
     if (cpt == 2 && nchan % 4 == 0 && !(HAS_X && UPC)) cpt = 4;
+    constexpr int NARR = (HAS_X ? 1 : 0) + (UPC ? 1 : 0);
+    const int wtile = plan_wide(nsamp, nchan, cpt).lanes_c * cpt;
+    const bool contig = nchan == wtile && (!HAS_X || ldx == nchan) && (!UPC || ldu == nchan);
+    const TmaPlan t = plan_wide_tma(nsamp, nchan, cpt, NARR, contig);
     const WidePlan p = plan_wide(nsamp, nchan, cpt);
+    const int64_t nslabs = t.ok ? t.nslabs : p.nslabs;
     double* ws0 = ws;
-    double* ws1 = ws + (UPC ? p.nslabs * nchan * (K + 1) : 0);
+    double* ws1 = ws + (UPC ? nslabs * nchan * (K + 1) : 0);
     const dim3 grid((unsigned)p.nctiles, (unsigned)p.nslabs);
     {
     ProfScope prof("reduce", st);
-    if (cpt == 4)
+    if (t.ok) {
+        int rc;
+        if (cpt == 4)
+            rc = launch_wide_tma_k<K, (HAS_X && UPC) ? 2 : 4, HAS_X, UPC>(t, x, u, w, nsamp, nchan, ldx, ldu, pivot, ws0, ws1, st);
+        else
+            rc = launch_wide_tma_k<K, 2, HAS_X, UPC>(t, x, u, w, nsamp, nchan, ldx, ldu, pivot, ws0, ws1, st);
+        if (rc != TXB_OK) return rc;
+    } else if (cpt == 4)
         k_reduce_wide<K, (HAS_X && UPC) ? 2 : 4, HAS_X, UPC>
             <<<grid, 256, 0, st>>>(x, u, w, nsamp, nchan, ldx, ldu, pivot, p.lanes_c, ws0, ws1);
     else if (cpt == 2)
@@ -473,8 +596,8 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     }
     TXB_CUDA_LAUNCH_CHECK("k_reduce_wide");
     int rc = TXB_OK;
-    if (UPC) rc = launch_sum_parts(ws0, p.nslabs, nchan * (K + 1), S0, st);
-    if (rc == TXB_OK && HAS_X) rc = launch_sum_parts(ws1, p.nslabs, nchan * (K + 1), S1, st);
+    if (UPC) rc = launch_sum_parts(ws0, nslabs, nchan * (K + 1), S0, st);
+    if (rc == TXB_OK && HAS_X) rc = launch_sum_parts(ws1, nslabs, nchan * (K + 1), S1, st);
     return rc;
 }
 

@@ -61,6 +61,40 @@ def reduce():
     print(json.dumps({"reduce_x_is_u": [n, nv, order], "ms": t * 1e3, "GBs": 8 * n * nv / t / 1e9}))
 
 
+def sys_modes():
+    import os
+    return os.environ.get("KB_MODES", "0,1").split(",")
+
+
+def reduce_wide():
+    """A/B of the register-staged and the bulk-copy (TMA ring) wide kernels, kernel time from the profile hook."""
+    import os
+    lib = _lib.load()
+    cases = [(4_000_000, 64, 6, False), (16_000_000, 64, 6, False), (400_000, 2000, 4, False), (16_000_000, 16, 6, False),
+             (2_000_000, 130, 6, False), (400_000, 2000, 4, True), (4_000_000, 64, 8, False), (2_000_000, 64, 6, "upc")]
+    for n, nv, order, kind in cases:
+        u = torch.randn((n, nv) if kind else (n,), dtype=torch.float64, device="cuda") * 5.3 + 175
+        x = None if kind is True else torch.randn((n, nv), dtype=torch.float64, device="cuda") * 0.02
+        byts = 8 * n * nv * (2 if kind == "upc" else 1) + (0 if kind else 8 * n)
+        row = {"reduce_wide": [n, nv, order, str(kind)]}
+        outs = {}
+        for mode in sys_modes():
+            os.environ["TXB_WIDE_TMA"] = mode[0]
+            os.environ["TXB_TMAP_L2"] = mode[1:] or "3"
+            fn = (lambda: K.reduce_vals(None, u, order, x_is_u=True)) if kind is True else (lambda: K.reduce_vals(x, u, order))
+            t, _ = timeit(fn)
+            lib.txb_profile_begin(b"reduce")
+            for _ in range(5):
+                outs[mode] = fn()
+            ms, nl = C.c_double(), C.c_int()
+            lib.txb_profile_end(C.byref(ms), C.byref(nl))
+            row["tma" + mode] = {"call_ms": t * 1e3, "kern_ms": ms.value / 5, "GBs": byts / (ms.value / 5 * 1e-3) / 1e9}
+        row["maxdiff"] = max(float((outs["0"] - o).abs().max()) for o in outs.values())
+        print(json.dumps(row), flush=True)
+        del x, u
+    os.environ.pop("TXB_WIDE_TMA", None)
+
+
 def reduce_big():
     for n, nv, order in [(1_000_000_000, 0, 8), (1_000_000_000, 0, 2), (50_000_000, 64, 6)]:
         u = torch.randn(n, dtype=torch.float64, device="cuda")
