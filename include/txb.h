@@ -246,7 +246,8 @@ int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* 
 
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",
- * "sampler_count", "sampler_gather") is bracketed by CUDA events on its own stream;
+ * "sampler_count", "sampler_gather"; "reduce_ring" = only the copy-engine-staged reduce
+ * kernels, which is how the tests check which kernel ran) is bracketed by CUDA events on its own stream;
  * txb_profile_end synchronises on them and returns the summed duration and the number of
  * launches.  No effect on results; not thread safe (measurement only).            */
 int txb_profile_begin(const char* tag);

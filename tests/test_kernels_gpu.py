@@ -87,6 +87,92 @@ def test_reduce_vals_fixture_uniform(K):
         np.testing.assert_allclose(raw[:, 1, i], np.average(x * u[:, None] ** i, axis=0), rtol=1e-12)
 
 
+# ------------------------------------------------------------------ K1, copy-engine ring kernels
+def ring_launches(fn):
+    """Run fn; return (result, number of cp.async.bulk-staged reduce kernels it launched)."""
+    import ctypes as C
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    lib.txb_profile_begin(b"reduce_ring")
+    out = fn()
+    ms, nl = C.c_double(), C.c_int()
+    lib.txb_profile_end(C.byref(ms), C.byref(nl))
+    return out, nl.value
+
+
+# shapes large enough that the ring path is taken (reduce_wide_tma.cu:plan_wide_ring): 256-thread whole-row
+# tiles (<= 128 channels), 512-thread tiles (<= 2048 channels, lane counts that are not powers of two),
+# two channels per thread at order >= 10, ragged last tiles
+@pytest.mark.parametrize("n,nv,order", [(20_001, 64, 6), (3001, 2000, 4), (6000, 130, 6), (40_003, 16, 8),
+                                        (9000, 500, 12), (330_000, 2, 3), (5000, 1022, 5), (12_345, 36, 10)])
+def test_reduce_vals_wide_ring(K, n, nv, order):
+    x, u, _ = make(n, nv, seed=11)
+    out, nring = ring_launches(lambda: K.reduce_vals(x, u, order))
+    assert nring == 1
+    ref = oc.comoments_two_pass(x, u, order)
+    assert relerr(out.cpu().numpy(), ref, oc.tolerance_scale(x, u, order)) < TOL
+
+
+def test_reduce_vals_wide_ring_weighted_strided_upc(K):
+    import torch
+
+    x, u, rng = make(20_000, 64, seed=12)
+    w = rng.random(20_000)
+    w[::5] = 0.0
+    ref = oc.comoments_two_pass(x, u, 6, w=w)
+    scale = oc.tolerance_scale(x, u, 6)
+    out, nring = ring_launches(lambda: K.reduce_vals(x, u, 6, w=w))
+    assert nring == 1 and relerr(out.cpu().numpy(), ref, scale) < TOL
+    # rows with padding, straight through the C ABI (the Python layer always packs): ld = 72 is streamed
+    # by whole-row copies that carry the padding along, ld = 128 stays on the register-staged kernel
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    ud, wd = torch.from_numpy(u).cuda(), torch.from_numpy(w).cuda()
+    for ld, expect in [(72, 1), (128, 0)]:
+        buf = torch.full((20_000, ld), float("nan"), dtype=torch.float64, device="cuda")
+        buf[:, :64] = torch.from_numpy(x).cuda()
+        outd = torch.empty((64, 2, 7), dtype=torch.float64, device="cuda")
+        nb = lib.txb_reduce_workspace_bytes(20_000, 64, 6)
+        ws = torch.empty(nb, dtype=torch.uint8, device="cuda")
+
+        def call():
+            _lib.check(lib.txb_reduce_vals_f64(buf.data_ptr(), ud.data_ptr(), wd.data_ptr(), 20_000, 64, ld, 0, 6, 0,
+                                               outd.data_ptr(), ws.data_ptr(), nb, None), "txb_reduce_vals_f64")
+            torch.cuda.synchronize()
+            return outd
+
+        out, nring = ring_launches(call)
+        assert nring == expect and relerr(out.cpu().numpy(), ref, scale) < TOL
+    # one energy per channel (both arrays wide) and x_is_u wide
+    uu = u[:, None] + rng.normal(0, 1.0, x.shape)
+    out, nring = ring_launches(lambda: K.reduce_vals(x, uu, 5))
+    assert nring == 1
+    assert relerr(out.cpu().numpy(), oc.comoments_two_pass(x, uu, 5), oc.tolerance_scale(x, uu, 5)) < TOL
+    uw = np.ascontiguousarray(np.tile(uu[:8000], (1, 4))[:, :200]) + rng.normal(0, 0.5, (8000, 200))
+    out, nring = ring_launches(lambda: K.reduce_vals(None, uw, 4, x_is_u=True))
+    assert nring == 1
+    refu = oc.comoments_two_pass(uw, uw, 4)
+    assert relerr(out.cpu().numpy(), refu, oc.tolerance_scale(uw, uw, 4).reshape(refu.shape)) < TOL
+
+
+@pytest.mark.parametrize("order,weighted", [(8, False), (9, True), (11, False)])
+def test_reduce_vals_scalar_ring(K, order, weighted):
+    n = 2_500_003  # ragged: 1220 full tiles of 2048 + 1443 samples
+    x, u, rng = make(n, 0, seed=13)
+    w = rng.random(n) if weighted else None
+    out, nring = ring_launches(lambda: K.reduce_vals(x, u, order, w=w))
+    assert nring == 1
+    ref = oc.comoments_two_pass(x, u, order, w=w)
+    assert relerr(out.cpu().numpy(), ref, oc.tolerance_scale(x, u, order)) < TOL
+    out, nring = ring_launches(lambda: K.reduce_vals(None, u, order, w=w, x_is_u=True))
+    assert nring == 1
+    refu = oc.comoments_two_pass(u, u, order, w=w).reshape(out.shape)
+    assert relerr(out.cpu().numpy(), refu, oc.tolerance_scale(u, u, order).reshape(out.shape)) < TOL
+
+
 @pytest.mark.parametrize("n,nv", [(5000, 0), (2000, 40), (999, 3)])
 @pytest.mark.parametrize("order", [1, 4, 9])
 def test_reduce_vals_x_is_u(K, n, nv, order):

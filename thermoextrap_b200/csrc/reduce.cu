@@ -419,18 +419,27 @@ static int64_t max_wide_parts_x_chan(int64_t nsamp, int64_t nchan) {
         const WidePlan p = plan_wide(nsamp, nchan, cpt);
         if (p.nslabs * nchan > m) m = p.nslabs * nchan;
     }
-    return m;
+    // the ring kernel (reduce_wide_tma.cu) runs one slab per resident CTA: 2 per SM at 256 threads
+    // (<= 128 channels), 1 per SM at 512 threads
+    const int64_t ring = (int64_t)sm_count() * (nchan <= 128 ? 2 : 1) * nchan;
+    return m > ring ? m : ring;
 }
 
 // u-only / scalar-x sums -> S0[K+1] (and S1[K+1])
 template <int K>
 static int launch_scalar(const double* x, const double* u, const double* w, int64_t nsamp,
                          const double* pivot, double* S0, double* S1, double* ws, cudaStream_t st) {
-    const int64_t nb = scalar_blocks(nsamp);
+    const bool vec = aligned16(u) && (!x || aligned16(x)) && (!w || aligned16(w));
+    const int64_t nb_ring = vec ? scalar_tma_blocks(nsamp, scalar_blocks(nsamp), K) : 0;
+    const int64_t nb = nb_ring ? nb_ring : scalar_blocks(nsamp);
     double* ws0 = ws;
     double* ws1 = ws + nb * (K + 1);
-    const bool vec = aligned16(u) && (!x || aligned16(x)) && (!w || aligned16(w));
-    {
+    if (nb_ring) {
+        ProfScope prof("reduce", st);
+        ProfScope ring("reduce_ring", st);
+        const int rc = launch_scalar_tma(K, x, u, w, nsamp, pivot, nb, ws0, ws1, st);
+        if (rc != TXB_OK) return rc;
+    } else {
     ProfScope prof("reduce", st);
 #define TXB_LAUNCH_SC(HX, HW, V) \
     k_reduce_scalar<K, HX, HW, V><<<(unsigned)nb, 256, 0, st>>>(x, u, w, nsamp, pivot, ws0, ws1)
@@ -449,114 +458,6 @@ static int launch_scalar(const double* x, const double* u, const double* w, int6
     return rc;
 }
 
-// Ring geometry of the bulk-copy kernel: tiles of (256 / lanes_c) * WT_UNR rows x lanes_c * cpt
-// channels; as many stages as fit ~100 KB so that two CTAs share an SM.
-struct TmaPlan {
-    bool ok;
-    bool use_map;
-    int cpt, lanes_c, nstage;
-    int64_t nctiles, nslabs;
-    size_t smem;
-};
-
-// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
-typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                      CUtensorMapFloatOOBfill);
-static TensorMapEncodeFn tensor_map_encoder() {
-    static TensorMapEncodeFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = (TensorMapEncodeFn)p;
-        cudaGetLastError();
-    }
-    return fn;
-}
-
-static int wide_tma_mode() {
-    // TXB_WIDE_TMA: 0 = register-staged kernel only, 1 (default) = bulk-copy ring for contiguous tiles,
-    // 2 = also tensor-map tiles for strided rows (measured no faster than the register-staged kernel)
-    const char* e = getenv("TXB_WIDE_TMA");
-    return e ? atoi(e) : 1;
-}
-
-// contig: every tile is one contiguous run (single channel tile, rows packed) -> 1-D bulk copies;
-// otherwise the rows are strided and the tile comes through a tensor map.
-static TmaPlan plan_wide_tma(int64_t nsamp, int64_t nchan, int cpt, int narr, bool contig) {
-    TmaPlan t{};
-    if (cpt < 2 || !wide_tma_mode()) return t;
-    const WidePlan p = plan_wide(nsamp, nchan, cpt);
-    t.cpt = cpt;
-    t.lanes_c = p.lanes_c;
-    t.nctiles = p.nctiles;
-    const int R = (256 / p.lanes_c) * WT_UNR;
-    t.use_map = !contig;
-    if (t.use_map && (wide_tma_mode() < 2 || R > 256 || nsamp >= (int64_t)1 << 31 || !tensor_map_encoder())) return t;
-    const size_t stage = (size_t)R * p.lanes_c * cpt * sizeof(double) * narr;
-    int ns = (int)((100u << 10) / stage);
-    if (ns > WT_MAXSTAGE) ns = WT_MAXSTAGE;
-    if (ns < 2) return t;
-    t.nstage = ns;
-    t.smem = stage * ns;
-    int64_t nslabs = ((int64_t)sm_count() * 2 + p.nctiles - 1) / p.nctiles;
-    const int64_t max_slabs = nsamp / ((int64_t)R * 2);  // at least two tiles per CTA
-    if (nslabs > max_slabs) nslabs = max_slabs;
-    if (nslabs < 1 || nslabs > p.nslabs) return t;  // tiny inputs / workspace sized by plan_wide
-    t.nslabs = nslabs;
-    t.ok = true;
-    return t;
-}
-
-static CUtensorMapL2promotion l2_promotion() {
-    const char* e = getenv("TXB_TMAP_L2");
-    return e ? (CUtensorMapL2promotion)atoi(e) : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
-}
-
-// [nsamp, nchan] fp64 matrix with row pitch ld, boxes of R rows x W channels
-static bool make_tensor_map(CUtensorMap* m, const double* a, int64_t nsamp, int64_t nchan, int64_t ld,
-                            int R, int W) {
-    const cuuint64_t dims[2] = {(cuuint64_t)nchan, (cuuint64_t)nsamp};
-    const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(double)};
-    const cuuint32_t box[2] = {(cuuint32_t)W, (cuuint32_t)R};
-    const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = tensor_map_encoder()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(a), dims,
-                                            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                            CU_TENSOR_MAP_SWIZZLE_NONE, l2_promotion(),
-                                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) set_error("cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return r == CUDA_SUCCESS;
-}
-
-template <int K, int CPT, bool HAS_X, bool UPC>
-static int launch_wide_tma_k(const TmaPlan& t, const double* x, const double* u, const double* w,
-                             int64_t nsamp, int64_t nchan, int64_t ldx, int64_t ldu,
-                             const double* pivot, double* ws0, double* ws1, cudaStream_t st) {
-    auto kern = k_reduce_wide_tma<K, CPT, HAS_X, UPC>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 << 10) != cudaSuccess) {
-            TXB_CUDA_LAUNCH_CHECK("k_reduce_wide_tma attribute");
-        }
-        attr_set = true;
-    }
-    CUtensorMap mx{}, mu{};
-    if (t.use_map) {
-        const int R = (256 / t.lanes_c) * WT_UNR, W = t.lanes_c * CPT;
-        if (HAS_X && !make_tensor_map(&mx, x, nsamp, nchan, ldx, R, W)) return TXB_ERR_CUDA;
-        if (UPC && !make_tensor_map(&mu, u, nsamp, nchan, ldu, R, W)) return TXB_ERR_CUDA;
-    }
-    const dim3 grid((unsigned)t.nctiles, (unsigned)t.nslabs);
-    kern<<<grid, 256, t.smem, st>>>(x, u, w, nsamp, nchan, ldx, ldu, pivot, t.lanes_c, t.nstage, ws0, ws1,
-                                    t.use_map ? 1 : 0, mx, mu);
-    return TXB_OK;
-}
-
 template <int K, bool HAS_X, bool UPC>
 static int launch_wide(const double* x, const double* u, const double* w, int64_t nsamp,
                        int64_t nchan, int64_t ldx, int64_t ldu, const double* pivot, double* S0,
@@ -566,10 +467,9 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     const bool ua = !UPC || (aligned16(u) && ldu % 2 == 0);
     if (xa && ua && nchan % 2 == 0) cpt = 2;
     if (cpt == 2 && nchan % 4 == 0 && !(HAS_X && UPC)) cpt = 4;
-    constexpr int NARR = (HAS_X ? 1 : 0) + (UPC ? 1 : 0);
-    const int wtile = plan_wide(nsamp, nchan, cpt).lanes_c * cpt;
-    const bool contig = nchan == wtile && (!HAS_X || ldx == nchan) && (!UPC || ldu == nchan);
-    const TmaPlan t = plan_wide_tma(nsamp, nchan, cpt, NARR, contig);
+    // copy-engine ring wherever it applies (reduce_wide_tma.cu), else register-staged loads
+    const WideRingPlan t = plan_wide_ring(nsamp, nchan, ldx, ldu, K, HAS_X, UPC, xa && ua,
+                                          max_wide_parts_x_chan(nsamp, nchan));
     const WidePlan p = plan_wide(nsamp, nchan, cpt);
     const int64_t nslabs = t.ok ? t.nslabs : p.nslabs;
     double* ws0 = ws;
@@ -578,11 +478,8 @@ static int launch_wide(const double* x, const double* u, const double* w, int64_
     {
     ProfScope prof("reduce", st);
     if (t.ok) {
-        int rc;
-        if (cpt == 4)
-            rc = launch_wide_tma_k<K, (HAS_X && UPC) ? 2 : 4, HAS_X, UPC>(t, x, u, w, nsamp, nchan, ldx, ldu, pivot, ws0, ws1, st);
-        else
-            rc = launch_wide_tma_k<K, 2, HAS_X, UPC>(t, x, u, w, nsamp, nchan, ldx, ldu, pivot, ws0, ws1, st);
+        ProfScope ring("reduce_ring", st);
+        const int rc = launch_wide_ring(t, K, x, u, w, nsamp, nchan, ldx, ldu, pivot, ws0, ws1, st);
         if (rc != TXB_OK) return rc;
     } else if (cpt == 4)
         k_reduce_wide<K, (HAS_X && UPC) ? 2 : 4, HAS_X, UPC>

@@ -71,7 +71,11 @@ def reduce_wide():
     import os
     lib = _lib.load()
     cases = [(4_000_000, 64, 6, False), (16_000_000, 64, 6, False), (400_000, 2000, 4, False), (16_000_000, 16, 6, False),
-             (2_000_000, 130, 6, False), (400_000, 2000, 4, True), (4_000_000, 64, 8, False), (2_000_000, 64, 6, "upc")]
+             (2_000_000, 130, 6, False), (400_000, 2000, 4, True), (4_000_000, 64, 8, False), (2_000_000, 64, 6, "upc"),
+             (1_000_000, 500, 6, False), (400_000, 1000, 6, "upc"), (200_000, 4000, 4, False), (8_000_000, 32, 12, False)]
+    if os.environ.get("KB_SHAPES"):
+        cases = [tuple(int(v) for v in c.split(",")[:3]) + ({"0": False, "1": True, "upc": "upc"}[c.split(",")[3]],)
+                 for c in os.environ["KB_SHAPES"].split(";")]
     for n, nv, order, kind in cases:
         u = torch.randn((n, nv) if kind else (n,), dtype=torch.float64, device="cuda") * 5.3 + 175
         x = None if kind is True else torch.randn((n, nv), dtype=torch.float64, device="cuda") * 0.02
@@ -93,6 +97,36 @@ def reduce_wide():
         print(json.dumps(row), flush=True)
         del x, u
     os.environ.pop("TXB_WIDE_TMA", None)
+
+
+def reduce_scalar():
+    """A/B of the register-staged and ring (cp.async.bulk) scalar kernels."""
+    import os
+    lib = _lib.load()
+    n = 100_000_000
+    u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+    x = torch.randn(n, dtype=torch.float64, device="cuda") * 0.02
+    w = torch.rand(n, dtype=torch.float64, device="cuda")
+    for nn, order, hasx, hasw in [(n, 1, True, False), (n, 2, True, False), (n, 4, True, False), (n, 6, True, False), (n, 8, True, False),
+                                  (n, 10, True, False), (n, 12, True, False), (n, 6, True, True), (n, 6, False, False),
+                                  (10_000_000, 8, True, False), (n - 3, 6, True, False)]:
+        xx, uu, ww = (x[:nn] if hasx else None), u[:nn], (w[:nn] if hasw else None)
+        byts = 8 * nn * (1 + hasx + hasw)
+        row = {"reduce_scalar": [nn, order, hasx, hasw]}
+        outs = {}
+        for mode in ("0", "1"):
+            os.environ["TXB_SCALAR_TMA"] = mode
+            fn = (lambda: K.reduce_vals(xx, uu, order, w=ww)) if hasx else (lambda: K.reduce_vals(None, uu, order, w=ww, x_is_u=True))
+            timeit(fn)
+            lib.txb_profile_begin(b"reduce")
+            for _ in range(5):
+                outs[mode] = fn()
+            ms, nl = C.c_double(), C.c_int()
+            lib.txb_profile_end(C.byref(ms), C.byref(nl))
+            row["ring" + mode] = round(byts / (ms.value / 5 * 1e-3) / 1e9)
+        row["maxdiff"] = float((outs["0"] - outs["1"]).abs().max())
+        print(json.dumps(row), flush=True)
+    os.environ.pop("TXB_SCALAR_TMA", None)
 
 
 def reduce_big():

@@ -23,6 +23,10 @@ if which == "gather":
     K.sampler_resample(np.random.default_rng(1), x, u, nrep, 8, sync_rng=False)
 elif which == "reduce":
     K.reduce_vals(x, u, 8)
+elif which == "wide":  # python tools/ncu_case.py wide nsamp nchan order   (TXB_WIDE_TMA picks the kernel)
+    nw, cw, kw = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+    xw = torch.randn((nw, cw), dtype=torch.float64, device="cuda")
+    K.reduce_vals(xw, u[:nw], kw)
 elif which == "resample":
     f8 = K.sampler_freq(np.random.default_rng(1), 64, n, dtype=torch.uint8)
     K.resample_vals(x, u, f8, 8)
