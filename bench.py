@@ -222,6 +222,9 @@ def run_b200(a) -> None:
         t_wait = time.perf_counter()
         while not clocks.rows and time.perf_counter() - t_wait < 5.0:
             time.sleep(0.05)
+        step_device()  # the wait above idles the GPU: bring the clocks back up before timing
+        step_device()
+        barrier()
         clocks.rows.clear()
     launches0 = K.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -249,3 +249,51 @@ def test_bucketed_windows_when_scratch_is_small(K):
     plan = K.SamplerPlan(np.random.default_rng(2), nrep, n)
     mid = K.sampler_resample(plan, x, u, order=order, reps=(17, 60))
     assert torch.allclose(mid, full[17:60], rtol=1e-10, atol=1e-300)
+
+
+@pytest.mark.parametrize("n,nchan,nrep,order,weighted", [(3001, 5, 300, 3, False), (4096, 64, 130, 6, True)])
+def test_wide_bootstrap_in_replicate_windows(K, n, nchan, nrep, order, weighted):
+    """Wide x, lazy sampler: the frequency table is built and contracted one replicate window at a
+    time (data.py:1803-1810 semantics at sizes where the reference's dense table cannot exist).
+    Windows of 128 replicates must give what the numpy table gives (tests/test_data.py:94-112)."""
+    rng = np.random.default_rng(4)
+    u = rng.normal(10.0, 2.0, n)
+    x = rng.normal(0.0, 1.0, (n, nchan)) + 0.3 * u[:, None]
+    w = rng.random(n) if weighted else None
+    a, b, c = (np.random.default_rng(33) for _ in range(3))
+    idx = a.choice(n, size=(nrep, n), replace=True)
+    timing = {}
+    out = K.sampler_resample_wide(b, x, u, nrep, order, w=w, table_bytes=1, timing=timing).cpu().numpy()
+    assert timing["windows"] == -(-nrep // 128) and _same_state(a, b)
+    one = K.sampler_resample_wide(c, x, u, nrep, order, w=w).cpu().numpy()  # one window
+    assert out.shape == one.shape == (nrep, nchan, 2, order + 1)
+    scale = oc.tolerance_scale(x, u, order)
+    assert float((np.abs(out - one) / np.maximum(np.abs(one), scale)).max()) < 1e-12  # slab split differs only
+    for r in (0, 127, 128, nrep - 1):
+        ref = oc.resample_vals_gather(x, u, order, idx[r : r + 1], w=w)[0]
+        assert float((np.abs(out[r] - ref) / np.maximum(np.abs(ref), scale)).max()) < TOL
+
+
+def test_wide_bootstrap_through_the_api_uses_windows(K, monkeypatch):
+    """``wrap_resample_vals`` with ``sampler={"nrep", "rng"}`` and wide x takes the windowed path when the
+    table is over the budget, and agrees with the one-table path."""
+    import thermoextrap_b200.backend as B
+    from thermoextrap_b200.core.xr import DataArray
+
+    n, nchan, nrep, order = 2000, 7, 200, 4
+    rng = np.random.default_rng(5)
+    u = rng.normal(1.0, 1.0, n)
+    x = rng.normal(0.0, 1.0, (n, nchan)) + u[:, None]
+    xv, uv = DataArray(x, dims=("rec", "val")), DataArray(u, dims=("rec",))
+    calls = []
+    real = K.sampler_resample_wide
+    monkeypatch.setattr(K, "sampler_resample_wide", lambda *a, **k: calls.append(1) or real(*a, **k))
+    full = B.wrap_resample_vals(xv, uv, mom=(1, order), sampler={"nrep": nrep, "rng": np.random.default_rng(9)},
+                                dim="rec").obj.values
+    assert not calls
+    monkeypatch.setattr(B, "WIDE_TABLE_BYTES", 1000)
+    win = B.wrap_resample_vals(xv, uv, mom=(1, order), sampler={"nrep": nrep, "rng": np.random.default_rng(9)},
+                               dim="rec").obj.values
+    assert calls and win.shape == full.shape == (nrep, nchan, 2, order + 1)
+    scale = oc.tolerance_scale(x, u, order)
+    assert float((np.abs(win - full) / np.maximum(np.abs(full), scale)).max()) < 1e-12

@@ -528,6 +528,10 @@ def wrap_resample_vals(
     return CentralMomentsData(res, mom_ndim=2, mom_dims=md)
 
 
+# byte budget of one frequency-table window of the wide-x bootstrap (None: a third of free device memory)
+WIDE_TABLE_BYTES: int | None = None
+
+
 def resample_device(xd, ud, wd, sampler: IndexSampler, order: int, x_is_u: bool = False):
     """Route one bootstrap to the best kernel: index gather (scalar x) or freq contraction."""
     scalar = x_is_u and ud.ndim == 1 or (xd is not None and xd.ndim == 1)
@@ -535,6 +539,12 @@ def resample_device(xd, ud, wd, sampler: IndexSampler, order: int, x_is_u: bool 
         return K.sampler_resample(sampler.plan, xd, ud, order=order, w=wd, x_is_u=x_is_u)
     if scalar and sampler.has_indices and sampler._freq is None:
         return K.resample_indices(xd, ud, to_device(sampler.indices), order, w=wd, x_is_u=x_is_u)
+    if sampler.plan is not None and sampler._freq_dev is None and sampler._freq is None:
+        # wide x from a lazy sampler: a table above the budget is built and consumed window by window
+        budget = WIDE_TABLE_BYTES or K.free_table_bytes()
+        if sampler.plan.nrep * sampler.plan.ndat > budget:
+            return K.sampler_resample_wide(sampler.plan, xd, ud, order=order, w=wd, x_is_u=x_is_u,
+                                           table_bytes=budget)
     return K.resample_vals(xd, ud, sampler.freq_device(), order, w=wd, x_is_u=x_is_u)
 
 

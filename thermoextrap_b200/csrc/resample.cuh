@@ -12,9 +12,12 @@
 //        scalar mode   cols = [ w du^j | w dx du^j ],  j = 0..K
 //        wide mode     cols (c, j) = w dx_c du^j   (or w du_c^j for x_is_u)
 //   micro-kernel: lane <-> replicate (TR reps per lane), warp <-> (column
-//      group, sample phase); each thread keeps a TR x TC accumulator tile in
-//      registers, A operands come from conflict-free LDS.128, B operands are
-//      warp-broadcast LDS.128.
+//      group, replicate half, sample phase); each thread keeps a TR x TC
+//      accumulator tile in registers, A operands come from conflict-free
+//      LDS.128, B operands are warp-broadcast LDS.128.  16 warps per SM: with
+//      8 (one 4 x TC tile per thread) ncu showed every DFMA followed by a
+//      fixed-latency `wait` stall that two warps per scheduler cannot cover
+//      (fp64 pipe 68 % active, profiles/r01_resample_wide_ncu_full.txt).
 // grid = (column tiles, replicate tiles, sample slabs); slab partials are
 // summed in a fixed order by k_sum_parts (deterministic, no atomics).
 #pragma once
@@ -61,10 +64,12 @@ struct RsCfg {
     static constexpr int ES = FreqElem<FT>::ES;
     static constexpr int VS = 16 / ES;                  // samples per 16-byte chunk
     static constexpr int TC = 2 * (K + 1);              // columns per thread
-    static constexpr int TR = (TC <= 18) ? 4 : 2;       // replicates per lane
-    static constexpr int RT = 32 * TR;                  // replicate tile
+    static constexpr int NT = 512;                      // threads per CTA
+    static constexpr int TR = (TC <= 18) ? 2 : 1;       // replicates per lane
+    static constexpr int RH = 2;                        // replicate halves (warps along replicates)
+    static constexpr int RT = 32 * TR * RH;             // replicate tile
     static constexpr int NCG = NCG_;                    // column groups (warps along columns)
-    static constexpr int KW = 8 / NCG;                  // sample phases (warps along samples)
+    static constexpr int KW = NT / 32 / (NCG * RH);     // sample phases (warps along samples)
     static constexpr int NCOL = NCG * TC;               // columns per CTA
     static constexpr int CT = (MODE == RS_WIDE) ? 2 * NCG : 1;   // channels per CTA
     static constexpr int ST = (MODE == RS_WIDE) ? 32 : 256 / ES; // samples per stage
@@ -94,19 +99,20 @@ struct RsArgs {
 };
 
 template <int K, int MODE, int NCG, typename FT>
-__global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
+__global__ void __launch_bounds__(512, 1) k_resample(const RsArgs a) {
     using C = RsCfg<K, MODE, NCG, FT>;
     constexpr int ES = C::ES, VS = C::VS, TC = C::TC, TR = C::TR, RT = C::RT, KW = C::KW;
     constexpr int NCOL = C::NCOL, CT = C::CT, ST = C::ST, NG = C::NG, PITCH = C::PITCH;
-    constexpr int NSTAGE = C::NSTAGE;
+    constexpr int NSTAGE = C::NSTAGE, NT = C::NT, RH = C::RH;
 
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned char* sA = smem;
     double* sP = reinterpret_cast<double*>(smem + (size_t)NSTAGE * C::A_BYTES);
 
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
-    const int cg = wrp % NCG;   // column group
-    const int kw = wrp / NCG;   // sample phase
+    const int cg = wrp % NCG;          // column group
+    const int rh = (wrp / NCG) % RH;   // replicate half
+    const int kw = wrp / (NCG * RH);   // sample phase
     const int64_t c_base = (int64_t)blockIdx.x * CT;   // first channel of this CTA (wide)
     const int64_t r_base = (int64_t)blockIdx.y * RT;
     const int64_t s_begin = (int64_t)blockIdx.z * a.slab_len;
@@ -122,7 +128,7 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
             unsigned char* dst = sA + (size_t)(it % NSTAGE) * C::A_BYTES;
             const int64_t s0 = s_begin + (int64_t)it * ST;
             if (a.aligned) {
-                for (int e = tid; e < RT * NG; e += 256) {
+                for (int e = tid; e < RT * NG; e += NT) {
                     const int r = e / NG, g = e % NG;
                     int64_t rr = r_base + r;
                     if (rr >= a.nrep) rr = a.nrep - 1;
@@ -134,7 +140,7 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
                 }
             } else {
                 const FT* f = reinterpret_cast<const FT*>(a.freq);
-                for (int e = tid; e < RT * ST; e += 256) {
+                for (int e = tid; e < RT * ST; e += NT) {
                     const int r = e / ST, sl = e % ST;
                     int64_t rr = r_base + r;
                     if (rr >= a.nrep) rr = a.nrep - 1;
@@ -148,14 +154,14 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
     };
 
     // ---- operand B: registers prefetched one stage ahead, expanded into sP
-    constexpr int NPRE = (MODE == RS_WIDE) ? (ST * CT + 255) / 256 : 1;
+    constexpr int NPRE = (MODE == RS_WIDE) ? (ST * CT + NT - 1) / NT : 1;
     double px[NPRE], pu[NPRE], pwt[NPRE];
     auto prefetch_P = [&](int it) {
         const int64_t s0 = s_begin + (int64_t)it * ST;
 #pragma unroll
         for (int q = 0; q < NPRE; ++q) {
             px[q] = 0.0, pu[q] = 0.0, pwt[q] = 0.0;
-            const int e = tid + 256 * q;
+            const int e = tid + NT * q;
             if (MODE == RS_SCALAR) {
                 const int64_t s = s0 + e;
                 if (e < ST && s < s_end && it < nstage) {
@@ -178,7 +184,7 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
         double* dst = sP + (size_t)(it & 1) * C::P_DBL;
 #pragma unroll
         for (int q = 0; q < NPRE; ++q) {
-            const int e = tid + 256 * q;
+            const int e = tid + NT * q;
             if (MODE == RS_SCALAR) {
                 if (e < ST) {
                     const double du = pu[q] - a.pivot[has_x ? 1 : 0];
@@ -242,7 +248,7 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
             uint4 raw[TR];
 #pragma unroll
             for (int i = 0; i < TR; ++i)
-                raw[i] = *reinterpret_cast<const uint4*>(bufA + (size_t)(i * 32 + lane) * PITCH + g * 16);
+                raw[i] = *reinterpret_cast<const uint4*>(bufA + (size_t)((rh * TR + i) * 32 + lane) * PITCH + g * 16);
 #pragma unroll
             for (int v = 0; v < VS; ++v) {
                 const double* prow = bufP + (size_t)(g * VS + v) * NCOL;
@@ -272,14 +278,14 @@ __global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
             for (int i = 0; i < TR; ++i)
 #pragma unroll
                 for (int c = 0; c < TC; ++c) {
-                    double* d = red + (size_t)(i * 32 + lane) * C::RED_PITCH + cg * TC + c;
+                    double* d = red + (size_t)((rh * TR + i) * 32 + lane) * C::RED_PITCH + cg * TC + c;
                     *d = (ph == 0) ? acc[i][c] : *d + acc[i][c];
                 }
         }
         __syncthreads();
     }
     const int64_t slab = blockIdx.z;
-    for (int e = tid; e < RT * NCOL; e += 256) {
+    for (int e = tid; e < RT * NCOL; e += NT) {
         const int r = e / NCOL, col = e % NCOL;
         const int64_t rr = r_base + r;
         if (rr >= a.nrep) continue;

@@ -60,7 +60,7 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
         ProfScope prof("resample", st);
-        k_resample<K, MODE, NCG, FT><<<grid, 256, C::SMEM, st>>>(a);
+        k_resample<K, MODE, NCG, FT><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample");
     int rc = TXB_OK;

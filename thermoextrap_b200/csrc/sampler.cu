@@ -134,8 +134,50 @@ __device__ __forceinline__ void freq_bump(FT* freq, int64_t off, int& bad) {
         const int64_t boff = off * (int64_t)sizeof(FT);
         unsigned* word = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(freq) + (boff & ~3ll));
         const int sh = (int)(boff & 3) * 8;
-        const unsigned old = atomicAdd(word, 1u << sh);
-        if (((old >> sh) & MASK) == MASK) bad |= 2;
+        // no return value -> RED.E.ADD (fire and forget); a saturated lane carries into its neighbour
+        // (or out of the word) and is caught afterwards by k_freq_rowsum_check
+        atomicAdd(word, 1u << sh);
+        (void)MASK;
+    }
+}
+
+// Narrow-table overflow check.  Every replicate row receives exactly `expect` increments; a
+// byte / half-word lane that wraps loses 2^BITS from the row's lane sum (its carry adds at most
+// 1 elsewhere), so the sum of the lanes equals `expect` iff no lane overflowed.
+template <int ES>
+__global__ void __launch_bounds__(1024) k_freq_rowsum_check(const unsigned char* __restrict__ freq, int64_t row_bytes,
+                                                            long long expect, int* __restrict__ status) {
+    const unsigned char* row = freq + (int64_t)blockIdx.x * row_bytes;
+    unsigned long long sum = 0;
+    auto lanes = [](unsigned w) -> unsigned {
+        return ES == 1 ? __dp4a(w, 0x01010101u, 0u) : (w & 0xffffu) + (w >> 16);
+    };
+    if ((reinterpret_cast<uintptr_t>(row) & 15) == 0 && row_bytes % 16 == 0) {
+        const uint4* p = reinterpret_cast<const uint4*>(row);
+        const int64_t n = row_bytes / 16;
+        unsigned acc = 0;  // <= expect < 2^31 even before any wrap
+        for (int64_t i = threadIdx.x; i < n; i += 1024) {
+            const uint4 q = __ldcs(p + i);
+            acc += lanes(q.x) + lanes(q.y) + lanes(q.z) + lanes(q.w);
+        }
+        sum = acc;
+    } else {
+        const unsigned* p = reinterpret_cast<const unsigned*>(row);
+        const int64_t n = row_bytes / 4;
+        unsigned acc = 0;
+        for (int64_t i = threadIdx.x; i < n; i += 1024) acc += lanes(__ldcs(p + i));
+        sum = acc;
+    }
+    __shared__ unsigned long long sm[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        sum = sm[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (threadIdx.x == 0 && sum != (unsigned long long)expect) atomicOr(status, 2);
     }
 }
 
@@ -788,6 +830,15 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
         default:      k_sampler<MODE_HIST, 1, false, false, uint8_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
     }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
+    if (status && esz[freq_dtype] < 4) {  // narrow lanes are bumped without a return value: verify the row sums
+        TXB_CHECK_ARG(nsamp < (1ll << 31), "txb_sampler_freq: nsamp must be < 2^31 for a narrow table");
+        const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
+        const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
+        const unsigned rows = (unsigned)(rep_hi - rep_lo);
+        if (freq_dtype == TXB_U16) k_freq_rowsum_check<2><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
+        else                       k_freq_rowsum_check<1><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
+        TXB_CUDA_LAUNCH_CHECK("k_freq_rowsum_check");
+    }
     return TXB_OK;
 }
 

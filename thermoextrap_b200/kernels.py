@@ -421,7 +421,7 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     dev = device()
     plan = _plan_of(src, nrep, nsamp, ndat)
     esz = torch.empty((), dtype=dtype).element_size()
-    ldf = -(-plan.ndat * esz // 4) * 4 // esz
+    ldf = -(-plan.ndat * esz // 16) * 16 // esz  # rows 16-byte aligned for the contraction's cp.async path
     lo, hi = _window(plan, reps)
     buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -496,6 +496,73 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
         return sampler_resample(src if plan is None else plan, x, u, nrep, order, w=w, x_is_u=x_is_u, nsamp=nsamp,
                                 sync_rng=False, reps=reps, buckets=False)
     return out.reshape(hi - lo, *val_shape, 2, order + 1)
+
+
+def free_table_bytes() -> int:
+    """Default byte budget of one frequency-table window: a third of the free device memory."""
+    return torch.cuda.mem_get_info(device())[0] // 3
+
+
+def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
+                          nsamp: int | None = None, table_bytes: int | None = None, timing: dict | None = None
+                          ) -> torch.Tensor:
+    """K6 + K2 for wide ``x[nsamp, *val]``: the sampler's frequency table is histogrammed on the device one
+    replicate WINDOW at a time and contracted against the samples in place, so a table that does not fit in
+    HBM (BASELINE config 3: 1e8 samples x 1e4 replicates = 1 TB even as uint8) never exists as a whole.
+
+    ``table_bytes`` bounds one window's table (default: a third of the free device memory); windows are
+    multiples of 128 replicates, the contraction kernel's replicate tile.  ``timing`` (optional dict)
+    receives the device milliseconds spent in the histogram and contraction legs.
+    """
+    dev = device()
+    xs = None if x_is_u else _as_f64(x, dev)
+    us = _as_f64(u, dev)
+    ndat = us.shape[0]
+    plan = _plan_of(src, nrep, ndat if nsamp is None else nsamp, ndat)
+    if plan.ndat != ndat:
+        msg = f"sampler ndat={plan.ndat} does not match {ndat} samples"
+        raise ValueError(msg)
+    if table_bytes is None:
+        table_bytes = free_table_bytes()
+    ldf = -(-ndat // 16) * 16
+    out = None
+    dtype = torch.uint8
+    lo = 0
+    ev = [] if timing is not None else None
+    while lo < plan.nrep:
+        esz = torch.empty((), dtype=dtype).element_size()
+        win = max(128, int(table_bytes // (ldf * esz)) // 128 * 128)
+        hi = min(plan.nrep, lo + win)
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if ev is not None else None
+        if marks:
+            marks[0].record()
+        try:
+            freq = sampler_freq(plan, dtype=dtype, reps=(lo, hi))
+        except OverflowError:
+            if dtype == torch.int32:
+                raise
+            dtype = torch.int32  # a sample drawn > 255 times in one replicate: widen and redo this window
+            continue
+        if marks:
+            marks[1].record()
+        part = resample_vals(xs, us, freq, order, w=w, x_is_u=x_is_u)
+        if marks:
+            marks[2].record()
+            ev.append(marks)
+        del freq
+        if lo == 0 and hi == plan.nrep:
+            out = part
+            break
+        if out is None:
+            out = torch.empty((plan.nrep, *part.shape[1:]), dtype=torch.float64, device=dev)
+        out[lo:hi] = part
+        lo = hi
+    if ev is not None:
+        torch.cuda.synchronize(dev)
+        timing["freq_ms"] = sum(m[0].elapsed_time(m[1]) for m in ev)
+        timing["contract_ms"] = sum(m[1].elapsed_time(m[2]) for m in ev)
+        timing["windows"] = len(ev)
+    return out
 
 
 def _tails(data, dev):

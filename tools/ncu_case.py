@@ -30,4 +30,9 @@ elif which == "wide":  # python tools/ncu_case.py wide nsamp nchan order   (TXB_
 elif which == "resample":
     f8 = K.sampler_freq(np.random.default_rng(1), 64, n, dtype=torch.uint8)
     K.resample_vals(x, u, f8, 8)
+elif which == "resample_wide":  # python tools/ncu_case.py resample_wide [nsamp nchan order nrep]
+    nw, cw, kw, rw = (int(v) for v in (sys.argv[2:6] if len(sys.argv) > 5 else (1_000_000, 64, 6, 128)))
+    xw = torch.randn((nw, cw), dtype=torch.float64, device="cuda") + 1e-3 * u[:nw, None]
+    f8 = K.sampler_freq(np.random.default_rng(1), rw, nw, dtype=torch.uint8)
+    K.resample_vals(xw, u[:nw], f8, kw)
 torch.cuda.synchronize()
