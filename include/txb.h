@@ -177,6 +177,14 @@ int txb_sampler_scan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t*
 int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t pos_lo,
                         int64_t pos_hi, int64_t* indices, int64_t* raw_used, int* status,
                         int prepared, void* workspace, size_t ws_bytes, void* stream);
+/* txb_sampler_freq `prepared` is a flag word (TXB_SAMPLER_PREPARED | TXB_SAMPLER_NO_BUCKETS, below).
+ * With only the head as workspace every draw is a global RED.ADD on the table (2.2e10 draws/s on a
+ * B200).  Given txb_sampler_freq_workspace_bytes (or part of it: replicates go in windows) and a
+ * uint8 / uint16 table, draws are partitioned by 65520-sample bucket through shared memory and every
+ * (bucket, replicate) slice is counted in a shared-memory histogram and stored coalesced
+ * (sampler_bucket.cuh).  *status |= 8 / 16 as for txb_sampler_resample_f64 (rerun with NO_BUCKETS);
+ * |= 2 when a narrow lane overflowed (checked through the row sums: every row must sum to nsamp). */
+size_t txb_sampler_freq_workspace_bytes(int64_t ndat, int64_t nrep, int64_t nsamp, int64_t nrep_out);
 int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
                      int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
                      int64_t* raw_used, int* status, int prepared, void* workspace, size_t ws_bytes,
@@ -240,9 +248,23 @@ int txb_eval_exprs_f64(const double* vars, int64_t nelem, int nexpr, const int* 
 int txb_poly_predict_f64(const double* coefs, int np1, int64_t nelem, const double* dalpha,
                          int nalpha, int mode, double* out, void* stream);
 
+/* ---- PerturbModel.predict (models.py:1009-1046; legacy/reweight.py:89-101) -----
+ * Exponential reweighting from one state: for every dalpha[a] = alpha_a - alpha0 (DEVICE array)
+ *   out[a, c] = sum_s e_a(s) x[s, c] / sum_s e_a(s),  e_a(s) = exp(-dalpha_a u_s - max_s(-dalpha_a u_s)),
+ * x[nsamp, ldx] (first nchan columns), u[nsamp], out[nalpha, nchan].  One streaming pass over the
+ * samples per tile of 4 alphas (plus a min/max pass over u). */
+size_t txb_perturb_workspace_bytes(int64_t nsamp, int64_t nchan, int nalpha);
+int txb_perturb_predict_f64(const double* x, const double* u, int64_t nsamp, int64_t nchan,
+                            int64_t ldx, const double* dalpha, int nalpha, double* out,
+                            void* workspace, size_t ws_bytes, void* stream);
+
 /* ---- measurement helper: fp64 FMA peak micro-benchmark (bench.py roofline) ---
  * scratch: >= 1 device double; *flops (HOST pointer) = flop count of the launch. */
 int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* flops, void* stream);
+/* the same pipe driven by a register-tiled contraction (TR x 14 accumulators, three register operands
+ * per DFMA; tile 0: TR = 4, tile 1: TR = 2): the ceiling a k_resample-style micro-kernel can reach. */
+int txb_fp64_tile_peak_launch(int iters, int blocks_per_sm, int tile, double* scratch, double* flops,
+                              void* stream);
 
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",

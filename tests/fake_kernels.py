@@ -168,3 +168,9 @@ def finalize_sums(pivot, S0, S1, order, x_is_u=False, val_shape=()):
 
 def free_table_bytes() -> int:
     return 1 << 62
+
+
+def perturb_predict(x, u, dalpha):
+    from oracle import perturb as op
+
+    return _t(op.perturb_predict(_np(x), _np(u), dalpha))

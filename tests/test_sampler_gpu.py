@@ -297,3 +297,46 @@ def test_wide_bootstrap_through_the_api_uses_windows(K, monkeypatch):
     assert calls and win.shape == full.shape == (nrep, nchan, 2, order + 1)
     scale = oc.tolerance_scale(x, u, order)
     assert float((np.abs(win - full) / np.maximum(np.abs(full), scale)).max()) < 1e-12
+
+
+@pytest.mark.parametrize("nrep,nsamp,ndat,dtype_name,scratch", [
+    (5, 2_000_000, 2_000_000, "uint8", None),
+    (5, 2_000_003, 2_000_003, "uint8", 14_000_000),   # rows not 16-byte multiples; two replicates per window
+    (3, 1_500_000, 2_000_000, "uint16", None),        # nsamp != ndat
+    (2, 9_000_000, 9_000_000, "uint8", None),         # 138 buckets
+])
+def test_bucketed_histogram_bit_exact(K, nrep, nsamp, ndat, dtype_name, scratch):
+    """K6 frequency table through the shared-memory path (bucket partition + per-bucket histogram):
+    identical integers to ``indices_to_freq(rng.choice(...))`` and to the global-atomic form."""
+    import torch
+
+    dt = getattr(torch, dtype_name)
+    a, b, c = (np.random.default_rng(17) for _ in range(3))
+    ref = oc.indices_to_freq(a.choice(ndat, size=(nrep, nsamp), replace=True), ndat)
+    lib = __import__("thermoextrap_b200._lib", fromlist=["load"]).load()
+    assert lib.txb_sampler_freq_workspace_bytes(ndat, nrep, nsamp, nrep) > lib.txb_sampler_workspace_bytes(ndat, nrep * nsamp)
+    lib.txb_profile_begin(b"bucket_hist")
+    out = K.sampler_freq(b, nrep, nsamp, ndat, dtype=dt, scratch_bytes=scratch)
+    import ctypes as C
+
+    ms, nl = C.c_double(), C.c_int()
+    lib.txb_profile_end(C.byref(ms), C.byref(nl))
+    assert nl.value >= (1 if scratch is None else 2), "the bucketed histogram kernel did not run"
+    assert np.array_equal(out.cpu().numpy().astype(np.int64), ref)
+    assert _same_state(a, b)
+    slow = K.sampler_freq(c, nrep, nsamp, ndat, dtype=dt, buckets=False)
+    assert torch.equal(out, slow)
+
+
+def test_bucketed_histogram_overflow_is_loud(K):
+    """A uint8 lane that wraps inside the shared-memory histogram is caught by the row-sum check."""
+    import torch
+
+    ndat, nsamp = 600_000, 120_000_000  # mean count 200: tens of samples exceed 255
+    with pytest.raises(OverflowError):
+        K.sampler_freq(np.random.default_rng(3), 1, nsamp, ndat, dtype=torch.uint8)
+    with pytest.raises(OverflowError):
+        K.sampler_freq(np.random.default_rng(3), 1, nsamp, ndat, dtype=torch.uint8, buckets=False)
+    f16 = K.sampler_freq(np.random.default_rng(3), 1, nsamp, ndat, dtype=torch.uint16)
+    ref = np.bincount(np.random.default_rng(3).choice(ndat, size=nsamp, replace=True), minlength=ndat)
+    assert ref.max() > 255 and np.array_equal(f16[0].cpu().numpy().astype(np.int64), ref)

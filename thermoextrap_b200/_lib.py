@@ -59,6 +59,7 @@ SIGNATURES = {
     "txb_sampler_count": (_int, [_p, _i64, _i64, _int, _int, _p, _sz, _p]),
     "txb_sampler_scan": (_int, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
     "txb_sampler_indices": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p]),
+    "txb_sampler_freq_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
     "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _int, _p, _sz, _p]),
     "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64, _i64, _i64]),
     "txb_sampler_resample_fast_workspace_bytes": (_sz, [_i64, _int, _int, _i64, _i64, _i64]),
@@ -71,9 +72,12 @@ SIGNATURES = {
     "txb_convert_f64": (_int, [_p, _p, _i64, _int, _int, _p]),
     "txb_eval_exprs_f64": (_int, [_p, _i64, _int, _p, _p, _p, _p, _p, _p, _p]),
     "txb_poly_predict_f64": (_int, [_p, _int, _i64, _p, _int, _int, _p, _p]),
+    "txb_perturb_workspace_bytes": (_sz, [_i64, _i64, _int]),
+    "txb_perturb_predict_f64": (_int, [_p, _p, _i64, _i64, _i64, _p, _int, _p, _p, _sz, _p]),
     "txb_profile_begin": (_int, [C.c_char_p]),
     "txb_profile_end": (_int, [C.POINTER(C.c_double), C.POINTER(_int)]),
     "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),
+    "txb_fp64_tile_peak_launch": (_int, [_int, _int, _int, _p, C.POINTER(C.c_double), _p]),
 }
 
 

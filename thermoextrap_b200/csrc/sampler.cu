@@ -792,56 +792,6 @@ extern "C" int txb_sampler_indices(const txb_pcg64* rng, int64_t ndat, int64_t c
     return TXB_OK;
 }
 
-extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
-                                int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
-                                int64_t* raw_used, int* status, int prepared, void* workspace,
-                                size_t ws_bytes, void* stream) {
-    TXB_CHECK_ARG(freq != nullptr, "txb_sampler_freq: null pointer");
-    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
-                  "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld window [%lld, %lld)", (long long)nrep,
-                  (long long)ldf, (long long)ndat, (long long)rep_lo, (long long)rep_hi);
-    TXB_CHECK_ARG(freq_dtype >= 0 && freq_dtype <= 3, "txb_sampler_freq: bad freq_dtype %d", freq_dtype);
-    static const size_t esz[4] = {8, 4, 2, 1};
-    TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
-                  "txb_sampler_freq: narrow table rows must be 4-byte aligned");
-    Plan p;
-    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
-    if (rc != TXB_OK) return rc;
-    rc = check_head("txb_sampler_freq", workspace, ws_bytes, p);
-    if (rc != TXB_OK) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
-        set_error("txb_sampler_freq: cudaMemsetAsync failed");
-        cudaGetLastError();
-        return TXB_ERR_CUDA;
-    }
-    EmitArgs e{};
-    rc = begin_emit(p, e, workspace, raw_used, status, prepared, st);
-    if (rc != TXB_OK) return rc;
-    e.freq = freq;
-    e.ldf = ldf;
-    e.rep_lo = rep_lo;
-    e.pos_lo = rep_lo * nsamp;
-    e.pos_hi = rep_hi * nsamp;
-    switch (freq_dtype) {
-        case TXB_I64: k_sampler<MODE_HIST, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
-        case TXB_I32: k_sampler<MODE_HIST, 1, false, false, int32_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
-        case TXB_U16: k_sampler<MODE_HIST, 1, false, false, uint16_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
-        default:      k_sampler<MODE_HIST, 1, false, false, uint8_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
-    }
-    TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
-    if (status && esz[freq_dtype] < 4) {  // narrow lanes are bumped without a return value: verify the row sums
-        TXB_CHECK_ARG(nsamp < (1ll << 31), "txb_sampler_freq: nsamp must be < 2^31 for a narrow table");
-        const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
-        const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
-        const unsigned rows = (unsigned)(rep_hi - rep_lo);
-        if (freq_dtype == TXB_U16) k_freq_rowsum_check<2><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
-        else                       k_freq_rowsum_check<1><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
-        TXB_CUDA_LAUNCH_CHECK("k_freq_rowsum_check");
-    }
-    return TXB_OK;
-}
-
 namespace {
 
 // geometry of the bucketed path for one call
@@ -900,6 +850,27 @@ BucketPlan bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp, int64_t nrep_
     return b;
 }
 
+// geometry of the bucketed histogram (txb_sampler_freq): 65520-sample buckets
+BucketPlan hist_bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp) {
+    BucketPlan b{};
+    b.nb = (int)((ndat + BK_HSIZE - 1) / BK_HSIZE);
+    b.m = (double)nsamp * BK_HSIZE / (double)ndat;
+    const double arrivals = (double)(BK_THREADS * 2 * SMP_T) / b.nb;
+    b.cap = BK_MINCAP;
+    for (;; b.cap *= 2) {  // same ring sizing rule as bucket_plan
+        double term = exp(-arrivals), cdf = 0.0;
+        for (int k = 0; k <= b.cap - 31; ++k) {
+            cdf += term;
+            term *= arrivals / (k + 1);
+        }
+        if (1.0 - cdf < 1e-12 || b.cap >= 4096) break;
+    }
+    b.ok = b.nb >= 8 && b.nb <= BK_MAXNB && b.m >= 8.0 * BK_LINE && b.cap < 4096 &&
+           (size_t)b.nb * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
+    b.fixed_bytes = p.head_bytes + 256;
+    return b;
+}
+
 template <int K>
 int launch_consume(const ConsumeArgs& c, bool has_x, bool has_w, int gy, cudaStream_t st) {
     const size_t smem = sizeof(double2) * BK_SIZE + (has_w ? sizeof(double) * BK_SIZE : 0);
@@ -929,6 +900,146 @@ int launch_consume(const ConsumeArgs& c, bool has_x, bool has_w, int gy, cudaStr
 }
 
 }  // namespace
+
+extern "C" size_t txb_sampler_freq_workspace_bytes(int64_t ndat, int64_t nrep, int64_t nsamp, int64_t nrep_out) {
+    const txb_pcg64 dummy = {0, 0, 0, 1, 0, 0};
+    Plan p;
+    if (make_plan(&dummy, ndat, nrep * nsamp, nsamp, p) != TXB_OK) return 0;
+    const BucketPlan b = hist_bucket_plan(p, ndat, nsamp);
+    if (!b.ok) return align_up(p.head_bytes + 256, 256);
+    const SegPlan sp = seg_plan(b, nsamp, -1, nrep_out);
+    return align_up(align_up(p.head_bytes + 256, 256) + sp.per_rep_bytes * (size_t)nrep_out + 8192, 256);
+}
+
+extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                                int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
+                                int64_t* raw_used, int* status, int prepared, void* workspace,
+                                size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(freq != nullptr, "txb_sampler_freq: null pointer");
+    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
+                  "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld window [%lld, %lld)", (long long)nrep,
+                  (long long)ldf, (long long)ndat, (long long)rep_lo, (long long)rep_hi);
+    TXB_CHECK_ARG(freq_dtype >= 0 && freq_dtype <= 3, "txb_sampler_freq: bad freq_dtype %d", freq_dtype);
+    static const size_t esz[4] = {8, 4, 2, 1};
+    TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
+                  "txb_sampler_freq: narrow table rows must be 4-byte aligned");
+    Plan p;
+    int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
+    if (rc != TXB_OK) return rc;
+    rc = check_head("txb_sampler_freq", workspace, ws_bytes, p);
+    if (rc != TXB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
+        set_error("txb_sampler_freq: cudaMemsetAsync failed");
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    EmitArgs e{};
+    rc = begin_emit(p, e, workspace, raw_used, status, prepared & TXB_SAMPLER_PREPARED, st);
+    if (rc != TXB_OK) return rc;
+    e.freq = freq;
+    e.ldf = ldf;
+    e.rep_lo = rep_lo;
+    e.pos_lo = rep_lo * nsamp;
+    e.pos_hi = rep_hi * nsamp;
+    // ---- bucketed histogram (narrow tables, scratch beyond the head): partition the draws by sample
+    // bucket in shared memory, then count every (bucket, replicate) in a shared-memory histogram
+    bool bucketed = false;
+    if (esz[freq_dtype] < 4 && !(prepared & TXB_SAMPLER_NO_BUCKETS) && nsamp < (1ll << 31)) {
+        const BucketPlan bp = hist_bucket_plan(p, ndat, nsamp);
+        const size_t used = align_up(p.head_bytes + 256, 256);
+        const size_t avail = ws_bytes > used + 4096 ? ws_bytes - used - 4096 : 0;
+        const int64_t nwin = rep_hi - rep_lo;
+        int64_t wrep = 0;
+        SegPlan sp{};
+        if (bp.ok) {
+            wrep = nwin;
+            sp = seg_plan(bp, nsamp, -1, wrep);
+            while (wrep > 0 && sp.per_rep_bytes * (size_t)wrep > avail) {
+                const int64_t fit = (int64_t)(avail / sp.per_rep_bytes);
+                wrep = fit < wrep ? fit : wrep - 1;
+                if (wrep > 0) sp = seg_plan(bp, nsamp, -1, wrep);
+            }
+        }
+        if (wrep > 0) {
+            char* dyn = reinterpret_cast<char*>(workspace) + used;
+            unsigned* nlines = reinterpret_cast<unsigned*>(dyn);
+            uint16_t* lists = reinterpret_cast<uint16_t*>(dyn + align_up(sizeof(unsigned) * (size_t)wrep * bp.nb * sp.nseg, 64));
+            const size_t hist_smem = (size_t)BK_HSIZE * esz[freq_dtype];
+            static bool attr_done = false;
+            if (!attr_done) {
+                if (cudaFuncSetAttribute(k_bucket_scatter<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess ||
+                    cudaFuncSetAttribute(k_bucket_hist<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         BK_HSIZE) != cudaSuccess ||
+                    cudaFuncSetAttribute(k_bucket_hist<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         BK_HSIZE * 2) != cudaSuccess) {
+                    set_error("txb_sampler_freq: shared memory opt-in failed");
+                    cudaGetLastError();
+                    return TXB_ERR_CUDA;
+                }
+                attr_done = true;
+            }
+            const size_t sc_smem = (size_t)bp.nb * (bp.cap * 2 + 12);
+            for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
+                const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
+                const int64_t nw = r1 - r0;
+                BucketArgs ba{};
+                ba.iter_base = e.iter_base;
+                ba.iter_count = e.iter_count;
+                ba.niter = (int64_t)p.nblocks * p.ipb;
+                ba.status = status;
+                ba.lists = lists;
+                ba.nlines = nlines;
+                ba.nb = bp.nb;
+                ba.cap = bp.cap;
+                ba.cap_lines = sp.cap_lines;
+                ba.nseg = sp.nseg;
+                ba.seg_len = sp.seg_len;
+                ba.rep_lo = r0;
+                {
+                    ProfScope prof("bucket_scatter", st);
+                    k_bucket_scatter<1><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
+                }
+                TXB_CUDA_LAUNCH_CHECK("k_bucket_scatter<1>");
+                HistArgs h{};
+                h.lists = lists;
+                h.nlines = nlines;
+                h.nb = bp.nb;
+                h.cap_lines = sp.cap_lines;
+                h.nseg = sp.nseg;
+                h.freq = reinterpret_cast<unsigned char*>(freq) + (size_t)(r0 - rep_lo) * ldf * esz[freq_dtype];
+                h.ldf = ldf;
+                h.ndat = ndat;
+                {
+                    ProfScope prof("bucket_hist", st);
+                    const dim3 grid((unsigned)bp.nb, (unsigned)nw);
+                    if (freq_dtype == TXB_U16) k_bucket_hist<uint16_t><<<grid, BK_THREADS, hist_smem, st>>>(h);
+                    else                       k_bucket_hist<uint8_t><<<grid, BK_THREADS, hist_smem, st>>>(h);
+                }
+                TXB_CUDA_LAUNCH_CHECK("k_bucket_hist");
+            }
+            bucketed = true;
+        }
+    }
+    if (!bucketed) switch (freq_dtype) {
+        case TXB_I64: k_sampler<MODE_HIST, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        case TXB_I32: k_sampler<MODE_HIST, 1, false, false, int32_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        case TXB_U16: k_sampler<MODE_HIST, 1, false, false, uint16_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+        default:      k_sampler<MODE_HIST, 1, false, false, uint8_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
+    }
+    TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
+    if (status && esz[freq_dtype] < 4) {  // narrow lanes are bumped without a return value: verify the row sums
+        TXB_CHECK_ARG(nsamp < (1ll << 31), "txb_sampler_freq: nsamp must be < 2^31 for a narrow table");
+        const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
+        const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
+        const unsigned rows = (unsigned)(rep_hi - rep_lo);
+        if (freq_dtype == TXB_U16) k_freq_rowsum_check<2><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
+        else                       k_freq_rowsum_check<1><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
+        TXB_CUDA_LAUNCH_CHECK("k_freq_rowsum_check");
+    }
+    return TXB_OK;
+}
 
 extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t nsamp,
                                                        int64_t nrep_out) {
@@ -1013,7 +1124,7 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
         lists = reinterpret_cast<uint16_t*>((reinterpret_cast<uintptr_t>(lists) + 63) & ~(uintptr_t)63);
         static bool attr_done = false;
         if (!attr_done) {
-            if (cudaFuncSetAttribute(k_bucket_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            if (cudaFuncSetAttribute(k_bucket_scatter<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess) {
                 set_error("k_bucket_scatter: shared memory opt-in failed");
                 cudaGetLastError();
@@ -1040,7 +1151,7 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             ba.rep_lo = r0;
             {
                 ProfScope prof("bucket_scatter", st);
-                k_bucket_scatter<<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
+                k_bucket_scatter<0><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
             }
             TXB_CUDA_LAUNCH_CHECK("k_bucket_scatter");
             ConsumeArgs c{};

@@ -28,6 +28,18 @@ constexpr int BK_LINE = 32;              // entries per flushed line (64 bytes)
 constexpr int BK_MAXNB = 1536;           // buckets a producer CTA can hold rings for
 constexpr int BK_THREADS = 512;
 constexpr uint16_t BK_EMPTY = 0xFFFFu;
+// bucket geometry.  0: 8192-sample buckets (the comoment consumer stages a bucket's samples in shared
+// memory).  1: 65520-sample buckets for the histogram consumer (16-bit local index with 0xFFFF left
+// free for padding; a multiple of 16 so every bucket's slice of a frequency row stays 16-byte aligned).
+constexpr int BK_HSIZE = 65520;
+template <int GEOM>
+__device__ __forceinline__ uint32_t bk_bucket(uint32_t v) {
+    return GEOM ? v / (uint32_t)BK_HSIZE : v >> BK_LOG;
+}
+template <int GEOM>
+__device__ __forceinline__ uint16_t bk_local(uint32_t v, uint32_t b) {
+    return (uint16_t)(GEOM ? v - b * (uint32_t)BK_HSIZE : v & (BK_SIZE - 1));
+}
 
 struct BucketArgs {
     const int64_t* iter_base;   // [niter] output position of the first draw of each iteration
@@ -67,6 +79,7 @@ __device__ __forceinline__ int bk_block_scan(int v, int* sm_warp, int& total) {
     return base + inc - v;
 }
 
+template <int GEOM>
 __global__ void __launch_bounds__(BK_THREADS, 1)
     k_bucket_scatter(const __grid_constant__ SamplerArgs a, const BucketArgs e) {
     constexpr int T = SMP_T;
@@ -159,8 +172,8 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         }
     };
     auto append = [&](uint32_t v) {
-        const int b = (int)(v >> BK_LOG);
-        const uint16_t loc = (uint16_t)(v & (BK_SIZE - 1));
+        const int b = (int)bk_bucket<GEOM>(v);
+        const uint16_t loc = bk_local<GEOM>(v, (uint32_t)b);
         const unsigned slot = atomicAdd(tail + b, 1u);
         if (slot - head[b] < cap) {
             rings[(size_t)b * cap + (slot & (cap - 1))] = loc;
@@ -206,11 +219,13 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
             unsigned slot[NSLOT];
 #pragma unroll
             for (int k = 0; k < NSLOT; ++k)
-                if (mask & (1u << k)) slot[k] = atomicAdd(tail + (val[k] >> BK_LOG), 1u);
+                if (mask & (1u << k)) slot[k] = atomicAdd(tail + bk_bucket<GEOM>(val[k]), 1u);
 #pragma unroll
             for (int k = 0; k < NSLOT; ++k)
-                if (mask & (1u << k))
-                    rings[(val[k] >> BK_LOG) * cap + (slot[k] & (cap - 1))] = (uint16_t)(val[k] & (BK_SIZE - 1));
+                if (mask & (1u << k)) {
+                    const uint32_t b = bk_bucket<GEOM>(val[k]);
+                    rings[b * cap + (slot[k] & (cap - 1))] = bk_local<GEOM>(val[k], b);
+                }
         } else {
             int tot;
             const int c = __popc(mask) + (pre_acc ? 1 : 0);
@@ -304,6 +319,65 @@ __global__ void __launch_bounds__(BK_THREADS, 1) k_bucket_consume(const ConsumeA
                 if (lane == 0) c.ws1[o + j] = a1;
             }
         }
+    }
+}
+
+struct HistArgs {
+    const uint16_t* lists;
+    const unsigned* nlines;
+    int nb, cap_lines, nseg;
+    void* freq;        // row 0 = first replicate of this window
+    int64_t ldf, ndat;
+};
+
+// K6 frequency table from the bucket lists: one CTA per (bucket, replicate) counts the bucket's draws in
+// a shared-memory histogram (shared-memory atomics; global RED.ADD on a 10-100 MB row measured only
+// 2.2e10 increments/s) and writes its 65520-entry slice of the replicate's row with coalesced stores.
+// A lane that wraps carries into its neighbour exactly as in the global-atomic form, so the row-sum
+// check (k_freq_rowsum_check) covers both.
+template <typename FT>
+__global__ void __launch_bounds__(BK_THREADS) k_bucket_hist(const HistArgs c) {
+    extern __shared__ __align__(16) unsigned char bk_smem[];
+    constexpr int ES = (int)sizeof(FT);
+    constexpr int NWORD = BK_HSIZE * ES / 4;
+    unsigned* h = reinterpret_cast<unsigned*>(bk_smem);
+    const int b = blockIdx.x;
+    const int64_t r = blockIdx.y;
+    for (int i = threadIdx.x; i < NWORD; i += BK_THREADS) h[i] = 0u;
+    __syncthreads();
+    for (int seg = 0; seg < c.nseg; ++seg) {
+        const int64_t list = (r * c.nb + b) * c.nseg + seg;
+        const uint4* L = reinterpret_cast<const uint4*>(c.lists + list * c.cap_lines * BK_LINE);
+        const int nq = (int)c.nlines[list] * 4;  // 16-byte chunks (8 entries each)
+        for (int i = threadIdx.x; i < nq; i += BK_THREADS) {
+            const uint4 q = __ldcs(L + i);
+            const uint32_t wds[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const uint32_t loc = (wds[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+                if (loc != BK_EMPTY) {
+                    const uint32_t byte = loc * ES;
+                    atomicAdd(h + (byte >> 2), 1u << (8 * (byte & 3)));
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int64_t s0 = (int64_t)b * BK_HSIZE;
+    const int64_t left = c.ndat - s0;
+    const int n_here = left < BK_HSIZE ? (int)left : BK_HSIZE;
+    const int nword = (n_here * ES + 3) / 4;  // rows are padded to whole words; lanes past ndat are zero
+    unsigned char* dst = reinterpret_cast<unsigned char*>(c.freq) + (r * c.ldf + s0) * ES;
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        const int nq = nword / 4;
+        uint4* d4 = reinterpret_cast<uint4*>(dst);
+        const uint4* h4 = reinterpret_cast<const uint4*>(h);
+        for (int i = threadIdx.x; i < nq; i += BK_THREADS) d4[i] = h4[i];
+        unsigned* d1 = reinterpret_cast<unsigned*>(dst);
+        for (int i = nq * 4 + threadIdx.x; i < nword; i += BK_THREADS) d1[i] = h[i];
+    } else {
+        unsigned* d1 = reinterpret_cast<unsigned*>(dst);
+        for (int i = threadIdx.x; i < nword; i += BK_THREADS) d1[i] = h[i];
     }
 }
 

@@ -414,8 +414,14 @@ def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat
 
 
 def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
-                 dtype: torch.dtype = torch.uint8, reps=None) -> torch.Tensor:
-    """Frequency table of the same stream, histogrammed on the device without the index table."""
+                 dtype: torch.dtype = torch.uint8, reps=None, buckets: bool = True,
+                 scratch_bytes: int | None = None) -> torch.Tensor:
+    """Frequency table of the same stream, histogrammed on the device without the index table.
+
+    uint8 / uint16 tables are built by partitioning the draws by sample bucket and counting in shared
+    memory when scratch allows (``scratch_bytes``, default up to a third of the free memory; replicates
+    go in as many windows as that needs); ``buckets=False`` forces global atomics.
+    """
     global launch_count
     lib = _lib.load()
     dev = device()
@@ -426,12 +432,23 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        ws = plan.workspace(0, dev)
+        nb = 0
+        if buckets and esz < 4:
+            want = lib.txb_sampler_freq_workspace_bytes(plan.ndat, plan.nrep, plan.nsamp, hi - lo)
+            held = _workspaces.get((dev.index or 0, torch.cuda.current_stream().cuda_stream))
+            free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
+            nb = min(want, free // 3 if scratch_bytes is None else plan.head.numel() + scratch_bytes)
+        ws = plan.workspace(nb, dev)
+        flags = _lib.SAMPLER_PREPARED | (0 if buckets else _lib.SAMPLER_NO_BUCKETS)
+        # the cached workspace only grows: an explicit scratch budget is honoured through the size we declare
+        ws_bytes = ws.numel() if scratch_bytes is None else min(ws.numel(), max(nb, plan.head.numel()))
         st = lib.txb_sampler_freq(C.byref(plan.state), plan.ndat, plan.nrep, plan.nsamp, lo, hi, buf.data_ptr(),
-                                  _FREQ_DTYPES[dtype], ldf, None, status.data_ptr(), 1, ws.data_ptr(), ws.numel(),
-                                  _stream_ptr())
+                                  _FREQ_DTYPES[dtype], ldf, None, status.data_ptr(), flags, ws.data_ptr(),
+                                  ws_bytes, _stream_ptr())
     check(st, "txb_sampler_freq")
     launch_count += 2
+    if buckets and int(status.item()) & 24:  # a bucket list / ring overflowed its margin: redo with atomics
+        return sampler_freq(plan, dtype=dtype, reps=reps, buckets=False)
     _sampler_flags(status, "txb_sampler_freq")
     return buf[:, : plan.ndat]
 
@@ -678,3 +695,31 @@ def poly_predict(coefs, dalpha, mode: int = PREDICT_SUM) -> torch.Tensor:
     check(st, "txb_poly_predict_f64")
     launch_count += 1
     return out
+
+
+def perturb_predict(x, u, dalpha) -> torch.Tensor:
+    """``PerturbModel.predict`` (models.py:1009-1046): ``out[alpha, *val]``, reweighting ``x[rec, *val]`` with
+    ``exp(-dalpha * u[rec])`` (max-shifted), one streaming pass per four alphas."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    x = _as_f64(x, dev)
+    u = _as_f64(u, dev)
+    if u.ndim != 1 or x.shape[0] != u.shape[0]:
+        msg = f"perturb_predict needs u[rec] and x[rec, ...]; got {tuple(u.shape)} and {tuple(x.shape)}"
+        raise ValueError(msg)
+    nsamp = u.shape[0]
+    val_shape = tuple(x.shape[1:])
+    x = x.reshape(nsamp, -1)
+    nchan = x.shape[1]
+    da = _as_f64(torch.as_tensor(np.atleast_1d(np.asarray(dalpha, dtype=np.float64))), dev)
+    nalpha = da.numel()
+    out = torch.empty((nalpha, nchan), dtype=torch.float64, device=dev)
+    nb = lib.txb_perturb_workspace_bytes(nsamp, nchan, nalpha)
+    ws = _workspace(nb, dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_perturb_predict_f64(x.data_ptr(), u.data_ptr(), nsamp, nchan, nchan, da.data_ptr(), nalpha,
+                                         out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_perturb_predict_f64")
+    launch_count += 4
+    return out.reshape(nalpha, *val_shape)

@@ -682,11 +682,33 @@ class PerturbModel(MyAttrsMixin):
         alpha = xrwrap_alpha(alpha, name=alpha_name)
         uv, xv = self.data.uv, self.data.xv
         rec_dim = self.data.rec_dim
-        dalpha_uv = (-1.0) * (alpha - self.alpha0) * uv
-        expvals = np.exp(dalpha_uv - dalpha_uv.max(rec_dim))
-        num = dot(expvals, xv, dims=rec_dim) / xv.sizes[rec_dim]
-        den = expvals.mean(rec_dim)
-        return num / den
+        dalpha = np.atleast_1d(np.asarray(alpha.values, dtype=np.float64)) - self.alpha0
+        scalar = alpha.ndim == 0
+        if rec_dim not in uv.dims or rec_dim not in xv.dims:
+            msg = f"uv and xv need dimension {rec_dim!r}"
+            raise ValueError(msg)
+        # uv[(rep,) rec], xv[(rep,) rec, *val]: one streaming reweighting kernel per replicate
+        # (``txb_perturb_predict_f64``); the result has dims (alpha, [rep,] *val) like the reference's
+        # broadcast ``num / den`` (models.py:1037-1046).
+        lead = [d for d in uv.dims if d != rec_dim]
+        if any(d not in xv.dims for d in lead):
+            msg = f"dims of uv {uv.dims} beyond {rec_dim!r} must be dims of xv {xv.dims}"
+            raise ValueError(msg)
+        val_dims = [d for d in xv.dims if d != rec_dim and d not in lead]
+        xt = xv.transpose(*lead, rec_dim, *val_dims)
+        ut = uv.transpose(*lead, rec_dim)
+        xa, ua = np.asarray(xt.values, dtype=np.float64), np.asarray(ut.values, dtype=np.float64)
+        lead_shape = ua.shape[:-1]
+        nrec, val_shape = ua.shape[-1], xa.shape[len(lead_shape) + 1 :]
+        xa = xa.reshape(-1, nrec, *val_shape)
+        ua = ua.reshape(-1, nrec)
+        parts = []
+        for r in range(ua.shape[0]):
+            xd, ud = cm.to_device(np.ascontiguousarray(xa[r])), cm.to_device(np.ascontiguousarray(ua[r]))
+            parts.append(cm._host(cm.K.perturb_predict(xd, ud, dalpha)))
+        out = np.stack(parts, axis=1).reshape(len(dalpha), *lead_shape, *val_shape)
+        res = DataArray(out, dims=(alpha_name, *lead, *val_dims), coords={alpha_name: np.atleast_1d(alpha.values)})
+        return res.isel({alpha_name: 0}, drop=True) if scalar else res
 
     def resample(self, sampler, **kws):
         return type(self)(alpha0=self.alpha0, data=self.data.resample(sampler=sampler, **kws), alpha_name=self.alpha_name)

@@ -43,6 +43,12 @@ def peak():
             _lib.check(lib.txb_fp64_peak_launch(20000, bps, scratch.data_ptr(), C.byref(fl), None), "peak")
         t, _ = timeit(run)
         out[f"fp64_tflops_bps{bps}"] = fl.value / t / 1e12
+    for tile in (0, 1, 2, 3):
+        for bps in (1, 2, 4):  # 8, 16, 32 warps per SM
+            def run():
+                _lib.check(lib.txb_fp64_tile_peak_launch(4000, bps, tile, scratch.data_ptr(), C.byref(fl), None), "tile peak")
+            t, _ = timeit(run)
+            out[f"fp64_{('tile4x14', 'tile2x14', 'dmma_m8n8k4', 'dmma_m16n8k16')[tile]}_tflops_{8 * bps}warps"] = fl.value / t / 1e12
     print(json.dumps({"peak": out}))
 
 
