@@ -274,6 +274,33 @@ def test_resample_vals_weighted_and_x_is_u(K):
     assert relerr(out, ref, oc.tolerance_scale(uu, uu, 4)) < TOL
 
 
+@pytest.mark.parametrize("dtype", ["uint8", "int64"])
+@pytest.mark.parametrize("n,nv,nrep,order,kind", [
+    (1500, 17, 150, 1, "x"), (1500, 17, 150, 8, "x"), (1203, 33, 70, 9, "xw"), (900, 16, 9, 12, "x"),
+    (1500, 20, 140, 5, "upc"), (777, 9, 66, 10, "upc"),
+])
+def test_resample_vals_wide_tensor_core_tiles(K, dtype, n, nv, nrep, order, kind):
+    """Wide x (> 4 channels) runs on the DMMA contraction (k_resample_mma): replicate tiles of 128 / 64
+    with ragged edges, channel tiles of 16 with ragged edges, weights, and the per-channel-u form."""
+    import torch
+
+    x, u, rng = make(n, nv, seed=12)
+    idx = rng.choice(n, (nrep, n), replace=True)
+    freq = K.indices_to_freq(idx, n, dtype=getattr(torch, dtype))
+    if kind == "upc":
+        uu = u[:, None] + x
+        out = K.resample_vals(None, uu, freq, order, x_is_u=True).cpu().numpy()
+        sub = [0, nrep // 2, nrep - 1]
+        ref = oc.resample_vals_gather(uu, uu, order, idx[sub])
+        assert relerr(out[sub], ref, oc.tolerance_scale(uu, uu, order)) < TOL
+        return
+    w = rng.random(n) if kind == "xw" else None
+    out = K.resample_vals(x, u, freq, order, w=w).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, order, idx, w=w)
+    assert out.shape == ref.shape
+    assert relerr(out, ref, oc.tolerance_scale(x, u, order)) < TOL
+
+
 def test_resample_identity_freq_equals_reduce(K):
     """freq == 1 for every sample reproduces reduce_vals (size-independent property)."""
     x, u, _ = make(50_000, 8, seed=10)

@@ -14,10 +14,10 @@
 //   micro-kernel: lane <-> replicate (TR reps per lane), warp <-> (column
 //      group, replicate half, sample phase); each thread keeps a TR x TC
 //      accumulator tile in registers, A operands come from conflict-free
-//      LDS.128, B operands are warp-broadcast LDS.128.  16 warps per SM: with
-//      8 (one 4 x TC tile per thread) ncu showed every DFMA followed by a
-//      fixed-latency `wait` stall that two warps per scheduler cannot cover
-//      (fp64 pipe 68 % active, profiles/r01_resample_wide_ncu_full.txt).
+//      LDS.128, B operands are warp-broadcast LDS.128.  8 warps per SM; the
+//      16-warp split (NT = 512, TR / 2, RH = 2) measured 10 % slower.  A DFMA
+//      tile with three register operands cannot pass ~27 TFLOP/s on a B200
+//      (peak.cu); the wide-x case therefore runs on DMMA (resample_mma.cuh).
 // grid = (column tiles, replicate tiles, sample slabs); slab partials are
 // summed in a fixed order by k_sum_parts (deterministic, no atomics).
 #pragma once
@@ -64,9 +64,9 @@ struct RsCfg {
     static constexpr int ES = FreqElem<FT>::ES;
     static constexpr int VS = 16 / ES;                  // samples per 16-byte chunk
     static constexpr int TC = 2 * (K + 1);              // columns per thread
-    static constexpr int NT = 512;                      // threads per CTA
-    static constexpr int TR = (TC <= 18) ? 2 : 1;       // replicates per lane
-    static constexpr int RH = 2;                        // replicate halves (warps along replicates)
+    static constexpr int NT = 256;                      // threads per CTA
+    static constexpr int TR = (TC <= 18) ? 4 : 2;       // replicates per lane
+    static constexpr int RH = 1;                        // warps along replicates (2 with NT = 512, TR / 2)
     static constexpr int RT = 32 * TR * RH;             // replicate tile
     static constexpr int NCG = NCG_;                    // column groups (warps along columns)
     static constexpr int KW = NT / 32 / (NCG * RH);     // sample phases (warps along samples)
@@ -99,7 +99,7 @@ struct RsArgs {
 };
 
 template <int K, int MODE, int NCG, typename FT>
-__global__ void __launch_bounds__(512, 1) k_resample(const RsArgs a) {
+__global__ void __launch_bounds__(256, 1) k_resample(const RsArgs a) {
     using C = RsCfg<K, MODE, NCG, FT>;
     constexpr int ES = C::ES, VS = C::VS, TC = C::TC, TR = C::TR, RT = C::RT, KW = C::KW;
     constexpr int NCOL = C::NCOL, CT = C::CT, ST = C::ST, NG = C::NG, PITCH = C::PITCH;

@@ -1,6 +1,7 @@
 // Host-side planning + launch of k_resample for one frequency element type.
 #pragma once
-#include "resample.cuh"
+#include "resample_mma.cuh"
+#include <cstdlib>
 
 namespace txb {
 
@@ -69,6 +70,46 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
     return rc;
 }
 
+// wide x on the fp64 tensor cores (k_resample_mma); TXB_RESAMPLE_MMA=0 selects the DFMA tile instead
+inline bool rs_use_mma() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("TXB_RESAMPLE_MMA");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+
+template <int K, typename FT>
+int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
+    using C = RmCfg<K, FT>;
+    const RsPlan p = rs_plan(a.nsamp, a.nchan, a.nrep, C::RT, C::ST, C::CT);
+    const bool upc = a.ldu != 0;
+    const int64_t n = a.nrep * a.nchan * (K + 1);
+    a.ws0 = ws;
+    a.ws1 = ws;
+    a.slab_len = p.slab_len;
+    const int es = FreqElem<FT>::ES;
+    a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(k_resample_mma<K, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)C::SMEM) != cudaSuccess) {
+            set_error("k_resample_mma: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        attr_done = true;
+    }
+    const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
+    {
+        ProfScope prof("resample", st);
+        k_resample_mma<K, FT><<<grid, C::NT, C::SMEM, st>>>(a);
+    }
+    TXB_CUDA_LAUNCH_CHECK("k_resample_mma");
+    return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
+}
+
 template <typename FT>
 int resample_sums_ft(const double* x, const double* u, const double* w, int64_t nsamp, int64_t nchan,
                      int64_t ldx, int64_t ldu, int order, const double* pivot, const void* freq,
@@ -95,10 +136,12 @@ int resample_sums_ft(const double* x, const double* u, const double* w, int64_t 
                 rc = rs_launch<K, RS_SCALAR, 1, FT>(b, S0, nullptr, ws, st);                         \
                 if (rc == TXB_OK)                                                                    \
                     rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                \
-                                    : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);               \
+                         : rs_use_mma() ? rs_launch_mma<K, FT>(a, S0, S1, ws, st)                    \
+                                        : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);           \
             } else {                                                                                 \
                 rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                    \
-                                : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);                   \
+                     : rs_use_mma() ? rs_launch_mma<K, FT>(a, S0, S1, ws, st)                        \
+                                    : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);               \
             }                                                                                        \
         });                                                                                          \
         return rc;                                                                                   \
