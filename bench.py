@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--nrep", type=int, default=NREP, help=argparse.SUPPRESS)
     ap.add_argument("--order", type=int, default=ORDER, help=argparse.SUPPRESS)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help=argparse.SUPPRESS)
+    ap.add_argument("--no-wide", action="store_true", help="skip the extra wide-x target section (N=1 only)")
     return ap.parse_args()
 
 
@@ -331,6 +332,88 @@ def fp64_peak_tflops() -> float:
     return best
 
 
+# --------------------------------------------------------------------------- north_star target shape
+def wide_target(n: int = 100_000_000, c: int = 64, k: int = 6, nrep: int = 1000, table_gb: float = 0.0) -> dict:
+    """north_star's target on ONE B200: order-``k`` reduction + ``nrep``-replicate bootstrap of ``n`` samples x ``c``
+    channels (one state point of BASELINE config 3): K1 wide reduce, K6 bucketed histogram per replicate window,
+    K2 DMMA contraction.  Synthetic data generated on the device; checked through size-independent properties."""
+    import numpy as np
+    import torch
+
+    from thermoextrap_b200 import kernels as K
+
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev).manual_seed(2)
+    u = torch.empty(n, dtype=torch.float64, device=dev).normal_(175.0, 5.3, generator=g)
+    slope = torch.linspace(0.5e-3, 2e-3, c, dtype=torch.float64, device=dev)
+    x = torch.empty((n, c), dtype=torch.float64, device=dev)
+    step = 1 << 22
+    for i in range(0, n, step):  # chunked: no second 51 GB temporary
+        xs = x[i : i + step]
+        xs.normal_(0.0, 0.02, generator=g)
+        xs.addcmul_(u[i : i + step, None], slope[None, :])
+    torch.cuda.synchronize()
+
+    def timed(fn, reps=3):
+        best, out = None, None
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t = e0.elapsed_time(e1)
+            best = t if best is None else min(best, t)
+        return best, out
+
+    K.reduce_vals(x[: 1 << 20], u[: 1 << 20], k)  # warm-up
+    red_ms, base = timed(lambda: K.reduce_vals(x, u, k))
+    red_bytes = 8.0 * n * (c + 1)
+
+    rng = np.random.default_rng(1)
+    t0 = time.perf_counter()
+    plan = K.SamplerPlan(rng, nrep, n)
+    torch.cuda.synchronize()
+    plan_ms = (time.perf_counter() - t0) * 1e3
+
+    timing: dict = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    boot = K.sampler_resample_wide(plan, x, u, order=k, table_bytes=int(table_gb * 1e9) or None, timing=timing)
+    e1.record()
+    torch.cuda.synchronize()
+    boot_ms = e0.elapsed_time(e1)
+
+    # size-independent checks: every replicate holds exactly nsamp draws; the replicate means scatter
+    # around the sample mean with the standard error sigma/sqrt(n)
+    w0 = boot[:, :, 0, 0]
+    assert bool((w0 == float(n)).all()), "a replicate's total weight differs from nsamp"
+    xm, xvar = base[:, 1, 0], x[: 1 << 20].var(dim=0)
+    z = ((boot[:, :, 1, 0] - xm[None]) / (xvar / n).sqrt()[None]).abs().max().item()
+    assert z < 6.5, f"bootstrap means {z:.1f} standard errors from the sample mean"
+    del x, u
+
+    flops = 2.0 * (k + 1) * (c + 1) * n * nrep
+    peak_hbm, src = measured_peaks()
+    peak64 = fp64_peak_tflops()
+    total_ms = red_ms + plan_ms + boot_ms
+    return {
+        "workload": f"order-{k} reduction + {nrep}-replicate bootstrap of {n:.0e} samples x {c} channels (1 B200)",
+        "total_ms": total_ms, "samples_per_s_reduce": n / red_ms * 1e3, "replicates_per_s": nrep / (plan_ms + boot_ms) * 1e3,
+        "reduce": {"ms": red_ms, "GBps": red_bytes / red_ms / 1e6, "frac_hbm": red_bytes / red_ms / 1e6 / peak_hbm,
+                   "peak_source": src},
+        "sampler_plan_ms": plan_ms,
+        "bootstrap": {"ms": boot_ms, "freq_ms": timing["freq_ms"], "contract_ms": timing["contract_ms"],
+                      "windows": timing["windows"], "draws_per_s_freq": nrep * n / timing["freq_ms"] * 1e3,
+                      "contract_tflops": flops / timing["contract_ms"] / 1e9, "fp64_peak_tflops": peak64,
+                      "contract_frac_fp64": flops / timing["contract_ms"] / 1e9 / peak64,
+                      "whole_bootstrap_frac_fp64": flops / boot_ms / 1e9 / peak64,
+                      "whole_job_frac_fp64": flops / total_ms / 1e9 / peak64},
+        "checks": {"weights_exact": True, "max_z_of_replicate_means": z},
+        "gpu": torch.cuda.get_device_name(0),
+    }
+
+
 #: algorithmic HBM bytes per bootstrap draw of each kernel family (DESIGN.md section 4)
 ALG_BYTES_PER_DRAW = {"sampler_gather": 16.0, "bucket_scatter": 2.0, "bucket_consume": 2.0, "sampler_count": 0.0}
 KERNEL_NAMES = {
@@ -399,6 +482,13 @@ def emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms, red_n, launches, h2d, d
         "clocks": clock_info,
         "gpu": torch.cuda.get_device_name(0),
     }
+    if world == 1 and not a.no_wide:
+        # north_star's target shape (wide x: bucketed histogram + DMMA contraction), outside the timed region
+        try:
+            free = torch.cuda.mem_get_info()[0]
+            line["wide_target"] = wide_target(100_000_000 if free > 100e9 else 10_000_000)
+        except Exception as exc:  # noqa: BLE001  (never lose the headline line to the extra section)
+            line["wide_target"] = {"error": repr(exc)}
     print(json.dumps(line), flush=True)
 
 

@@ -29,7 +29,9 @@ struct RmCfg {
     static constexpr int CT = 16;                         // channels per CTA
     static constexpr int NCOL = CT * (K + 1);             // = WN * NTL * 8
     static constexpr int PP = NCOL + 4;                   // P row pitch (doubles): B-fragment loads conflict-free
-    static constexpr int ST = 32;                         // samples per stage
+    // samples per stage: 64 (half the block-wide syncs of 32) while three F stages + two P buffers fit
+    static constexpr size_t SMEM64 = (size_t)3 * RT * (64 * ES + 16) + 2 * (size_t)64 * PP * 8;
+    static constexpr int ST = SMEM64 <= 160 * 1024 ? 64 : 32;
     static constexpr int NG = ST / VS;
     static constexpr int PITCH = ST * ES + 16;            // F row pitch (bytes)
     static constexpr int NSTAGE = 3;

@@ -1,0 +1,130 @@
+"""Kernel-level measurements for the BASELINE configs other than the headline (development tool; bench.py is
+the judged harness).  One JSON line per case; copied to profiles/ by hand.
+
+    python tools/configs_bench.py [c4] [c5] [ksweep] [perturb]
+
+c4      lnPi width: K1 on uv[rec=1e6, n=2000] (x_is_u, order 4 -> 1-D moments to order 5) and on xv[rec, 2000] + uv[rec]
+c5      volume order 1 on 1e9 samples streamed in 2^26-sample chunks: additive pivot sums of (x, W) and (dxdq, W)
+        per chunk, one finalize at the end (what VolumeDataCallback needs: raw moments order 1 + <dxdq>)
+ksweep  scalar x, 1e7 samples, 1024 replicates, k = 2..10, table dtype int64 / int32 / uint8:
+        where the table-driven K2 crosses from HBM-bound to fp64-bound
+perturb PerturbModel.predict kernel: 1e8 scalar samples x 8 alphas; 4e6 samples x 64 channels x 8 alphas
+"""
+
+from __future__ import annotations
+
+import json
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+import numpy as np
+import torch
+
+from bench import fp64_peak_tflops, measured_peaks
+from thermoextrap_b200 import kernels as K
+
+PEAK_HBM, _ = measured_peaks()
+
+
+def timeit(fn, warm=2, rep=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(rep):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e-3)
+    return min(ts)
+
+
+def c4():
+    n, c, k = 1_000_000, 2000, 4
+    u2 = torch.empty((n, c), dtype=torch.float64, device="cuda")
+    for i in range(0, n, 1 << 16):
+        u2[i : i + (1 << 16)].normal_(0.0, 1.0)
+    u2.mul_(0.9 * torch.sqrt(torch.arange(1, c + 1, device="cuda", dtype=torch.float64)))
+    u2.sub_(4.8 * torch.arange(1, c + 1, device="cuda", dtype=torch.float64))
+    t = timeit(lambda: K.reduce_vals(None, u2, k, x_is_u=True))
+    print(json.dumps({"c4_lnpi_x_is_u": [n, c, k], "ms": t * 1e3, "GBps": 8.0 * n * c / t / 1e9,
+                      "frac_hbm": 8.0 * n * c / t / 1e9 / PEAK_HBM, "frames_per_s": n / t}), flush=True)
+    u1 = u2[:, 0].contiguous()
+    t = timeit(lambda: K.reduce_vals(u2, u1, k))
+    print(json.dumps({"c4_wide_x_plus_u": [n, c, k], "ms": t * 1e3, "GBps": 8.0 * n * (c + 1) / t / 1e9,
+                      "frac_hbm": 8.0 * n * (c + 1) / t / 1e9 / PEAK_HBM, "frames_per_s": n / t}), flush=True)
+
+
+def c5():
+    total, chunk = 1_000_000_000, 1 << 26
+    g = torch.Generator(device="cuda").manual_seed(5)
+    w = torch.empty(chunk, dtype=torch.float64, device="cuda")
+    x = torch.empty(chunk, dtype=torch.float64, device="cuda")
+    dxdq = torch.empty(chunk, dtype=torch.float64, device="cuda")
+    w.normal_(0.0, 1.0, generator=g)
+    x.uniform_(0.0, 1.0, generator=g).add_(w, alpha=0.1)
+    dxdq.copy_(x)
+    piv, _, _, _ = K.reduce_sums(x, w, 1)
+    piv2, _, _, _ = K.reduce_sums(dxdq, w, 1)
+    nchunks = (total + chunk - 1) // chunk
+
+    def job():
+        acc = None
+        left = total
+        for _ in range(nchunks):  # the same resident chunk stands in for every streamed one (kernel time only)
+            m = min(chunk, left)
+            left -= m
+            _, s0, s1, _ = K.reduce_sums(x[:m], w[:m], 1, pivot=piv)
+            _, _, d1, _ = K.reduce_sums(dxdq[:m], w[:m], 1, pivot=piv2)
+            acc = [s0, s1, d1] if acc is None else [a + b for a, b in zip(acc, (s0, s1, d1))]
+        return K.finalize_sums(piv, acc[0], acc[1], 1), acc
+
+    t = timeit(job, warm=1, rep=3)
+    out, acc = job()
+    nbytes = 8.0 * total * 4  # x, W and dxdq, W again (two passes share W)
+    assert float(out[0, 0]) == float(total)
+    print(json.dumps({"c5_volume_order1_streamed": [total, chunk], "ms": t * 1e3, "samples_per_s": total / t,
+                      "GBps": nbytes / t / 1e9, "frac_hbm": nbytes / t / 1e9 / PEAK_HBM,
+                      "note": "two K1 passes per chunk ((x, W) and (dxdq, W)); algorithmic bytes count W twice"}), flush=True)
+
+
+def ksweep():
+    n, nrep = 10_000_000, 1024
+    peak64 = fp64_peak_tflops()
+    u = torch.randn(n, dtype=torch.float64, device="cuda") * 5.3 + 175
+    x = 1e-3 * u + 0.02 * torch.randn(n, dtype=torch.float64, device="cuda")
+    f8 = K.sampler_freq(np.random.default_rng(1), nrep, n, dtype=torch.uint8)
+    tables = {"uint8": f8, "int32": f8.to(torch.int32), "int64": f8.to(torch.int64)}
+    for name, f in tables.items():
+        for k in range(2, 11):
+            t = timeit(lambda: K.resample_vals(x, u, f, k), warm=1, rep=3)
+            flops = 4.0 * (k + 1) * n * nrep
+            tb = f.element_size() * n * nrep
+            print(json.dumps({"ksweep": name, "order": k, "ms": t * 1e3, "tflops": flops / t / 1e12,
+                              "frac_fp64": flops / t / 1e12 / peak64, "table_GBps": tb / t / 1e9,
+                              "frac_hbm": tb / t / 1e9 / PEAK_HBM, "replicates_per_s": nrep / t}), flush=True)
+        del f
+    del tables
+
+
+def perturb():
+    for n, c, na in [(100_000_000, 0, 8), (4_000_000, 64, 8), (400_000, 2000, 4)]:
+        u = torch.randn(n, dtype=torch.float64, device="cuda") * 1.5 + 3.0
+        x = torch.randn((n, c) if c else (n,), dtype=torch.float64, device="cuda")
+        da = np.linspace(-0.4, 0.5, na)
+        t = timeit(lambda: K.perturb_predict(x, u, da), warm=1, rep=3)
+        passes = (na + 3) // 4
+        nbytes = 8.0 * n * (max(c, 1) + 1) * passes + 8.0 * n
+        print(json.dumps({"perturb": [n, c, na], "ms": t * 1e3, "GBps": nbytes / t / 1e9,
+                          "frac_hbm": nbytes / t / 1e9 / PEAK_HBM, "sample_alphas_per_s": n * na / t}), flush=True)
+        del x, u
+
+
+if __name__ == "__main__":
+    for w in sys.argv[1:] or ["c4", "c5", "ksweep", "perturb"]:
+        globals()[w]()
