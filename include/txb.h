@@ -265,6 +265,10 @@ int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* 
  * per DFMA; tile 0: TR = 4, tile 1: TR = 2): the ceiling a k_resample-style micro-kernel can reach. */
 int txb_fp64_tile_peak_launch(int iters, int blocks_per_sm, int tile, double* scratch, double* flops,
                               void* stream);
+/* shared-memory atomicAdd (value returned) on `nbins` spread counters, 512-thread CTAs: the ceiling of the
+ * slot reservation in k_bucket_scatter (one per draw).  *ops (HOST) = atomics issued by the launch. */
+int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double* scratch, double* ops,
+                                void* stream);
 
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",

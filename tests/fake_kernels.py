@@ -140,6 +140,15 @@ def sampler_resample(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=
     return resample_indices(x, u, plan._idx[_win(plan, reps)], order, w=w, x_is_u=x_is_u)
 
 
+def sampler_resample_wide(src, x, u, nrep=None, order=1, w=None, x_is_u=False, nsamp=None, table_bytes=None,
+                          timing=None, reps=None):
+    n = _np(u).shape[0]
+    plan = src if isinstance(src, SamplerPlan) else SamplerPlan(src, nrep, n if nsamp is None else nsamp, n)
+    uu = _np(u)
+    xx = uu if x_is_u else _np(x)
+    return _t(oc.resample_vals_gather(xx, uu, order, plan._idx[_win(plan, reps)], w=_np(w)))
+
+
 def reduce_sums(x, u, order, w=None, pivot=None):
     x, u = _np(x).astype(np.float64), _np(u).astype(np.float64)
     val_shape = x.shape[1:]

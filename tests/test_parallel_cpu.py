@@ -55,6 +55,11 @@ def _worker(rank, world, port, out_dir):
     slab = par.bootstrap_sharded(np.random.default_rng(123), x[:, 0], u, nrep, order, gather=False).numpy()
     a, b = par.shard_range(nrep, rank, world)
     assert np.allclose(slab, bref[a:b], rtol=1e-9, atol=1e-12)
+    # wide x: every rank bootstraps its replicate slice of the same table through the windowed path
+    wide = par.bootstrap_sharded(np.random.default_rng(123), x, u, nrep, order).numpy()
+    wref = oc.resample_vals_gather(x, u, order, idx)
+    assert wide.shape == wref.shape == (nrep, nv, 2, order + 1)
+    assert np.all(np.abs(wide - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
     (Path(out_dir) / f"ok{rank}").write_text("ok")
     dist.destroy_process_group()
 

@@ -147,7 +147,11 @@ def test_replicate_windows_tile_the_table(K):
     whole = K.sampler_resample(plan, x, u, order=order)
     cuts = [(0, 4), (4, 5), (5, 11)]
     parts = [K.sampler_resample(plan, x, u, order=order, reps=c) for c in cuts]
-    assert torch.allclose(torch.cat(parts), whole, rtol=1e-12, atol=0)
+    # the gather path flushes replicate sums with fp64 atomics (order varies run to run): compare on the
+    # comoment scale, not with atol=0 (odd central moments are ~0)
+    scale = oc.tolerance_scale(x, u, order)
+    got, want = torch.cat(parts).cpu().numpy(), whole.cpu().numpy()
+    assert float((np.abs(got - want) / np.maximum(np.abs(want), scale)).max()) < 1e-12
     for a, b in cuts:
         assert np.array_equal(K.sampler_indices(plan, reps=(a, b)).cpu().numpy(), ref_idx[a:b])
         f = K.sampler_freq(plan, dtype=torch.int32, reps=(a, b)).cpu().numpy()

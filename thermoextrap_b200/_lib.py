@@ -78,6 +78,7 @@ SIGNATURES = {
     "txb_profile_end": (_int, [C.POINTER(C.c_double), C.POINTER(_int)]),
     "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),
     "txb_fp64_tile_peak_launch": (_int, [_int, _int, _int, _p, C.POINTER(C.c_double), _p]),
+    "txb_smem_atomic_peak_launch": (_int, [_int, _int, _int, _p, C.POINTER(C.c_double), _p]),
 }
 
 

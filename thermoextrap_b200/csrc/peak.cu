@@ -88,7 +88,39 @@ __global__ void __launch_bounds__(256) k_dmma16816_peak(int iters, double seed, 
     for (int i = 0; i < NACC; ++i) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
     if (s == 123.456) out[0] = s;
 }
+// Shared-memory atomic throughput with returned values on spread addresses: the slot reservation of
+// k_bucket_scatter (one atomicAdd on tail[bucket] per draw, ~1200-1500 buckets, result needed).
+__global__ void __launch_bounds__(512) k_smem_atomic_peak(int iters, unsigned mask, unsigned* out) {
+    extern __shared__ unsigned bins[];
+    for (unsigned i = threadIdx.x; i <= mask; i += 512) bins[i] = 0u;
+    __syncthreads();
+    unsigned s = threadIdx.x * 2654435761u + blockIdx.x * 40503u, acc = 0u;
+    for (int it = 0; it < iters; ++it) {
+        unsigned slot[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s = s * 1664525u + 1013904223u;
+            slot[k] = atomicAdd(bins + ((s >> 10) & mask), 1u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc += slot[k];
+    }
+    if (acc == 0xdeadbeefu) out[0] = acc;
+}
 }  // namespace txb
+
+// *ops = shared-memory atomics issued (lanes); nbins must be a power of two <= 8192
+extern "C" int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double* scratch, double* ops,
+                                           void* stream) {
+    TXB_CHECK_ARG(iters > 0 && blocks_per_sm > 0 && scratch && ops && nbins >= 32 && nbins <= 8192 &&
+                      (nbins & (nbins - 1)) == 0, "txb_smem_atomic_peak_launch: bad args");
+    const int nb = txb::sm_count() * blocks_per_sm;
+    txb::k_smem_atomic_peak<<<nb, 512, nbins * sizeof(unsigned), (cudaStream_t)stream>>>(
+        iters, (unsigned)nbins - 1u, reinterpret_cast<unsigned*>(scratch));
+    TXB_CUDA_LAUNCH_CHECK("k_smem_atomic_peak");
+    *ops = 8.0 * (double)iters * 512.0 * (double)nb;
+    return TXB_OK;
+}
 
 // tile = 0: 4 x 14 accumulators (k_resample at order 6, 8 warps per SM at blocks_per_sm = 1);
 // tile = 1: 2 x 14; tile = 2 / 3: the tensor-core forms (DMMA m8n8k4 / m16n8k16).  *flops as below.

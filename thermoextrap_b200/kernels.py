@@ -521,15 +521,16 @@ def free_table_bytes() -> int:
 
 
 def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
-                          nsamp: int | None = None, table_bytes: int | None = None, timing: dict | None = None
-                          ) -> torch.Tensor:
+                          nsamp: int | None = None, table_bytes: int | None = None, timing: dict | None = None,
+                          reps=None) -> torch.Tensor:
     """K6 + K2 for wide ``x[nsamp, *val]``: the sampler's frequency table is histogrammed on the device one
     replicate WINDOW at a time and contracted against the samples in place, so a table that does not fit in
     HBM (BASELINE config 3: 1e8 samples x 1e4 replicates = 1 TB even as uint8) never exists as a whole.
 
     ``table_bytes`` bounds one window's table (default: a third of the free device memory); windows are
     multiples of 128 replicates, the contraction kernel's replicate tile.  ``timing`` (optional dict)
-    receives the device milliseconds spent in the histogram and contraction legs.
+    receives the device milliseconds spent in the histogram and contraction legs.  ``reps=(lo, hi)``
+    bootstraps only that slice of the plan's replicates (a rank's share, parallel.bootstrap_sharded).
     """
     dev = device()
     xs = None if x_is_u else _as_f64(x, dev)
@@ -544,12 +545,13 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     ldf = -(-ndat // 16) * 16
     out = None
     dtype = torch.uint8
-    lo = 0
+    first, last = _window(plan, reps)
+    lo = first
     ev = [] if timing is not None else None
-    while lo < plan.nrep:
+    while lo < last:
         esz = torch.empty((), dtype=dtype).element_size()
         win = max(128, int(table_bytes // (ldf * esz)) // 128 * 128)
-        hi = min(plan.nrep, lo + win)
+        hi = min(last, lo + win)
         marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if ev is not None else None
         if marks:
             marks[0].record()
@@ -567,12 +569,12 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
             marks[2].record()
             ev.append(marks)
         del freq
-        if lo == 0 and hi == plan.nrep:
+        if lo == first and hi == last:
             out = part
             break
         if out is None:
-            out = torch.empty((plan.nrep, *part.shape[1:]), dtype=torch.float64, device=dev)
-        out[lo:hi] = part
+            out = torch.empty((last - first, *part.shape[1:]), dtype=torch.float64, device=dev)
+        out[lo - first : hi - first] = part
         lo = hi
     if ev is not None:
         torch.cuda.synchronize(dev)

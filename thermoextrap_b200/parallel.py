@@ -45,7 +45,8 @@ def reduce_vals_sharded(x_local, u_local, order: int, w_local=None, group=None) 
 
 def bootstrap_sharded(rng: np.random.Generator, x, u, nrep: int, order: int, w=None, x_is_u: bool = False,
                       group=None, gather: bool = True) -> torch.Tensor:
-    """``.resample(sampler={"nrep": nrep, "rng": rng})`` for scalar x with the replicates split over ranks.
+    """``.resample(sampler={"nrep": nrep, "rng": rng})`` with the replicates split over ranks (scalar x: fused
+    sampler + bucketed bootstrap; wide ``x[rec, *val]``: windowed frequency table + tensor-core contraction).
 
     Every rank must pass a generator in the SAME state (e.g. ``default_rng(seed)``); it is advanced
     exactly as numpy would advance it for the whole table.  Returns ``[nrep, 2, order+1]`` on every
@@ -55,10 +56,17 @@ def bootstrap_sharded(rng: np.random.Generator, x, u, nrep: int, order: int, w=N
     n = int(u.shape[0])
     plan = K.SamplerPlan(rng, nrep, n, n, group=group)
     lo, hi = shard_range(nrep, rank, world)
-    slab = K.sampler_resample(plan, x, u, order=order, w=w, x_is_u=x_is_u, reps=(lo, hi)) if hi > lo else None
+    wide = (u if x_is_u else x).ndim > 1
+    val_shape = tuple((u if x_is_u else x).shape[1:]) if wide else ()
+    if hi <= lo:
+        slab = None
+    elif wide:
+        slab = K.sampler_resample_wide(plan, x, u, order=order, w=w, x_is_u=x_is_u, reps=(lo, hi))
+    else:
+        slab = K.sampler_resample(plan, x, u, order=order, w=w, x_is_u=x_is_u, reps=(lo, hi))
     if not gather:
         return slab
-    tail = (2, order + 1)
+    tail = (*val_shape, 2, order + 1)
     sizes = [shard_range(nrep, r, world) for r in range(world)]
     width = max(b - a for a, b in sizes)
     buf = torch.zeros((width, *tail), dtype=torch.float64, device=K.device())

@@ -49,6 +49,12 @@ def peak():
                 _lib.check(lib.txb_fp64_tile_peak_launch(4000, bps, tile, scratch.data_ptr(), C.byref(fl), None), "tile peak")
             t, _ = timeit(run)
             out[f"fp64_{('tile4x14', 'tile2x14', 'dmma_m8n8k4', 'dmma_m16n8k16')[tile]}_tflops_{8 * bps}warps"] = fl.value / t / 1e12
+    for nbins in (1024, 2048):
+        for bps in (1, 2):
+            def run():
+                _lib.check(lib.txb_smem_atomic_peak_launch(4000, bps, nbins, scratch.data_ptr(), C.byref(fl), None), "atoms")
+            t, _ = timeit(run)
+            out[f"smem_atomics_per_s_{nbins}bins_{16 * bps}warps"] = fl.value / t
     print(json.dumps({"peak": out}))
 
 
