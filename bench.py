@@ -204,9 +204,11 @@ def run_b200(a) -> None:
     xd, ud = xh.to(dev), uh.to(dev)
     rng = np.random.default_rng(1 + rank)
 
+    pending: list = []  # device status words of the timed steps, verified in one go after the region
+
     def step_device():
         c = K.reduce_vals(xd, ud, a.order)
-        b = K.sampler_resample(rng, xd, ud, a.nrep, a.order, sync_rng=False)
+        b = K.sampler_resample(rng, xd, ud, a.nrep, a.order, sync_rng=False, status_out=pending)
         return c, b
 
     def barrier():
@@ -227,6 +229,7 @@ def run_b200(a) -> None:
         step_device()
         barrier()
         clocks.rows.clear()
+    K.check_deferred(pending)  # warm-up steps
     launches0 = K.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -236,6 +239,7 @@ def run_b200(a) -> None:
     ev1.record()
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
+    K.check_deferred(pending)   # raises if any timed step overflowed a bucket list / ring (one sync, after timing)
     launches = K.launch_count - launches0
     # per-kernel device time of the bootstrap's kernels: same loop again, one family bracketed at a time
     # (events on the launching stream; the profile hook adds two event records per launch)
@@ -248,6 +252,7 @@ def run_b200(a) -> None:
         _lib.check(lib.txb_profile_end(C.byref(ms), C.byref(nl)), "txb_profile_end")
         if nl.value:
             kernels[tag] = {"ms_per_step": ms.value / a.steps, "launches_per_step": nl.value / a.steps}
+        K.check_deferred(pending)
 
     # K1 alone (samples/s) and its kernel time, outside the headline region
     lib.txb_profile_begin(b"reduce")

@@ -344,3 +344,22 @@ def test_bucketed_histogram_overflow_is_loud(K):
     f16 = K.sampler_freq(np.random.default_rng(3), 1, nsamp, ndat, dtype=torch.uint16)
     ref = np.bincount(np.random.default_rng(3).choice(ndat, size=nsamp, replace=True), minlength=ndat)
     assert ref.max() > 255 and np.array_equal(f16[0].cpu().numpy().astype(np.int64), ref)
+
+
+def test_deferred_status_gives_the_same_bootstrap(K):
+    """``status_out`` skips the per-call status read-back (bench steady state); ``check_deferred`` verifies later."""
+    n, nrep, order = 4_500_000, 3, 4   # large enough for the bucketed path
+    rng = np.random.default_rng(6)
+    u = rng.normal(0.0, 1.0, n)
+    x = u + rng.normal(0.0, 1.0, n)
+    a = K.sampler_resample(np.random.default_rng(2), x, u, nrep, order, sync_rng=False)
+    pending = []
+    b = K.sampler_resample(np.random.default_rng(2), x, u, nrep, order, sync_rng=False, status_out=pending)
+    assert len(pending) == 1
+    K.check_deferred(pending)
+    assert not pending
+    # same draws, same lists; the order of entries inside a list depends on the order of the shared-memory
+    # atomics, so the sums agree to rounding, not bit for bit
+    scale = oc.tolerance_scale(x, u, order)
+    a, b = a.cpu().numpy(), b.cpu().numpy()
+    assert float((np.abs(a - b) / np.maximum(np.abs(a), scale)).max()) < 1e-12

@@ -167,21 +167,29 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma(const RsArgs a) {
 
         const unsigned char* bufA = sA + (size_t)(it % NSTAGE) * C::A_BYTES + (size_t)a_row0 * PITCH;
         const double* bufP = sP + (size_t)(it & 1) * C::P_DBL + b_col0;
-#pragma unroll 2
-        for (int t = 0; t < ST / 4; ++t) {
+        // fragments of step t+1 are fetched (LDS) before the DMMAs of step t are issued
+        FT av[MT];
+        double bf[NTL];
+        auto fetch = [&](int t) {
             const int sl = 4 * t + fk;
-            double af[MT], bf[NTL];
 #pragma unroll
-            for (int m = 0; m < MT; ++m) {
-                const FT v = *reinterpret_cast<const FT*>(bufA + (size_t)(m * 8) * PITCH + sl * ES);
-                af[m] = u32_to_f64((uint32_t)v);
-            }
+            for (int m = 0; m < MT; ++m) av[m] = *reinterpret_cast<const FT*>(bufA + (size_t)(m * 8) * PITCH + sl * ES);
 #pragma unroll
             for (int n = 0; n < NTL; ++n) bf[n] = bufP[(size_t)sl * PP + n * 8];
+        };
+        fetch(0);
+#pragma unroll 4
+        for (int t = 0; t < ST / 4; ++t) {
+            double af[MT], bc[NTL];
+#pragma unroll
+            for (int m = 0; m < MT; ++m) af[m] = u32_to_f64((uint32_t)av[m]);
+#pragma unroll
+            for (int n = 0; n < NTL; ++n) bc[n] = bf[n];
+            if (t + 1 < ST / 4) fetch(t + 1);
 #pragma unroll
             for (int m = 0; m < MT; ++m)
 #pragma unroll
-                for (int n = 0; n < NTL; ++n) dmma884(acc[m][n][0], acc[m][n][1], af[m], bf[n]);
+                for (int n = 0; n < NTL; ++n) dmma884(acc[m][n][0], acc[m][n][1], af[m], bc[n]);
         }
     }
     cp_async_wait<0>();

@@ -843,8 +843,8 @@ BucketPlan bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp, int64_t nrep_
     }
     // worth it only for tables too big for L2-resident gathers, with mostly full lines, and when the
     // rings fit in shared memory (a window of bucket counts around 800-1170 does not: gather path)
-    b.ok = ndat >= (int64_t)4 << 20 && b.nb <= BK_MAXNB && b.m >= 8.0 * BK_LINE &&
-           (size_t)b.nb * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
+    b.ok = ndat >= (int64_t)4 << 20 && b.nb < BK_MAXNB && b.m >= 8.0 * BK_LINE &&
+           (size_t)(b.nb + 1) * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
     b.fixed_bytes = p.head_bytes + 256 + sizeof(double2) * (size_t)ndat +
                     sizeof(double) * (8 + 2 * (size_t)nrep_out * (order + 2));
     return b;
@@ -865,8 +865,8 @@ BucketPlan hist_bucket_plan(const Plan& p, int64_t ndat, int64_t nsamp) {
         }
         if (1.0 - cdf < 1e-12 || b.cap >= 4096) break;
     }
-    b.ok = b.nb >= 8 && b.nb <= BK_MAXNB && b.m >= 8.0 * BK_LINE && b.cap < 4096 &&
-           (size_t)b.nb * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
+    b.ok = b.nb >= 8 && b.nb < BK_MAXNB && b.m >= 8.0 * BK_LINE && b.cap < 4096 &&
+           (size_t)(b.nb + 1) * (b.cap * 2 + 12) <= (size_t)BK_MAXNB * (BK_MINCAP * 2 + 12);
     b.fixed_bytes = p.head_bytes + 256;
     return b;
 }
@@ -980,7 +980,7 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
                 }
                 attr_done = true;
             }
-            const size_t sc_smem = (size_t)bp.nb * (bp.cap * 2 + 12);
+            const size_t sc_smem = (size_t)(bp.nb + 1) * (bp.cap * 2 + 12);  // + the ring for rejected draws
             for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
                 const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
                 const int64_t nw = r1 - r0;
@@ -1132,7 +1132,7 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             }
             attr_done = true;
         }
-        const size_t sc_smem = (size_t)bp.nb * (bp.cap * 2 + 12);
+        const size_t sc_smem = (size_t)(bp.nb + 1) * (bp.cap * 2 + 12);  // + the ring for rejected draws
         for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
             const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
             const int64_t nw = r1 - r0;

@@ -87,10 +87,13 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     extern __shared__ __align__(16) unsigned char bk_smem[];
     const int nb = e.nb;
     const unsigned cap = (unsigned)e.cap;
-    uint16_t* rings = reinterpret_cast<uint16_t*>(bk_smem);                        // [nb][cap]
-    unsigned* tail = reinterpret_cast<unsigned*>(bk_smem + (size_t)nb * cap * 2);  // [nb]
-    unsigned* head = tail + nb;                                                    // [nb]
-    unsigned* lines = head + nb;                                                   // [nb] lines written
+    // ring nb is a sink: rejected raw draws are "appended" there so that the fast path is branch-free
+    // (it is never drained; its tail just wraps)
+    const int nbp = nb + 1;
+    uint16_t* rings = reinterpret_cast<uint16_t*>(bk_smem);                         // [nb + 1][cap]
+    unsigned* tail = reinterpret_cast<unsigned*>(bk_smem + (size_t)nbp * cap * 2);  // [nb + 1]
+    unsigned* head = tail + nbp;                                                    // [nb + 1]
+    unsigned* lines = head + nbp;                                                   // [nb + 1] lines written
     __shared__ int sm_warp[BK_THREADS / 32];
     __shared__ long long sm_j0;
 
@@ -102,7 +105,7 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     if (B > rep_begin + a.nsamp) B = rep_begin + a.nsamp;
     const int64_t list0 = (r * nb) * e.nseg + seg;  // + b * nseg
 
-    for (int b = threadIdx.x; b < nb; b += BK_THREADS) tail[b] = 0u, head[b] = 0u, lines[b] = 0u;
+    for (int b = threadIdx.x; b < nbp; b += BK_THREADS) tail[b] = 0u, head[b] = 0u, lines[b] = 0u;
     if (threadIdx.x == 0) {
         // last iteration whose first output position is <= A
         int64_t lo = 0, hi = e.niter - 1;
@@ -217,15 +220,15 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
             if (pre_acc) append(pre_val);
             // all slot reservations first (independent shared-memory atomics), then the stores
             unsigned slot[NSLOT];
+            uint32_t bk[NSLOT];
+#pragma unroll
+            for (int k = 0; k < NSLOT; ++k) {
+                bk[k] = (mask & (1u << k)) ? bk_bucket<GEOM>(val[k]) : (uint32_t)nb;
+                slot[k] = atomicAdd(tail + bk[k], 1u);
+            }
 #pragma unroll
             for (int k = 0; k < NSLOT; ++k)
-                if (mask & (1u << k)) slot[k] = atomicAdd(tail + bk_bucket<GEOM>(val[k]), 1u);
-#pragma unroll
-            for (int k = 0; k < NSLOT; ++k)
-                if (mask & (1u << k)) {
-                    const uint32_t b = bk_bucket<GEOM>(val[k]);
-                    rings[b * cap + (slot[k] & (cap - 1))] = bk_local<GEOM>(val[k], b);
-                }
+                rings[bk[k] * cap + (slot[k] & (cap - 1))] = bk_local<GEOM>(val[k], bk[k]);
         } else {
             int tot;
             const int c = __popc(mask) + (pre_acc ? 1 : 0);

@@ -453,14 +453,30 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     return buf[:, : plan.ndat]
 
 
+def check_deferred(statuses: list) -> None:
+    """Verify the status words collected by ``sampler_resample(..., status_out=list)`` (one sync for all)."""
+    global launch_count
+    for st in statuses:
+        flag = int(st.item())
+        launch_count += 6 if flag & 32 else 2
+        if flag & 24:
+            msg = "a bucket list / ring overflowed in a deferred-status bootstrap: rerun it with buckets=False"
+            raise _lib.TxbError(msg)
+        if flag & 4:
+            raise _lib.TxbError("txb_sampler_resample_f64: raw-draw range estimate too short (report this)")
+    statuses.clear()
+
+
 def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None, x_is_u: bool = False,
                      nsamp: int | None = None, sync_rng: bool = True, reps=None, buckets: bool = True,
-                     scratch_bytes: int | None = None) -> torch.Tensor:
+                     scratch_bytes: int | None = None, status_out: list | None = None) -> torch.Tensor:
     """K2 fused with the generator (scalar x): bootstrap comoments for ``{"nrep": nrep, "rng": rng}``.
 
     Neither the index nor the frequency table is materialised.  With a raw ``Generator`` and
     ``sync_rng=False`` the counting pass runs inside the call and ``rng`` is left untouched
-    (no device->host read at all: the benchmark's steady-state form).
+    (no device->host read at all: the benchmark's steady-state form).  ``status_out`` (a list)
+    defers the status check: the device status word is appended instead of being read back, and the
+    caller verifies a whole batch of calls with :func:`check_deferred` -- no host sync per call.
     """
     global launch_count
     lib = _lib.load()
@@ -497,14 +513,23 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
             # otherwise as many as fit in a third of what is free (the library windows the rest)
             fast = lib.txb_sampler_resample_fast_workspace_bytes(ndat, order, mode, nrep, nsamp, hi - lo)
             held = _workspaces.get((dev.index or 0, torch.cuda.current_stream().cuda_stream))
-            free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
-            nb = max(nb, min(fast, free // 3 if scratch_bytes is None else nb + scratch_bytes))
+            if scratch_bytes is not None:
+                nb = max(nb, min(fast, nb + scratch_bytes))
+            elif held is not None and held.numel() >= fast:
+                nb = max(nb, fast)  # steady state: the cached workspace already covers it (no driver query)
+            else:
+                free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
+                nb = max(nb, min(fast, free // 3))
         ws = plan.workspace(nb, dev) if plan is not None else _workspace(nb, dev)
         st = lib.txb_sampler_resample_f64(
             C.byref(state), _ptr(x), _ptr(u), _ptr(w), ndat, 1, order, mode, nrep, nsamp, lo, hi, out.data_ptr(),
             None, status.data_ptr(), flags, ws.data_ptr(), ws.numel(), _stream_ptr(),
         )
     check(st, "txb_sampler_resample_f64")
+    if status_out is not None:
+        status_out.append(status)
+        launch_count += 3 + (0 if prepared else 4)  # check_deferred adds the path-dependent rest
+        return out.reshape(hi - lo, *val_shape, 2, order + 1)
     flag = int(status.item())
     # kernels launched: pivot x2, pack, [count, scan, iter_scan, locate], then
     # gather + finalize, or scatter + consume + sum_parts x2 + finalize + status note (per window)
