@@ -192,12 +192,14 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         }
     };
 
-    for (int64_t j = j0; j < e.niter; ++j) {
-        const int64_t P = e.iter_base[j];
-        if (P >= B) break;
-        const int total = e.iter_count[j];
-        uint32_t val[NSLOT];
-        uint32_t mask = 0;
+    // The draws of iteration j + 1 are generated (pure ALU: 8 dependent 128-bit LCG steps) right after
+    // this thread's share of the drain of iteration j, i.e. between the two block-wide barriers, so
+    // that warps still waiting on the drain's shared-memory loads overlap with warps already issuing
+    // integer work.
+    uint32_t val[NSLOT];
+    uint32_t mask = 0;
+    auto generate = [&]() {
+        mask = 0;
 #pragma unroll
         for (int k = 0; k < T; ++k) {
             const uint64_t o = pcg_step_out(hi, lo, a.inc_hi, a.inc_lo);
@@ -207,6 +209,19 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
             val[2 * k + 1] = (uint32_t)(m1 >> 32);
             if ((uint32_t)m0 >= thresh) mask |= 1u << (2 * k);
             if ((uint32_t)m1 >= thresh) mask |= 1u << (2 * k + 1);
+        }
+    };
+    generate();
+    // position / size of the next iteration are fetched one iteration ahead (global loads off the critical path)
+    int64_t P_next = e.iter_base[j0];
+    int total_next = e.iter_count[j0];
+    for (int64_t j = j0; j < e.niter; ++j) {
+        const int64_t P = P_next;
+        if (P >= B) break;
+        const int total = total_next;
+        if (j + 1 < e.niter) {
+            P_next = e.iter_base[j + 1];
+            total_next = e.iter_count[j + 1];
         }
         const bool pre = j == 0 && threadIdx.x == 0 && a.pre_valid != 0;
         uint32_t pre_val = 0;
@@ -247,8 +262,9 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         }
         __syncthreads();
         drain(false);
-        __syncthreads();
         affine_apply(hi, lo, a.iter_jump2);
+        generate();  // iteration j + 1 (one unused set at the end of the block's range)
+        __syncthreads();
     }
     drain(true);
     for (int b = threadIdx.x; b < nb; b += BK_THREADS) {
