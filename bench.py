@@ -225,9 +225,12 @@ def run_b200(a) -> None:
         t_wait = time.perf_counter()
         while not clocks.rows and time.perf_counter() - t_wait < 5.0:
             time.sleep(0.05)
-        step_device()  # the wait above idles the GPU: bring the clocks back up before timing
-        step_device()
-        barrier()
+    # every rank: the wait above idles the GPU, bring the clocks back up before timing (collectives
+    # must be entered by ALL ranks -- a barrier inside the rank-0 branch deadlocks N > 1)
+    step_device()
+    step_device()
+    barrier()
+    if clocks is not None:
         clocks.rows.clear()
     K.check_deferred(pending)  # warm-up steps
     launches0 = K.launch_count

@@ -301,6 +301,33 @@ def test_resample_vals_wide_tensor_core_tiles(K, dtype, n, nv, nrep, order, kind
     assert relerr(out, ref, oc.tolerance_scale(x, u, order)) < TOL
 
 
+@pytest.mark.parametrize("dtype", ["int64", "int32", "uint16", "uint8"])
+@pytest.mark.parametrize("n,nrep,order,kind", [
+    (1001, 130, 1, "x"), (4099, 300, 6, "x"), (2500, 9, 7, "xw"), (777, 129, 12, "x"), (3000, 70, 3, "u"), (1500, 140, 11, "uw"),
+])
+def test_resample_vals_scalar_tensor_core_tiles(K, dtype, n, nrep, order, kind):
+    """Scalar x from a frequency table (the reference sampler's own int64 table included) on the DMMA
+    contraction (k_resample_mma_scalar) or the DFMA tile, whichever the dispatch picks: ragged replicate tiles,
+    rows that are not 16-byte multiples, weights, x_is_u."""
+    import torch
+
+    x, u, rng = make(n, 0, seed=13)
+    idx = rng.choice(n, (nrep, n), replace=True)
+    freq = K.indices_to_freq(idx, n, dtype=getattr(torch, dtype))
+    w = rng.random(n) if kind.endswith("w") else None
+    sub = [0, 1, nrep // 2, nrep - 2, nrep - 1]
+    if kind[0] == "u":
+        out = K.resample_vals(None, u, freq, order, w=w, x_is_u=True).cpu().numpy()
+        ref = oc.resample_vals_gather(u, u, order, idx[sub], w=w).reshape(len(sub), *out.shape[1:])
+        scale = oc.tolerance_scale(u, u, order).reshape(out.shape[1:])
+    else:
+        out = K.resample_vals(x, u, freq, order, w=w).cpu().numpy()
+        ref = oc.resample_vals_gather(x, u, order, idx[sub], w=w)
+        scale = oc.tolerance_scale(x, u, order)
+    assert out.shape[0] == nrep
+    assert relerr(out[sub], ref, scale) < TOL
+
+
 def test_resample_identity_freq_equals_reduce(K):
     """freq == 1 for every sample reproduces reduce_vals (size-independent property)."""
     x, u, _ = make(50_000, 8, seed=10)

@@ -1,6 +1,6 @@
 // Host-side planning + launch of k_resample for one frequency element type.
 #pragma once
-#include "resample_mma.cuh"
+#include "resample_mma_scalar.cuh"
 #include <cstdlib>
 
 namespace txb {
@@ -110,6 +110,56 @@ int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st)
     return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
 }
 
+// scalar x on DMMA: always for 4- and 8-byte tables (the kernel then waits on the table, not on the FMA
+// pipe), for narrow tables only where padding the columns to whole 8-wide fragments wastes <= 15 %
+template <int K, bool HAS_X, typename FT>
+inline bool rs_use_mma_scalar() {
+    using C = RmsCfg<K, HAS_X, FT>;
+    return rs_use_mma() && (C::ES >= 4 || (C::NCOLP - C::NCOL) * 100 <= 15 * C::NCOLP);
+}
+
+template <int K, bool HAS_X, typename FT>
+int rs_launch_mma_scalar(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
+    using C = RmsCfg<K, HAS_X, FT>;
+    const RsPlan p = rs_plan(a.nsamp, 1, a.nrep, C::RT, C::ST, 0);
+    const int64_t n0 = a.nrep * (K + 1);
+    a.ws0 = ws;
+    a.ws1 = ws + p.nslab * n0;
+    a.slab_len = p.slab_len;
+    const int es = FreqElem<FT>::ES;
+    a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(k_resample_mma_scalar<K, HAS_X, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)C::SMEM) != cudaSuccess) {
+            set_error("k_resample_mma_scalar: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        attr_done = true;
+    }
+    const dim3 grid(1u, (unsigned)p.nreptile, (unsigned)p.nslab);
+    {
+        ProfScope prof("resample", st);
+        k_resample_mma_scalar<K, HAS_X, FT><<<grid, C::NT, C::SMEM, st>>>(a);
+    }
+    TXB_CUDA_LAUNCH_CHECK("k_resample_mma_scalar");
+    int rc = launch_sum_parts(a.ws0, p.nslab, n0, S0, st);
+    if (rc == TXB_OK && HAS_X) rc = launch_sum_parts(a.ws1, p.nslab, n0, S1, st);
+    return rc;
+}
+
+// scalar-mode dispatch: DMMA where it pays, else the DFMA tile
+template <int K, typename FT>
+int rs_launch_scalar(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
+    if (a.x != nullptr) {
+        if (rs_use_mma_scalar<K, true, FT>()) return rs_launch_mma_scalar<K, true, FT>(a, S0, S1, ws, st);
+    } else {
+        if (rs_use_mma_scalar<K, false, FT>()) return rs_launch_mma_scalar<K, false, FT>(a, S0, S1, ws, st);
+    }
+    return rs_launch<K, RS_SCALAR, 1, FT>(a, S0, S1, ws, st);
+}
+
 template <typename FT>
 int resample_sums_ft(const double* x, const double* u, const double* w, int64_t nsamp, int64_t nchan,
                      int64_t ldx, int64_t ldu, int order, const double* pivot, const void* freq,
@@ -129,11 +179,11 @@ int resample_sums_ft(const double* x, const double* u, const double* w, int64_t 
         TXB_DISPATCH_ORDER(order, {                                                                  \
             if (ldu == 0 && (!x || nchan == 1)) {                                                    \
                 a.nchan = 1;                                                                         \
-                rc = rs_launch<K, RS_SCALAR, 1, FT>(a, S0, S1, ws, st);                              \
+                rc = rs_launch_scalar<K, FT>(a, S0, S1, ws, st);                                     \
             } else if (ldu == 0) {                                                                   \
                 RsArgs b = a;                                                                        \
                 b.x = nullptr; b.nchan = 1; b.ldx = 0; b.pivot = pivot + nchan;                      \
-                rc = rs_launch<K, RS_SCALAR, 1, FT>(b, S0, nullptr, ws, st);                         \
+                rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);                                \
                 if (rc == TXB_OK)                                                                    \
                     rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                \
                          : rs_use_mma() ? rs_launch_mma<K, FT>(a, S0, S1, ws, st)                    \

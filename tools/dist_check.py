@@ -39,7 +39,17 @@ assert torch.allclose(boot, single, rtol=1e-11, atol=0)
 assert g.bit_generator.state["state"] == g1.bit_generator.state["state"]
 idx = K.sampler_indices(np.random.default_rng(77), nrep, n)
 assert np.array_equal(idx[:2, :1000].cpu().numpy(), np.random.default_rng(77).choice(n, (nrep, n))[:2, :1000])
+# wide x: replicate slices of ONE table through the windowed histogram + tensor-core contraction
+nrep_w = 300
+gw, gw1 = np.random.default_rng(78), np.random.default_rng(78)
+wide = par.bootstrap_sharded(gw, x, u, nrep_w, order)
+wide1 = K.sampler_resample_wide(gw1, x, u, nrep_w, order)
+scale = torch.as_tensor(np.abs(ref.cpu().numpy()), device=wide.device).clamp_min(1e-30)
+werr = float(((wide - wide1).abs() / torch.maximum(wide1.abs(), scale)).max())
+assert wide.shape == wide1.shape == (nrep_w, nv, 2, order + 1) and werr < 1e-11, werr
+assert gw.bit_generator.state["state"] == gw1.bit_generator.state["state"]
 dist.barrier()
 if rank == 0:
-    print(f"dist_check ok: world={world} sharded reduce max rel err {err:.2e}; sharded bootstrap == single-GPU; rng state == numpy")
+    print(f"dist_check ok: world={world} sharded reduce max rel err {err:.2e}; sharded bootstrap == single-GPU "
+          f"(scalar and wide, wide max err {werr:.1e}); rng state == numpy")
 dist.destroy_process_group()
