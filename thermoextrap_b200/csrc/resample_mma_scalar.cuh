@@ -9,7 +9,7 @@
 // roofline at order 8 (profiles/r01_configs_c4_c5_ksweep_perturb.jsonl); here a warp instruction carries 256
 // FMAs and the kernel waits on the table instead.  Columns are padded to whole 8-wide fragments (NCOLP), so for
 // narrow tables it only replaces the DFMA tile where the padding is small (see rs_use_mma_scalar).
-//   8 warps along the replicates (RT = 128), each MT = 2 row fragments x NTL column fragments.
+//   8 warps along the replicates, each MT row fragments x NTL column fragments.
 #pragma once
 #include "resample_mma.cuh"
 
@@ -20,8 +20,10 @@ struct RmsCfg {
     static constexpr int ES = FreqElem<FT>::ES;
     static constexpr int VS = 16 / ES;
     static constexpr int NT = 256;
-    static constexpr int MT = 2;
-    static constexpr int RT = (NT / 32) * MT * 8;                 // 128 replicates per CTA
+    // wide table elements: one row fragment per warp (RT = 64) so that three CTAs fit on an SM (73 KB of
+    // shared memory each) and the per-stage barrier of one overlaps the loads / DMMAs of the others
+    static constexpr int MT = ES >= 4 ? 1 : 2;
+    static constexpr int RT = (NT / 32) * MT * 8;                 // replicates per CTA (64 or 128)
     static constexpr int NCOL = HAS_X ? 2 * (K + 1) : (K + 1);    // useful columns
     static constexpr int NTL = (NCOL + 7) / 8;                    // 8-column fragments
     static constexpr int NCOLP = NTL * 8;
@@ -36,7 +38,7 @@ struct RmsCfg {
 };
 
 template <int K, bool HAS_X, typename FT>
-__global__ void __launch_bounds__(256, 2) k_resample_mma_scalar(const RsArgs a) {
+__global__ void __launch_bounds__(256, 3) k_resample_mma_scalar(const RsArgs a) {
     using C = RmsCfg<K, HAS_X, FT>;
     constexpr int ES = C::ES, VS = C::VS, NT = C::NT, MT = C::MT, NTL = C::NTL, RT = C::RT;
     constexpr int PP = C::PP, ST = C::ST, NG = C::NG, PITCH = C::PITCH, NSTAGE = C::NSTAGE;
