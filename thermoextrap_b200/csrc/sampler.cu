@@ -923,17 +923,24 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
     static const size_t esz[4] = {8, 4, 2, 1};
     TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
                   "txb_sampler_freq: narrow table rows must be 4-byte aligned");
+    TXB_CHECK_ARG(esz[freq_dtype] >= 4 || nsamp < (1ll << 31),
+                  "txb_sampler_freq: nsamp must be < 2^31 for a narrow table (row-sum overflow check)");
     Plan p;
     int rc = make_plan(rng, ndat, nrep * nsamp, nsamp, p);
     if (rc != TXB_OK) return rc;
     rc = check_head("txb_sampler_freq", workspace, ws_bytes, p);
     if (rc != TXB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
-        set_error("txb_sampler_freq: cudaMemsetAsync failed");
-        cudaGetLastError();
-        return TXB_ERR_CUDA;
-    }
+    // the atomic form increments a zeroed table; the bucketed form stores every lane of every row itself
+    // (k_bucket_hist also covers the row padding when it is short), so it skips this pass over the table
+    auto zero_table = [&]() -> int {
+        if (cudaMemsetAsync(freq, 0, (size_t)(rep_hi - rep_lo) * ldf * esz[freq_dtype], st) != cudaSuccess) {
+            set_error("txb_sampler_freq: cudaMemsetAsync failed");
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        return TXB_OK;
+    };
     EmitArgs e{};
     rc = begin_emit(p, e, workspace, raw_used, status, prepared & TXB_SAMPLER_PREPARED, st);
     if (rc != TXB_OK) return rc;
@@ -962,6 +969,8 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
             }
         }
         if (wrep > 0) {
+            // row padding [ndat, ldf) lies inside the last bucket's slice?  else clear the table as before
+            if (ldf > (int64_t)bp.nb * BK_HSIZE && (rc = zero_table()) != TXB_OK) return rc;
             char* dyn = reinterpret_cast<char*>(workspace) + used;
             unsigned* nlines = reinterpret_cast<unsigned*>(dyn);
             uint16_t* lists = reinterpret_cast<uint16_t*>(dyn + align_up(sizeof(unsigned) * (size_t)wrep * bp.nb * sp.nseg, 64));
@@ -1022,6 +1031,7 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
             bucketed = true;
         }
     }
+    if (!bucketed && (rc = zero_table()) != TXB_OK) return rc;
     if (!bucketed) switch (freq_dtype) {
         case TXB_I64: k_sampler<MODE_HIST, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
         case TXB_I32: k_sampler<MODE_HIST, 1, false, false, int32_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
@@ -1030,7 +1040,6 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
     }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
     if (status && esz[freq_dtype] < 4) {  // narrow lanes are bumped without a return value: verify the row sums
-        TXB_CHECK_ARG(nsamp < (1ll << 31), "txb_sampler_freq: nsamp must be < 2^31 for a narrow table");
         const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
         const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
         const unsigned rows = (unsigned)(rep_hi - rep_lo);

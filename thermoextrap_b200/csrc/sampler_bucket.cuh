@@ -384,8 +384,12 @@ __global__ void __launch_bounds__(BK_THREADS) k_bucket_hist(const HistArgs c) {
     __syncthreads();
     const int64_t s0 = (int64_t)b * BK_HSIZE;
     const int64_t left = c.ndat - s0;
-    const int n_here = left < BK_HSIZE ? (int)left : BK_HSIZE;
-    const int nword = (n_here * ES + 3) / 4;  // rows are padded to whole words; lanes past ndat are zero
+    // the last bucket also stores the (zero) lanes of the row padding [ndat, ldf) when they fit in its slice,
+    // so the caller does not have to clear the table first; rows are whole words
+    const int64_t cover = (b == c.nb - 1 ? c.ldf : c.ndat) - s0;
+    const int n_here = cover < BK_HSIZE ? (int)cover : BK_HSIZE;
+    (void)left;
+    const int nword = (n_here * ES + 3) / 4;
     unsigned char* dst = reinterpret_cast<unsigned char*>(c.freq) + (r * c.ldf + s0) * ES;
     if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
         const int nq = nword / 4;
