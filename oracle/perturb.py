@@ -1,9 +1,10 @@
 """CPU restatement of ``PerturbModel.predict`` -- TEST INFRASTRUCTURE ONLY (never imported by the product).
 
 Follows /root/reference/src/thermoextrap/models.py:1009-1046 (xarray form) and
-legacy/reweight.py:89-101 (numpy form) line by line.  Pinned by: ``dalpha = 0`` gives the plain
-sample mean; a Gaussian ``u`` gives the analytic reweighted mean (tests/test_perturb.py); the
-reference's own test (tests/test_beta.py:154-162) compares these two forms with each other.
+legacy/reweight.py:89-101 (numpy form) line by line.  Pinned by: tests/golden/perturb.json, the output of
+the reference's own ``legacy.PerturbModel.predict`` run from /root/reference on its FixtureData
+(tests/golden/make_golden.py; the reference's test tests/test_beta.py:154-162 compares exactly these two
+forms); ``dalpha = 0`` gives the plain sample mean; a Gaussian ``u`` gives the analytic reweighted mean.
 """
 
 from __future__ import annotations

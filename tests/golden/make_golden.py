@@ -11,6 +11,7 @@ lazy_loader are not installed), but its symbolic layer (``beta.py``, ``lnpi.py``
     legacy_derivs.json derivatives + raw moments from the reference's legacy implementation
                        on the reference's FixtureData (tests/conftest.py:15-28)
     lnpi_sample.json   every 10th macrostate of tests/lnpi_data/sample_data.json
+    perturb.json       legacy PerturbModel.predict (legacy/reweight.py) on the reference's FixtureData
 """
 
 from __future__ import annotations
@@ -187,8 +188,35 @@ def make_lnpi():
     print("lnpi_sample.json written:", len(out["ref"]["lnPi"]), "macrostates")
 
 
+def make_perturb():
+    """``legacy.PerturbModel.predict`` (legacy/reweight.py:54-101) -- the implementation the reference's own test
+    compares ``PerturbModel`` with (tests/test_beta.py:154-162) -- on the reference's FixtureData."""
+    # reweight.py imports ``.interp`` (-> cmomy, xarray): give it a stub package and stub siblings
+    pkg = types.ModuleType("ref_legacy")
+    pkg.__path__ = [str(SRC / "legacy")]
+    sys.modules["ref_legacy"] = pkg
+    sys.modules["ref_legacy.interp"] = _Permissive("ref_legacy.interp")
+    sys.modules["ref_legacy.interp"].InterpModel = object
+    spec = importlib.util.spec_from_file_location("ref_legacy.reweight", SRC / "legacy" / "reweight.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ref_legacy.reweight"] = mod
+    spec.loader.exec_module(mod)
+    rng = np.random.default_rng(0)
+    n, nv = 100, 5
+    u = rng.random(n)
+    x = rng.random((n, nv))
+    beta0, betas = 0.5, [0.3, 0.7, 0.5, 2.5]
+    pm = mod.PerturbModel(beta0, xData=x, uData=u)
+    out = {"seed": 0, "n": n, "nv": nv, "beta0": beta0, "betas": betas,
+           "predict": np.asarray(pm.predict(betas)).tolist(),
+           "check_u_sum": float(u.sum()), "check_x_sum": float(x.sum())}
+    (OUT / "perturb.json").write_text(json.dumps(out))
+    print("perturb.json written")
+
+
 if __name__ == "__main__":
     make_lnpi()
     make_legacy()
     install_stubs()
     make_exprs()
+    make_perturb()

@@ -18,6 +18,34 @@ def _samples(n, nchan=None, seed=0):
     return x, u
 
 
+def _golden():
+    import json
+    from pathlib import Path
+
+    g = json.loads((Path(__file__).parent / "golden" / "perturb.json").read_text())
+    rng = np.random.default_rng(g["seed"])  # the reference's FixtureData draw order (tests/conftest.py:15-28)
+    u = rng.random(g["n"])
+    x = rng.random((g["n"], g["nv"]))
+    assert abs(u.sum() - g["check_u_sum"]) < 1e-12 and abs(x.sum() - g["check_x_sum"]) < 1e-10
+    return g, x, u
+
+
+def test_oracle_matches_reference_legacy_golden():
+    """tests/golden/perturb.json holds ``legacy.PerturbModel.predict`` run from /root/reference (make_golden.py)."""
+    g, x, u = _golden()
+    out = op.perturb_predict(x, u, np.asarray(g["betas"]) - g["beta0"])
+    assert np.allclose(out, np.asarray(g["predict"]), rtol=1e-13, atol=0)
+
+
+@pytest.mark.gpu
+def test_kernel_matches_reference_legacy_golden():
+    from thermoextrap_b200 import kernels as K
+
+    g, x, u = _golden()
+    out = K.perturb_predict(x, u, np.asarray(g["betas"]) - g["beta0"]).cpu().numpy()
+    assert np.allclose(out, np.asarray(g["predict"]), rtol=1e-10, atol=0)
+
+
 def test_oracle_dalpha_zero_is_the_mean():
     x, u = _samples(1000, 3)
     assert np.allclose(op.perturb_predict(x, u, [0.0])[0], x.mean(axis=0), rtol=1e-13)
