@@ -424,6 +424,11 @@ def wide_target(n: int = 100_000_000, c: int = 64, k: int = 6, nrep: int = 1000,
 
 #: algorithmic HBM bytes per bootstrap draw of each kernel family
 ALG_BYTES_PER_DRAW = {"sampler_gather": 16.0, "bucket_scatter": 2.0, "bucket_consume": 2.0, "sampler_count": 0.0}
+#: DRAM bytes per draw measured by `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum over a 64-replicate
+#: launch = 6.4e8 draws; profiles/r01_bucket_kernels_ncu_full_s21.txt, r01_gather_ncu_full.txt) -> roofline.traffic
+NCU_DRAM_BYTES_PER_DRAW = {"bucket_scatter": (0.001503 + 1.255659) * 1e9 / 6.4e8,
+                           "bucket_consume": (1.550797 + 0.009994) * 1e9 / 6.4e8,
+                           "sampler_count": 0.0, "sampler_gather": 60.0}
 KERNEL_NAMES = {
     "sampler_gather": "k_sampler<MODE_GATHER> (fused PCG64 sampler + HBM gather + power sums)",
     "bucket_scatter": "k_bucket_scatter (PCG64 sampler + shared-memory write-combining partition by sample bucket)",
@@ -473,7 +478,9 @@ def emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms, red_n, launches, h2d, d
         "roofline": {
             "kernel": KERNEL_NAMES[top],
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "peak_source": peak_src, "traffic": None, "launch_ms": k_s * 1e3,
+            "peak_source": peak_src, "traffic": NCU_DRAM_BYTES_PER_DRAW[top] * draws_per_launch,
+            "traffic_unit": "bytes per launch (ncu dram read + write per draw x draws of this launch)",
+            "launch_ms": k_s * 1e3,
             "launches_per_step": kernels[top]["launches_per_step"],
             "share_of_step": kernels[top]["ms_per_step"] / step_ms,
             "note": "the partition kernel is instruction-issue bound (integer PCG64 + shared-memory atomics), "
