@@ -99,6 +99,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_perturb(const PtArgs a) {
             for (int i = 0; i < PT_NA; ++i) num[i][0] = fma(e[i], xx, num[i][0]);
         } else {
             const int nrow = (int)min((int64_t)32, s_end - s0);
+#pragma unroll 4
             for (int j = 0; j < nrow; ++j) {
                 const double* row = a.x + (s0 + j) * a.ldx + c0 + lane;
                 double xv[QC];

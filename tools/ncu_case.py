@@ -35,4 +35,11 @@ elif which == "resample_wide":  # python tools/ncu_case.py resample_wide [nsamp 
     xw = torch.randn((nw, cw), dtype=torch.float64, device="cuda") + 1e-3 * u[:nw, None]
     f8 = K.sampler_freq(np.random.default_rng(1), rw, nw, dtype=torch.uint8)
     K.resample_vals(xw, u[:nw], f8, kw)
+elif which == "resample_i64":  # scalar x from the reference's own int64 frequency table (k_resample_mma_scalar)
+    nr = 256
+    f64 = K.sampler_freq(np.random.default_rng(1), nr, 2_000_000, dtype=torch.uint8).to(torch.int64)
+    K.resample_vals(x[:2_000_000], u[:2_000_000], f64, 8)
+elif which == "perturb":
+    xw = torch.randn((4_000_000, 64), dtype=torch.float64, device="cuda")
+    K.perturb_predict(xw, u[:4_000_000] * 0.01, np.linspace(-0.4, 0.5, 8))
 torch.cuda.synchronize()
