@@ -148,16 +148,20 @@ __global__ void __launch_bounds__(PT_THREADS) k_perturb(const PtArgs a) {
 
 __global__ void __launch_bounds__(256) k_perturb_final(const double* __restrict__ part, int64_t nslab, int nalpha,
                                                        int64_t nchan, double* __restrict__ out) {
-    const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    // one warp per output element: lanes stride over the slabs (fixed order -> deterministic), then a shuffle sum
+    const int64_t e = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (e >= (int64_t)nalpha * nchan) return;
+    const int lane = threadIdx.x & 31;
     const int64_t ai = e / nchan, c = e % nchan;
     double num = 0.0, den = 0.0;
-    for (int64_t s = 0; s < nslab; ++s) {
+    for (int64_t s = lane; s < nslab; s += 32) {
         const double* p = part + (s * nalpha + ai) * (nchan + 1);
         num += p[c];
         den += p[nchan];
     }
-    out[e] = num / den;
+    num = warp_sum(num);
+    den = warp_sum(den);
+    if (lane == 0) out[e] = num / den;
 }
 
 static int64_t pt_nslab(int64_t nsamp, int64_t nchan, int nalpha) {
@@ -219,7 +223,7 @@ extern "C" int txb_perturb_predict_f64(const double* x, const double* u, int64_t
     }
     TXB_CUDA_LAUNCH_CHECK("k_perturb");
     const int64_t nout = (int64_t)nalpha * nchan;
-    k_perturb_final<<<(unsigned)((nout + 255) / 256), 256, 0, st>>>(part, nslab_used, nalpha, nchan, out);
+    k_perturb_final<<<(unsigned)((nout + 7) / 8), 256, 0, st>>>(part, nslab_used, nalpha, nchan, out);
     TXB_CUDA_LAUNCH_CHECK("k_perturb_final");
     return TXB_OK;
 }
