@@ -500,6 +500,12 @@ def emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms, red_n, launches, h2d, d
     if world == 1 and not a.no_wide:
         # north_star's target shape (wide x: bucketed histogram + DMMA contraction), outside the timed region
         try:
+            from thermoextrap_b200 import backend as _backend
+            from thermoextrap_b200 import kernels as _kernels
+
+            _backend.clear_device_cache()   # hand the headline's buffers back before the 51 GB sample set
+            _kernels._workspaces.clear()
+            torch.cuda.empty_cache()
             free = torch.cuda.mem_get_info()[0]
             line["wide_target"] = wide_target(100_000_000 if free > 100e9 else 10_000_000)
         except Exception as exc:  # noqa: BLE001  (never lose the headline line to the extra section)

@@ -415,12 +415,13 @@ def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat
 
 def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
                  dtype: torch.dtype = torch.uint8, reps=None, buckets: bool = True,
-                 scratch_bytes: int | None = None) -> torch.Tensor:
+                 scratch_bytes: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
     """Frequency table of the same stream, histogrammed on the device without the index table.
 
     uint8 / uint16 tables are built by partitioning the draws by sample bucket and counting in shared
     memory when scratch allows (``scratch_bytes``, default up to a third of the free memory; replicates
-    go in as many windows as that needs); ``buckets=False`` forces global atomics.
+    go in as many windows as that needs); ``buckets=False`` forces global atomics.  ``out`` (optional,
+    ``[>= hi - lo, ldf]`` of ``dtype`` with 16-byte rows) is filled instead of a new allocation.
     """
     global launch_count
     lib = _lib.load()
@@ -429,7 +430,13 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     esz = torch.empty((), dtype=dtype).element_size()
     ldf = -(-plan.ndat * esz // 16) * 16 // esz  # rows 16-byte aligned for the contraction's cp.async path
     lo, hi = _window(plan, reps)
-    buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev)
+    if out is None:
+        buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev)
+    else:
+        if out.dtype != dtype or out.ndim != 2 or out.shape[0] < hi - lo or out.shape[1] != ldf or not out.is_contiguous():
+            msg = f"out must be a contiguous [>= {hi - lo}, {ldf}] tensor of {dtype}"
+            raise ValueError(msg)
+        buf = out[: hi - lo]
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         nb = 0
@@ -448,7 +455,7 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
     check(st, "txb_sampler_freq")
     launch_count += 2
     if buckets and int(status.item()) & 24:  # a bucket list / ring overflowed its margin: redo with atomics
-        return sampler_freq(plan, dtype=dtype, reps=reps, buckets=False)
+        return sampler_freq(plan, dtype=dtype, reps=reps, buckets=False, out=out)
     _sampler_flags(status, "txb_sampler_freq")
     return buf[:, : plan.ndat]
 
@@ -573,15 +580,19 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     first, last = _window(plan, reps)
     lo = first
     ev = [] if timing is not None else None
+    table = None  # one allocation serves every window (no 10-GB-class alloc / free per window)
     while lo < last:
         esz = torch.empty((), dtype=dtype).element_size()
         win = max(128, int(table_bytes // (ldf * esz)) // 128 * 128)
         hi = min(last, lo + win)
+        if table is None or table.dtype != dtype:
+            table = None
+            table = torch.empty((min(win, last - lo), -(-ndat * esz // 16) * 16 // esz), dtype=dtype, device=dev)
         marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if ev is not None else None
         if marks:
             marks[0].record()
         try:
-            freq = sampler_freq(plan, dtype=dtype, reps=(lo, hi))
+            freq = sampler_freq(plan, dtype=dtype, reps=(lo, hi), out=table)
         except OverflowError:
             if dtype == torch.int32:
                 raise
