@@ -1,7 +1,9 @@
 """Kernel-level measurements for the BASELINE configs other than the headline (development tool; bench.py is
 the judged harness).  One JSON line per case; copied to profiles/ by hand.
 
-    python tools/configs_bench.py [c4] [c5] [ksweep] [perturb]
+    python tools/configs_bench.py [c1] [c4] [c5] [ksweep] [perturb]
+
+c1      ideal-gas beta extrapolation through the public API (order 6, 1e5 samples): wall clock per call
 
 c4      lnPi width: K1 on uv[rec=1e6, n=2000] (x_is_u, order 4 -> 1-D moments to order 5) and on xv[rec, 2000] + uv[rec]
 c5      volume order 1 on 1e9 samples streamed in 2^26-sample chunks: additive pivot sums of (x, W) and (dxdq, W)
@@ -42,6 +44,35 @@ def timeit(fn, warm=2, rep=5):
         torch.cuda.synchronize()
         ts.append(a.elapsed_time(b) * 1e-3)
     return min(ts)
+
+
+def c1():
+    """BASELINE config 1 through the public API: ideal-gas beta extrapolation, order 6, 1e5 samples, scalar x."""
+    import time
+
+    import thermoextrap_b200 as xt
+    from thermoextrap_b200 import backend
+
+    beta0, order, betas = 5.6, 6, np.array([5.1, 5.5, 5.7, 6.1])
+    rng = np.random.default_rng(0)
+    xdata, udata = xt.idealgas.generate_data((100_000, 1000), beta0, 1.0, rng=rng)
+    xv, uv = xt.DataArray(xdata, dims=("rec",)), xt.DataArray(udata, dims=("rec",))
+
+    def job():
+        backend.clear_device_cache()
+        data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+        return xt.beta.factory_extrapmodel(beta=beta0, data=data).predict(betas).values
+
+    job()
+    ts = []
+    for _ in range(10):
+        t0 = time.perf_counter()
+        pred = job()
+        ts.append(time.perf_counter() - t0)
+    true, _ = xt.idealgas.x_beta_extrap(order, beta0, betas, 1.0)
+    print(json.dumps({"c1_idealgas_api": [100_000, order], "ms_per_call": min(ts) * 1e3, "samples_per_s": 1e5 / min(ts),
+                      "max_abs_err_vs_analytic": float(np.max(np.abs(pred - true))),
+                      "note": "from_vals (H2D + K1) + factory_extrapmodel + predict (K5 + K7), host wall clock"}), flush=True)
 
 
 def c4():
