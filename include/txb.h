@@ -101,7 +101,12 @@ int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t nsamp, int
 /* ---- K2: resample_vals ----------------------------------------------------
  * replaces cmomy.wrap_resample_vals(x, u, weight=, sampler=, mom=(1,order))
  * data.py:1354-1366, 1803-1810.  freq[nrep, ldf] is the sampler's table
- * (int64 unchanged, or a narrowed copy).  Counts must be < 2^31.             */
+ * (int64 unchanged, or a narrowed copy).  Counts must be < 2^31.
+ * The contraction S[r, col] = sum_s freq[r, s] * P[s, col] runs on the fp64 tensor
+ * cores (DMMA.8x8x4) for more than 4 channels and for scalar x with 4/8-byte tables
+ * (or little column padding), else on a register-tiled DFMA kernel; environment
+ * TXB_RESAMPLE_MMA=0 forces the DFMA kernels (A/B measurements).  Rows that are
+ * 16-byte aligned (freq pointer and ldf * element size) take the cp.async path. */
 size_t txb_resample_workspace_bytes(int64_t nsamp, int64_t nchan, int order, int64_t nrep);
 int txb_resample_sums_f64(const double* x, const double* u, const double* w, int64_t nsamp,
                           int64_t nchan, int64_t ldx, int64_t ldu, int order, const double* pivot,
