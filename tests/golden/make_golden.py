@@ -12,6 +12,10 @@ lazy_loader are not installed), but its symbolic layer (``beta.py``, ``lnpi.py``
                        on the reference's FixtureData (tests/conftest.py:15-28)
     lnpi_sample.json   every 10th macrostate of tests/lnpi_data/sample_data.json
     perturb.json       legacy PerturbModel.predict (legacy/reweight.py) on the reference's FixtureData
+    legacy_extrap.json legacy ExtrapModel (legacy/extrap.py:40-118): derivatives to order 6 and predict at every
+                       order 0..6 on the reference's FixtureData -- what tests/test_beta.py:43-47 compares with
+    idealgas.json      the reference's idealgas.py (only ``validate_rng`` shimmed): analytic functions, the seeded
+                       sampler / generate_data, and every x_*_extrap variant (tests/test_idealgas.py)
 """
 
 from __future__ import annotations
@@ -125,8 +129,8 @@ def make_exprs():
     cases = []
     for central in (True, False):
         for post in (None, "minus_log", "pow_2"):
-            cases.append(("x_ave", dict(central=central, xalpha=False, post_func=post), 6))
-            cases.append(("u_ave", dict(central=central, post_func=post), 6))
+            cases.append(("x_ave", dict(central=central, xalpha=False, post_func=post), 8 if post is None else 6))
+            cases.append(("u_ave", dict(central=central, post_func=post), 8 if post is None else 6))
         cases.append(("x_ave", dict(central=central, xalpha=True), 4))
     for n in (2, 3):
         cases.append(("dun_ave", dict(n=n, central=True), 5))
@@ -214,9 +218,73 @@ def make_perturb():
     print("perturb.json written")
 
 
+def make_legacy_extrap():
+    """``legacy.ExtrapModel`` (legacy/extrap.py:9-118) trained on the reference's FixtureData."""
+    pkg = sys.modules.get("ref_legacy")
+    if pkg is None:
+        pkg = types.ModuleType("ref_legacy")
+        pkg.__path__ = [str(SRC / "legacy")]
+        sys.modules["ref_legacy"] = pkg
+    for name in ("utilities", "extrap"):
+        spec = importlib.util.spec_from_file_location(f"ref_legacy.{name}", SRC / "legacy" / f"{name}.py")
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[f"ref_legacy.{name}"] = mod
+        spec.loader.exec_module(mod)
+    extrap = sys.modules["ref_legacy.extrap"]
+    rng = np.random.default_rng(0)
+    n, nv, order = 100, 5, 6
+    u = rng.random(n)
+    x = rng.random((n, nv))
+    beta0, betas = 0.5, [0.3, 0.4, 0.55, 0.9]
+    em = extrap.ExtrapModel(maxOrder=order, refB=beta0, xData=x, uData=u)
+    out = {"seed": 0, "n": n, "nv": nv, "order": order, "beta0": beta0, "betas": betas,
+           "derivs": np.asarray(em.params).tolist(),
+           "predict": [np.asarray(em.predict(betas, order=o)).tolist() for o in range(order + 1)],
+           "check_u_sum": float(u.sum()), "check_x_sum": float(x.sum())}
+    (OUT / "legacy_extrap.json").write_text(json.dumps(out))
+    print("legacy_extrap.json written")
+
+
+def make_idealgas():
+    """The reference's ``idealgas.py`` itself (``validate_rng`` is the only shim, install_stubs)."""
+    import thermoextrap.idealgas as ig
+
+    b = np.linspace(0.1, 10, 5)
+    rng = np.random.default_rng(seed=1234)
+    x = rng.random()
+    beta = rng.random()
+    seed = 456
+    xs = ig.x_sample(5, b[:, None], rng=np.random.default_rng(seed))
+    us = ig.u_sample((4, 7), 2.5, 1.3, rng=np.random.default_rng(seed))
+    xd, ud = ig.generate_data((100, 1000), beta, 1.0, rng=np.random.default_rng(seed))
+    out = {
+        "b": b.tolist(), "x": x, "beta": beta, "seed": seed,
+        "x_ave": np.asarray(ig.x_ave(b)).tolist(), "x_ave_vol": np.asarray(ig.x_ave(b, 2.0)).tolist(),
+        "x_var": np.asarray(ig.x_var(b)).tolist(), "x_prob": np.asarray(ig.x_prob(x, b)).tolist(),
+        "u_prob": np.asarray(ig.u_prob(x * 300, 1000, b)).tolist(), "x_cdf": np.asarray(ig.x_cdf(x, b)).tolist(),
+        "x_sample": np.asarray(xs).tolist(), "u_sample": np.asarray(us).tolist(),
+        "generate_data_x": np.asarray(xd).tolist(), "generate_data_u": np.asarray(ud).tolist(),
+        "dbeta_xave": [float(ig.dbeta_xave(k)(1.7, 1.2)) for k in range(7)],
+        "dbeta_xave_minuslog": [float(ig.dbeta_xave_minuslog(k)(1.7, 1.2)) for k in range(7)],
+        "dbeta_xave_depend": [float(ig.dbeta_xave_depend(k)(1.7, 1.2)) for k in range(7)],
+        "dbeta_xave_depend_minuslog": [float(ig.dbeta_xave_depend_minuslog(k)(1.7, 1.2)) for k in range(7)],
+        "dvol_xave": [float(ig.dvol_xave(k)(1.7, 1.2)) for k in range(7)],
+    }
+    betas = np.array([0.7, 1.5, 2.0])
+    for name in ("x_beta_extrap", "x_beta_extrap_minuslog", "x_beta_extrap_depend", "x_beta_extrap_depend_minuslog"):
+        tot, coef = getattr(ig, name)(5, beta0=1.0, beta=betas, vol=1.3)
+        out[name] = {"tot": np.asarray(tot, dtype=float).tolist(), "coef": np.asarray(coef, dtype=float).tolist()}
+    tot, coef = ig.x_vol_extrap(order=5, vol0=0.3, beta=beta, vol=np.array([0.5, 1.0]))
+    out["x_vol_extrap"] = {"tot": np.asarray(tot, dtype=float).tolist(), "coef": np.asarray(coef, dtype=float).tolist()}
+    (OUT / "idealgas.json").write_text(json.dumps(out))
+    print("idealgas.json written")
+
+
 if __name__ == "__main__":
     make_lnpi()
     make_legacy()
     install_stubs()
     make_exprs()
     make_perturb()
+    make_legacy_extrap()
+    make_idealgas()

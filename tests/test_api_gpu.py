@@ -4,5 +4,6 @@ import pytest
 
 from test_api import *  # noqa: F403
 from test_api_models import *  # noqa: F403
+from test_parity_api import *  # noqa: F403
 
 pytestmark = pytest.mark.gpu

@@ -507,14 +507,24 @@ def concat(objs, dim, **_kw) -> DataArray:
     aligned = [o.transpose(*first._dims) for o in objs]
     val = np.stack([o._values for o in aligned], axis=0)
     out = first._replace(val, dims=(dim, *first._dims))
-    # scalar coords that differ between the objects become coords along the new dim
+    # coords that differ between the objects are stacked along the new dim, as xarray.concat does
+    # (scalar coords such as ``beta0`` -> ``(dim,)``; non-index coords such as ``dalpha(alpha)`` ->
+    # ``(dim, alpha)``); index coords must agree, coords missing from some object are dropped
     for k, (cd, cv) in first._coords.items():
-        if cd == () and all(k in o._coords and o._coords[k][0] == () for o in aligned):
-            vals = np.asarray([o._coords[k][1] for o in aligned])
-            if k == dim or not np.all(vals == vals[0]):
-                out._coords[k] = ((dim,), vals)
-            else:
-                out._coords[k] = ((), cv)
+        if not all(k in o._coords and o._coords[k][0] == cd and o._coords[k][1].shape == cv.shape for o in aligned):
+            out._coords.pop(k, None)
+            continue
+        vals = np.stack([np.asarray(o._coords[k][1]) for o in aligned], axis=0)
+        same = all(np.array_equal(v, vals[0]) for v in vals[1:])
+        if cd == (k,):  # dimension (index) coordinate
+            if not same:
+                msg = f"cannot concatenate along new dimension {dim!r}: index coordinate {k!r} differs"
+                raise ValueError(msg)
+            out._coords[k] = (cd, cv)
+        elif k == dim or not same:
+            out._coords[k] = ((dim, *cd), vals)
+        else:
+            out._coords[k] = (cd, cv)
     if coord_vals is not None:
         out._coords[dim] = ((dim,), np.asarray(coord_vals))
     return out

@@ -34,9 +34,9 @@ __global__ void __launch_bounds__(256)
                 if (p == 127) {
                     term *= log(v);
                 } else {
-                    double pw = v;
+                    double pw = 1.0;   // p == 0 -> 1 (sympy never emits it, the ABI accepts it)
                     const int ap = p < 0 ? -p : p;
-                    for (int q = 1; q < ap; ++q) pw *= v;
+                    for (int q = 0; q < ap; ++q) pw *= v;
                     term = p < 0 ? term / pw : term * pw;
                 }
             }
@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(256)
     k_poly_predict(const double* __restrict__ coefs, int np1, int64_t nelem,
                    const double* __restrict__ dalpha, int nalpha, int mode, double* __restrict__ out) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int a = blockIdx.y;
     if (e >= nelem) return;
+    for (int a = blockIdx.y; a < nalpha; a += gridDim.y) {   // any nalpha: grid.y is capped at 65535
     const double d = dalpha[a];
     double pw = 1.0, acc = 0.0;
     for (int p = 0; p < np1; ++p) {
@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(256)
         pw *= d;
     }
     if (mode == 0) out[(int64_t)a * nelem + e] = acc;
+    }
 }
 
 }  // namespace txb
@@ -86,10 +87,10 @@ extern "C" int txb_eval_exprs_f64(const double* vars, int64_t nelem, int nexpr, 
 extern "C" int txb_poly_predict_f64(const double* coefs, int np1, int64_t nelem, const double* dalpha,
                                     int nalpha, int mode, double* out, void* stream) {
     TXB_CHECK_ARG(coefs && dalpha && out, "txb_poly_predict_f64: null pointer");
-    TXB_CHECK_ARG(np1 >= 1 && nalpha >= 0 && nalpha <= 65535 && mode >= 0 && mode <= 2,
+    TXB_CHECK_ARG(np1 >= 1 && nalpha >= 0 && mode >= 0 && mode <= 2,
                   "txb_poly_predict_f64: bad sizes/mode");
     if (nelem == 0 || nalpha == 0) return TXB_OK;
-    const dim3 grid((unsigned)((nelem + 255) / 256), (unsigned)nalpha);
+    const dim3 grid((unsigned)((nelem + 255) / 256), (unsigned)(nalpha < 65535 ? nalpha : 65535));
     k_poly_predict<<<grid, 256, 0, (cudaStream_t)stream>>>(coefs, np1, nelem, dalpha, nalpha, mode, out);
     TXB_CUDA_LAUNCH_CHECK("k_poly_predict");
     return TXB_OK;

@@ -4,14 +4,25 @@
 //   convert       central <-> raw, .cmom()                (K5)
 // All are latency/launch bound (report us, not roofline %).
 #include "txb_common.cuh"
+#include <mutex>
 
 namespace txb {
 
 __constant__ double c_binom[TXB_MAXK + 2][TXB_MAXK + 2];
-static bool g_binom_ready = false;
+// __constant__ memory is per device (and per context): readiness is tracked per device, under a lock
+// (a C-ABI caller may drive several GPUs from one process, or call from several threads)
+static std::mutex g_binom_mu;
+static bool g_binom_ready[64] = {};
 
 static int ensure_binom() {
-    if (g_binom_ready) return TXB_OK;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("ensure_binom: cudaGetDevice failed or device index %d out of range", dev);
+        cudaGetLastError();
+        return TXB_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(g_binom_mu);
+    if (g_binom_ready[dev]) return TXB_OK;
     static double h[TXB_MAXK + 2][TXB_MAXK + 2];
     for (int n = 0; n < TXB_MAXK + 2; ++n)
         for (int k = 0; k < TXB_MAXK + 2; ++k)
@@ -20,7 +31,7 @@ static int ensure_binom() {
         set_error("cudaMemcpyToSymbol(c_binom) failed");
         return TXB_ERR_CUDA;
     }
-    g_binom_ready = true;
+    g_binom_ready[dev] = true;
     return TXB_OK;
 }
 

@@ -88,6 +88,32 @@ __global__ void __launch_bounds__(256) k_dmma16816_peak(int iters, double seed, 
     for (int i = 0; i < NACC; ++i) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
     if (s == 123.456) out[0] = s;
 }
+// int8 tensor-core form reachable with mma.sync (IMMA m16n8k32, u8 x s8 -> s32): the rate an exact
+// integer-sliced (Ozaki-style) version of the bootstrap contraction could issue at without tcgen05.
+__global__ void __launch_bounds__(256) k_imma16832_peak(int iters, double seed, double* out) {
+    constexpr int NACC = 8;
+    int c[NACC][4];
+    unsigned a[4], b[2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a[k] = 0x01020304u * (threadIdx.x + k + 1) + (unsigned)seed;
+    b[0] = 0x7f01fe02u + threadIdx.x, b[1] = 0x03fd04fcu ^ threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < NACC; ++i)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c[i][k] = i + k;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < NACC; ++i)
+            asm volatile(
+                "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                : "+r"(c[i][0]), "+r"(c[i][1]), "+r"(c[i][2]), "+r"(c[i][3])
+                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+    }
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < NACC; ++i) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+    if (s == 123456789) out[0] = s;
+}
 // Shared-memory atomic throughput with returned values on spread addresses: the slot reservation of
 // k_bucket_scatter (one atomicAdd on tail[bucket] per draw, ~1200-1500 buckets, result needed).
 __global__ void __launch_bounds__(512) k_smem_atomic_peak(int iters, unsigned mask, unsigned* out) {
@@ -138,9 +164,12 @@ extern "C" int txb_fp64_tile_peak_launch(int iters, int blocks_per_sm, int tile,
     } else if (tile == 2) {  // DMMA m8n8k4: 512 flops per warp instruction, 8 per iteration
         txb::k_dmma884_peak<<<nb, 256, 0, (cudaStream_t)stream>>>(iters, 1.0, scratch);
         per_thread = 8.0 * 512.0 / 32.0;
-    } else {                 // DMMA m16n8k16: 4096 flops per warp instruction, 4 per iteration
+    } else if (tile == 3) {  // DMMA m16n8k16: 4096 flops per warp instruction, 4 per iteration
         txb::k_dmma16816_peak<<<nb, 256, 0, (cudaStream_t)stream>>>(iters, 1.0, scratch);
         per_thread = 4.0 * 4096.0 / 32.0;
+    } else {                 // IMMA m16n8k32 (u8 x s8): 8192 integer ops per warp instruction, 8 per iteration
+        txb::k_imma16832_peak<<<nb, 256, 0, (cudaStream_t)stream>>>(iters, 1.0, scratch);
+        per_thread = 8.0 * 8192.0 / 32.0;
     }
     TXB_CUDA_LAUNCH_CHECK("k_fp64_tile_peak");
     *flops = per_thread * (double)iters * 256.0 * (double)nb;

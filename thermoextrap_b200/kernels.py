@@ -541,6 +541,8 @@ def sampler_resample(src, x, u, nrep: int | None = None, order: int = 1, w=None,
     # kernels launched: pivot x2, pack, [count, scan, iter_scan, locate], then
     # gather + finalize, or scatter + consume + sum_parts x2 + finalize + status note (per window)
     launch_count += 3 + (0 if prepared else 4) + (6 if flag & 32 else 2)
+    if flag & 4:  # the in-call counting pass found fewer accepted draws than nrep * nsamp: sums are incomplete
+        raise _lib.TxbError("txb_sampler_resample_f64: raw-draw range estimate too short (report this)")
     if buckets and flag & 24:  # a bucket list / ring overflowed its margin: redo by gathering
         return sampler_resample(src if plan is None else plan, x, u, nrep, order, w=w, x_is_u=x_is_u, nsamp=nsamp,
                                 sync_rng=False, reps=reps, buckets=False)

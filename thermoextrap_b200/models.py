@@ -337,9 +337,16 @@ class Derivatives(MyAttrsMixin):
         if order is None:
             msg = "must specify order or data"
             raise ValueError(msg)
+        out = None
         if self.exprs is not None and self.args is not None:
-            out = self._program(order)(*args)
-        else:
+            try:
+                out = self._program(order)(*args)
+            except NotImplementedError:
+                # not a polynomial / log expression in Symbols and Indexed entries (a user's
+                # Derivatives.from_sympy may hold anything): evaluate the lambdified functions
+                # as the reference does (models.py:371)
+                out = None
+        if out is None:
             out = [self.funcs[i](*args) for i in range(order + 1)]
         if minus_log:
             out = self._apply_minus_log(X=out, order=order)
