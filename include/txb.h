@@ -194,6 +194,20 @@ int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t n
                      int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
                      int64_t* raw_used, int* status, int prepared, void* workspace, size_t ws_bytes,
                      void* stream);
+/* Column-range form for SAMPLE-SHARDED bootstraps (reference semantics data.py:1751-1813
+ * with the samples of one state split over ranks): only draws whose index lies in [col_lo, col_hi) are counted;
+ * freq[rep_hi - rep_lo, ldf >= col_hi - col_lo] holds those columns (column c of the table = sample col_lo + c).
+ * col_lo must be a multiple of TXB_FREQ_BUCKET; uint8 / uint16 tables on the bucketed path only (else
+ * TXB_ERR_UNSUPPORTED: build the full table and slice it).  A column range cannot verify "every row sums to nsamp"
+ * on its own, so rowsum[rep_hi - rep_lo] (int64, device) receives the sums of the first sum_cols columns of every
+ * row: ranks whose ranges overlap (a range starts at the bucket boundary below the rank's first sample) each pass
+ * the width up to the next rank's start, the caller adds the sums over the ranks (one integer all_reduce) and
+ * compares with nsamp -- a wrapped lane still loses 2^bits from that total.                                        */
+enum { TXB_FREQ_BUCKET = 65520 };
+int txb_sampler_freq_cols(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                          int64_t rep_lo, int64_t rep_hi, int64_t col_lo, int64_t col_hi, void* freq,
+                          int freq_dtype, int64_t ldf, int64_t* rowsum, int64_t sum_cols, int* status,
+                          int prepared, void* workspace, size_t ws_bytes, void* stream);
 /* txb_sampler_resample_f64 `flags`: TXB_SAMPLER_PREPARED = the workspace head holds the result of
  * txb_sampler_prepare (or count + scan) for the same (rng, ndat, nrep * nsamp);
  * TXB_SAMPLER_NO_BUCKETS = always use the gather kernel.  With the minimum workspace

@@ -128,10 +128,33 @@ def _resample(x, u, w, has_w, freq, order, binom):
     return out
 
 
+@njit(cache=True, parallel=True)
+def _resample_wide(xt, u, w, has_w, freq, order, binom):
+    # cmomy's gufunc broadcasts over (rep, channel): one independent push loop per pair
+    nrep, nchan = freq.shape[0], xt.shape[0]
+    out = np.zeros((nrep, nchan, 2, order + 1))
+    for rc in prange(nrep * nchan):
+        r, c = rc // nchan, rc % nchan
+        data = out[r, c]
+        x = xt[c]
+        for s in range(u.shape[0]):
+            f = freq[r, s]
+            if f != 0:
+                push_val(x[s], u[s], (w[s] if has_w else 1.0) * f, data, binom)
+    return out
+
+
 def resample_vals(x, u, freq, order, w=None):
-    """``out[rep] = comoments`` of the samples reweighted by ``freq[rep]`` (scalar ``x``)."""
+    """``out[rep] = comoments`` of the samples reweighted by ``freq[rep]`` (scalar ``x[nsamp]``), or
+    ``out[rep, chan]`` for channels ``x[nsamp, nchan]``."""
     has_w = w is not None
     wv = np.ascontiguousarray(w, dtype=np.float64) if has_w else np.zeros(1)
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 2:
+        return _resample_wide(
+            np.ascontiguousarray(x.T), np.ascontiguousarray(u, dtype=np.float64), wv, has_w,
+            np.ascontiguousarray(freq, dtype=np.int64), order, _BINOM,
+        )
     return _resample(
         np.ascontiguousarray(x, dtype=np.float64), np.ascontiguousarray(u, dtype=np.float64), wv, has_w,
         np.ascontiguousarray(freq, dtype=np.int64), order, _BINOM,

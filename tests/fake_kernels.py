@@ -150,29 +150,88 @@ def sampler_resample_wide(src, x, u, nrep=None, order=1, w=None, x_is_u=False, n
 
 
 def reduce_sums(x, u, order, w=None, pivot=None):
-    x, u = _np(x).astype(np.float64), _np(u).astype(np.float64)
+    u = _np(u).astype(np.float64)
+    ww = np.ones(u.shape[0]) if w is None else _np(w)
+    if x is None:  # x_is_u: powers of u (per channel when u is 2-D)
+        u2 = u.reshape(u.shape[0], -1)
+        if pivot is None:
+            pivot = _t(u2[:256].mean(0))
+        du = u2 - _np(pivot)[None, :]
+        pw = du[:, :, None] ** np.arange(order + 1)[None, None, :] * ww[:, None, None]
+        return pivot, _t(pw.sum(0)), None, u.shape[1:]
+    x = _np(x).astype(np.float64)
     val_shape = x.shape[1:]
     x2 = x.reshape(x.shape[0], -1)
     if pivot is None:
         pivot = _t(np.concatenate([x2[:256].mean(0), [u[:256].mean()]]))
     pv = _np(pivot)
     dx, du = x2 - pv[:-1], u - pv[-1]
-    ww = np.ones_like(u) if w is None else _np(w)
     pw = du[:, None] ** np.arange(order + 1)[None, :] * ww[:, None]
     return pivot, _t(pw.sum(0)[None, :]), _t(dx.T @ pw), val_shape
 
 
 def finalize_sums(pivot, S0, S1, order, x_is_u=False, val_shape=()):
-    pv, s0, s1 = _np(pivot), _np(S0), _np(S1)
-    nchan = s1.shape[0]
-    raw = np.zeros((nchan, 2, order + 1))
-    raw[:, 0, :] = s0[0] / s0[0, 0]
-    raw[:, 1, :] = s1 / s0[0, 0]
-    raw[:, 0, 0] = s0[0, 0]
-    out = oc.raw_to_central(raw)
-    out[:, 1, 0] += pv[:-1]
-    out[:, 0, 1] += pv[-1]
-    return _t(out.reshape(*val_shape, 2, order + 1))
+    pv, s0, s1 = _np(pivot), _np(S0), (None if S1 is None else _np(S1))
+    lead = s0.shape[:-2]
+    s0 = s0.reshape(-1, *s0.shape[-2:])
+    outs = []
+    for r in range(s0.shape[0]):
+        if x_is_u:
+            nu = s0.shape[1]
+            m = s0[r] / s0[r, :, :1]                     # raw moments about the pivot, orders 0..order+1
+            raw = np.zeros((nu, 2, order + 2))
+            raw[:, 0, :] = m
+            raw[:, 0, 0] = s0[r, :, 0]
+            cen = oc.raw_to_central(raw)[:, 0, :]        # central moments of u (about its mean), [nu, order+2]
+            out = np.zeros((nu, 2, order + 1))
+            out[:, 0, :] = cen[:, : order + 1]
+            out[:, 1, :] = cen[:, 1:]
+            mean = cen[:, 1] + pv[:nu]
+            out[:, 0, 1] = mean
+            out[:, 1, 0] = mean
+        else:
+            s1r = s1.reshape(-1, *s1.shape[-2:])[r]
+            nchan = s1r.shape[0]
+            raw = np.zeros((nchan, 2, order + 1))
+            raw[:, 0, :] = s0[r, 0] / s0[r, 0, 0]
+            raw[:, 1, :] = s1r / s0[r, 0, 0]
+            raw[:, 0, 0] = s0[r, 0, 0]
+            out = oc.raw_to_central(raw)
+            out[:, 1, 0] += pv[:-1]
+            out[:, 0, 1] += pv[-1]
+        outs.append(out)
+    res = np.stack(outs).reshape(*lead, *val_shape, 2, order + 1)
+    return _t(res)
+
+
+FREQ_BUCKET = 65520
+
+
+def sampler_resample_sums_rows(plan, x_local, u_local, order, row_lo, pivot, w=None, table_bytes=None,
+                               next_row_lo=None):
+    x, u = _np(x_local).astype(np.float64), _np(u_local).astype(np.float64)
+    n_local = u.shape[0]
+    val_shape = x.shape[1:]
+    x2 = x.reshape(n_local, -1)
+    idx = plan._idx
+    pv = _np(pivot)
+    dx, du = x2 - pv[:-1], u - pv[-1]
+    ww = np.ones_like(u) if w is None else _np(w)
+    pw = du[:, None] ** np.arange(order + 1)[None, :] * ww[:, None]
+    nrep = idx.shape[0]
+    S0 = np.zeros((nrep, 1, order + 1))
+    S1 = np.zeros((nrep, x2.shape[1], order + 1))
+    rowsum = np.zeros(nrep, dtype=np.int64)
+    for r in range(nrep):
+        sel = idx[r][(idx[r] >= row_lo) & (idx[r] < row_lo + n_local)] - row_lo
+        f = np.bincount(sel, minlength=n_local).astype(np.float64)
+        S0[r, 0] = f @ pw
+        S1[r] = (dx * f[:, None]).T @ pw
+        # the real kernel counts table columns from the bucket boundary below row_lo up to the next rank's table
+        col_lo = row_lo // FREQ_BUCKET * FREQ_BUCKET
+        nxt = plan.ndat if next_row_lo is None else next_row_lo // FREQ_BUCKET * FREQ_BUCKET
+        rowsum[r] = int(((idx[r] >= col_lo) & (idx[r] < min(nxt, row_lo + n_local))).sum())
+    return _t(S0), _t(S1), val_shape, _t(rowsum)
 
 
 def free_table_bytes() -> int:

@@ -39,3 +39,16 @@ def test_resample_matches_gather():
     out2 = cp.bootstrap_reference_path(x, u, order, nrep, np.random.default_rng(5))
     ref2 = oc.resample_vals_gather(x, u, order, np.random.default_rng(5).choice(n, size=(nrep, n)))
     assert np.all(np.abs(out2 - ref2) <= 1e-9 * np.maximum(np.abs(ref2), oc.tolerance_scale(x, u, order)))
+
+
+def test_resample_wide_matches_gather():
+    """Channels x[nsamp, nchan]: one push loop per (replicate, channel), as cmomy's gufunc broadcasts."""
+    rng = np.random.default_rng(2)
+    n, nv, nrep, order = 300, 3, 5, 4
+    u = rng.normal(0.0, 1.0, n)
+    x = u[:, None] + rng.normal(0.0, 1.0, (n, nv))
+    idx = rng.choice(n, size=(nrep, n), replace=True)
+    out = cp.resample_vals(x, u, cp.indices_to_freq(idx, n), order)
+    ref = oc.resample_vals_gather(x, u, order, idx)
+    assert out.shape == ref.shape == (nrep, nv, 2, order + 1)
+    assert np.all(np.abs(out - ref) <= 1e-9 * np.maximum(np.abs(ref), oc.tolerance_scale(x, u, order)[None]))

@@ -60,6 +60,44 @@ def _worker(rank, world, port, out_dir):
     wref = oc.resample_vals_gather(x, u, order, idx)
     assert wide.shape == wref.shape == (nrep, nv, 2, order + 1)
     assert np.all(np.abs(wide - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
+    # samples sharded bootstrap: every rank keeps the frequency columns of its own rows
+    ss = par.bootstrap_sample_sharded(np.random.default_rng(123), x[lo:hi], u[lo:hi], nrep, order).numpy()
+    assert ss.shape == wref.shape
+    assert np.all(np.abs(ss - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
+    # x_is_u sharded reduce
+    ru = par.reduce_vals_sharded(None, u[lo:hi], order, x_is_u=True).numpy()
+    uref = oc.comoments_two_pass(u, u, order)
+    assert np.all(np.abs(ru.reshape(uref.shape) - uref) <= 1e-9 * np.maximum(np.abs(uref), oc.tolerance_scale(u, u, order)))
+    # ragged / equal row gathers
+    import torch
+
+    full = par.all_gather_rows(torch.from_numpy(x[lo:hi].copy()))
+    assert np.array_equal(full.numpy(), x)
+    # ---- the public API in N-GPU mode: every rank hands in its row shard, every rank gets the full answer
+    import thermoextrap_b200 as xt
+    import thermoextrap_b200.backend as backend
+
+    backend.K = fake_kernels
+    backend.clear_device_cache()
+    par.enable()
+    try:
+        xv = xt.DataArray(x[lo:hi].copy(), dims=("rec", "val"))
+        uv = xt.DataArray(u[lo:hi].copy(), dims=("rec",))
+        data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+        got = data.dxduave.obj.values
+        assert np.all(np.abs(got - ref) <= 1e-9 * np.maximum(np.abs(ref), oc.tolerance_scale(x, u, order)))
+        model = xt.beta.factory_extrapmodel(beta=0.5, data=data)
+        boot = model.resample(sampler={"nrep": nrep, "rng": np.random.default_rng(123)})
+        bv = boot.data.dxduave.obj.values
+        assert bv.shape == wref.shape
+        assert np.all(np.abs(bv - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
+        pred = boot.predict([0.4, 0.6]).values
+        assert pred.shape == (2, nrep, nv) and np.isfinite(pred).all()
+        # an explicit index table over the GLOBAL row numbering
+        b2 = model.resample(sampler={"indices": idx}).data.dxduave.obj.values
+        assert np.all(np.abs(b2 - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
+    finally:
+        par.disable()
     (Path(out_dir) / f"ok{rank}").write_text("ok")
     dist.destroy_process_group()
 

@@ -61,6 +61,8 @@ SIGNATURES = {
     "txb_sampler_indices": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p, _int, _p, _sz, _p]),
     "txb_sampler_freq_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
     "txb_sampler_freq": (_int, [_p, _i64, _i64, _i64, _i64, _i64, _p, _int, _i64, _p, _p, _int, _p, _sz, _p]),
+    "txb_sampler_freq_cols": (
+        _int, [_p, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _p, _int, _i64, _p, _i64, _p, _int, _p, _sz, _p]),
     "txb_sampler_resample_workspace_bytes": (_sz, [_i64, _int, _i64, _i64, _i64]),
     "txb_sampler_resample_fast_workspace_bytes": (_sz, [_i64, _int, _int, _i64, _i64, _i64]),
     "txb_sampler_resample_f64": (

@@ -124,6 +124,18 @@ def clear_device_cache() -> None:
     _dev_cache.clear()
 
 
+# ------------------------------------------------------------------ N-GPU mode (parallel.enable)
+#: ``parallel.DistMode`` once ``parallel.enable()`` ran: the arrays handed to the data classes are then this
+#: rank's ROW SHARD of the sample set (reduce: all_reduce of pivot sums; resample: row shards exchanged once over
+#: NVLink, replicates split over the ranks, slabs gathered -- every rank returns the full result).
+_dist = None
+
+
+def global_rows(n_local: int) -> int:
+    """Number of samples of the whole (possibly rank-sharded) sample set."""
+    return int(n_local) if _dist is None else _dist.global_rows(int(n_local))
+
+
 # ------------------------------------------------------------------ random
 class _Random:
     """``cmomy.random``: a process-global numpy Generator (PCG64)."""
@@ -284,6 +296,8 @@ def factory_sampler(
         nm = mom_ndim or 0
         ax = _axis_of(data, axis, dim, nm)
         ndat = np.shape(_values(data))[ax]
+        if _dist is not None and not nm:   # sample arrays are row shards: the table spans all ranks' rows
+            ndat = _dist.global_rows(ndat)
     if indices is not None or freq is not None:
         return IndexSampler(indices=indices, freq=freq, ndat=ndat)
     if nrep is None or ndat is None:
@@ -294,7 +308,8 @@ def factory_sampler(
     if replace and 2 <= ndat < 2**32 and type(g.bit_generator).__name__ == "PCG64":
         # numpy's own stream, regenerated bit-exactly on the device; `g` is advanced now,
         # exactly as the eager table would have advanced it
-        return IndexSampler(plan=K.SamplerPlan(g, nrep, nsamp, ndat), ndat=ndat)
+        group = {} if _dist is None else {"group": _dist.group}   # the counting pass is split over the ranks
+        return IndexSampler(plan=K.SamplerPlan(g, nrep, nsamp, ndat, **group), ndat=ndat)
     idx = g.choice(ndat, size=(nrep, nsamp), replace=replace)
     return IndexSampler(indices=idx, ndat=ndat)
 
@@ -511,7 +526,10 @@ def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dim
             msg = "mom must be >= 1"
             raise ValueError(msg)
         k = max(m - 1, 1)
-        out = _host(K.reduce_vals(None, xd, k, w=wd, x_is_u=True))
+        if _dist is not None:
+            out = _host(_dist.reduce_vals(None, xd, k, w=wd, x_is_u=True))
+        else:
+            out = _host(K.reduce_vals(None, xd, k, w=wd, x_is_u=True))
         vals = _moments_1d_from_x_is_u(out, m)
         md = _mom_dims_tuple(mom_dims, 1)
         return CentralMomentsData(DataArray(vals, dims=(*rest_dims, *md)), mom_ndim=1, mom_dims=md)
@@ -522,8 +540,12 @@ def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dim
         msg = f"u has dims {extra} that x lacks"
         raise ValueError(msg)
     if u.ndim == 1:
-        out = _host(K.reduce_vals(to_device(np.asarray(x.values, dtype=np.float64)), to_device(np.asarray(u.values, dtype=np.float64)), k, w=wd))
+        xd, ud = to_device(np.asarray(x.values, dtype=np.float64)), to_device(np.asarray(u.values, dtype=np.float64))
+        out = _host(K.reduce_vals(xd, ud, k, w=wd) if _dist is None else _dist.reduce_vals(xd, ud, k, w=wd))
         return CentralMomentsData(DataArray(out, dims=(*rest_dims, *md)), mom_ndim=2, mom_dims=md)
+    if _dist is not None:
+        msg = "N-GPU mode supports u[rec] only"
+        raise NotImplementedError(msg)
     # u carries some of x's other dims (e.g. a leading `rep` dim): batch over those
     shared = tuple(u.dims[1:])
     xt = x.transpose(*shared, dim, ...)
@@ -560,8 +582,9 @@ def wrap_resample_vals(
     x_in_dims = x.dims if is_dataarray(x) else None
     x, u, weight, dim = _prep_samples(x, u, weight, axis, dim)
     sampler = factory_sampler(sampler, data=x, dim=dim)
-    if sampler.ndat != x.sizes[dim]:
-        msg = f"sampler ndat={sampler.ndat} does not match {x.sizes[dim]} samples"
+    nrows = global_rows(x.sizes[dim])
+    if sampler.ndat != nrows:
+        msg = f"sampler ndat={sampler.ndat} does not match {nrows} samples"
         raise ValueError(msg)
     if u.ndim != 1:
         msg = "resampling needs u[rec]"
@@ -585,6 +608,8 @@ WIDE_TABLE_BYTES: int | None = None
 
 def resample_device(xd, ud, wd, sampler: IndexSampler, order: int, x_is_u: bool = False):
     """Route one bootstrap to the best kernel: index gather (scalar x) or freq contraction."""
+    if _dist is not None:
+        return _dist.resample(xd, ud, wd, sampler, order, x_is_u=x_is_u)
     scalar = x_is_u and ud.ndim == 1 or (xd is not None and xd.ndim == 1)
     if scalar and sampler.plan is not None and sampler._freq_dev is None:
         return K.sampler_resample(sampler.plan, xd, ud, order=order, w=wd, x_is_u=x_is_u)

@@ -146,26 +146,34 @@ __device__ __forceinline__ void freq_bump(FT* freq, int64_t off, int& bad) {
 // 1 elsewhere), so the sum of the lanes equals `expect` iff no lane overflowed.
 template <int ES>
 __global__ void __launch_bounds__(1024) k_freq_rowsum_check(const unsigned char* __restrict__ freq, int64_t row_bytes,
-                                                            long long expect, int* __restrict__ status) {
+                                                            long long expect, int* __restrict__ status,
+                                                            long long* __restrict__ sums = nullptr,
+                                                            int64_t len_bytes = -1) {
+    // row_bytes = pitch; len_bytes = leading bytes of every row that are summed (default: the whole pitch)
     const unsigned char* row = freq + (int64_t)blockIdx.x * row_bytes;
+    const int64_t len = len_bytes < 0 ? row_bytes : len_bytes;
     unsigned long long sum = 0;
     auto lanes = [](unsigned w) -> unsigned {
         return ES == 1 ? __dp4a(w, 0x01010101u, 0u) : (w & 0xffffu) + (w >> 16);
     };
-    if ((reinterpret_cast<uintptr_t>(row) & 15) == 0 && row_bytes % 16 == 0) {
+    if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
         const uint4* p = reinterpret_cast<const uint4*>(row);
-        const int64_t n = row_bytes / 16;
+        const int64_t n = len / 16;
         unsigned acc = 0;  // <= expect < 2^31 even before any wrap
         for (int64_t i = threadIdx.x; i < n; i += 1024) {
             const uint4 q = __ldcs(p + i);
             acc += lanes(q.x) + lanes(q.y) + lanes(q.z) + lanes(q.w);
         }
+        for (int64_t i = n * 16 + (int64_t)threadIdx.x * ES; i < len; i += 1024 * ES)   // tail elements
+            acc += ES == 1 ? (unsigned)row[i] : (unsigned)*reinterpret_cast<const unsigned short*>(row + i);
         sum = acc;
     } else {
         const unsigned* p = reinterpret_cast<const unsigned*>(row);
-        const int64_t n = row_bytes / 4;
+        const int64_t n = len / 4;
         unsigned acc = 0;
         for (int64_t i = threadIdx.x; i < n; i += 1024) acc += lanes(__ldcs(p + i));
+        for (int64_t i = n * 4 + (int64_t)threadIdx.x * ES; i < len; i += 1024 * ES)
+            acc += ES == 1 ? (unsigned)row[i] : (unsigned)*reinterpret_cast<const unsigned short*>(row + i);
         sum = acc;
     }
     __shared__ unsigned long long sm[32];
@@ -177,7 +185,9 @@ __global__ void __launch_bounds__(1024) k_freq_rowsum_check(const unsigned char*
         sum = sm[threadIdx.x];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (threadIdx.x == 0 && sum != (unsigned long long)expect) atomicOr(status, 2);
+        // column-range tables (one rank's sample shard) cannot be checked locally: the caller adds the ranks' sums
+        if (threadIdx.x == 0 && sums) sums[blockIdx.x] = (long long)sum;
+        else if (threadIdx.x == 0 && sum != (unsigned long long)expect) atomicOr(status, 2);
     }
 }
 
@@ -911,14 +921,22 @@ extern "C" size_t txb_sampler_freq_workspace_bytes(int64_t ndat, int64_t nrep, i
     return align_up(align_up(p.head_bytes + 256, 256) + sp.per_rep_bytes * (size_t)nrep_out + 8192, 256);
 }
 
-extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
-                                int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
-                                int64_t* raw_used, int* status, int prepared, void* workspace,
-                                size_t ws_bytes, void* stream) {
+// Shared body of txb_sampler_freq (all columns) and txb_sampler_freq_cols (columns [col_lo, col_hi) only:
+// the frequency columns of one rank's sample shard; `freq` then holds col_hi - col_lo columns per row and
+// `rowsum` receives the row sums, which the caller adds over ranks to redo the overflow check).
+static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                             int64_t rep_lo, int64_t rep_hi, int64_t col_lo, int64_t col_hi, void* freq,
+                             int freq_dtype, int64_t ldf, int64_t* raw_used, long long* rowsum, int64_t sum_cols,
+                             int* status, int prepared, void* workspace, size_t ws_bytes, void* stream) {
     TXB_CHECK_ARG(freq != nullptr, "txb_sampler_freq: null pointer");
-    TXB_CHECK_ARG(nrep >= 1 && ldf >= ndat && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
-                  "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld ndat=%lld window [%lld, %lld)", (long long)nrep,
-                  (long long)ldf, (long long)ndat, (long long)rep_lo, (long long)rep_hi);
+    const bool partial = !(col_lo == 0 && col_hi == ndat);
+    const int64_t ncol = col_hi - col_lo;
+    TXB_CHECK_ARG(0 <= col_lo && col_lo < col_hi && col_hi <= ndat && col_lo % BK_HSIZE == 0,
+                  "txb_sampler_freq: column range [%lld, %lld) must lie in [0, ndat) and start at a multiple of %d",
+                  (long long)col_lo, (long long)col_hi, BK_HSIZE);
+    TXB_CHECK_ARG(nrep >= 1 && ldf >= ncol && 0 <= rep_lo && rep_lo < rep_hi && rep_hi <= nrep,
+                  "txb_sampler_freq: bad sizes nrep=%lld ldf=%lld columns=%lld window [%lld, %lld)", (long long)nrep,
+                  (long long)ldf, (long long)ncol, (long long)rep_lo, (long long)rep_hi);
     TXB_CHECK_ARG(freq_dtype >= 0 && freq_dtype <= 3, "txb_sampler_freq: bad freq_dtype %d", freq_dtype);
     static const size_t esz[4] = {8, 4, 2, 1};
     TXB_CHECK_ARG((reinterpret_cast<uintptr_t>(freq) & 3) == 0 && ((ldf * esz[freq_dtype]) & 3) == 0,
@@ -959,21 +977,26 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
         const int64_t nwin = rep_hi - rep_lo;
         int64_t wrep = 0;
         SegPlan sp{};
+        // buckets kept by this call (all of them unless a column range was given); lists are sized for those
+        const int b_lo = (int)(col_lo / BK_HSIZE);
+        const int nbl = (int)((col_hi + BK_HSIZE - 1) / BK_HSIZE) - b_lo;
+        BucketPlan bl = bp;
+        bl.nb = nbl;
         if (bp.ok) {
             wrep = nwin;
-            sp = seg_plan(bp, nsamp, -1, wrep);
+            sp = seg_plan(bl, nsamp, -1, wrep);
             while (wrep > 0 && sp.per_rep_bytes * (size_t)wrep > avail) {
                 const int64_t fit = (int64_t)(avail / sp.per_rep_bytes);
                 wrep = fit < wrep ? fit : wrep - 1;
-                if (wrep > 0) sp = seg_plan(bp, nsamp, -1, wrep);
+                if (wrep > 0) sp = seg_plan(bl, nsamp, -1, wrep);
             }
         }
         if (wrep > 0) {
-            // row padding [ndat, ldf) lies inside the last bucket's slice?  else clear the table as before
-            if (ldf > (int64_t)bp.nb * BK_HSIZE && (rc = zero_table()) != TXB_OK) return rc;
+            // row padding [ncol, ldf) lies inside the last bucket's slice?  else clear the table as before
+            if (ldf > (int64_t)nbl * BK_HSIZE && (rc = zero_table()) != TXB_OK) return rc;
             char* dyn = reinterpret_cast<char*>(workspace) + used;
             unsigned* nlines = reinterpret_cast<unsigned*>(dyn);
-            uint16_t* lists = reinterpret_cast<uint16_t*>(dyn + align_up(sizeof(unsigned) * (size_t)wrep * bp.nb * sp.nseg, 64));
+            uint16_t* lists = reinterpret_cast<uint16_t*>(dyn + align_up(sizeof(unsigned) * (size_t)wrep * nbl * sp.nseg, 64));
             const size_t hist_smem = (size_t)BK_HSIZE * esz[freq_dtype];
             static bool attr_done = false;
             if (!attr_done) {
@@ -989,7 +1012,7 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
                 }
                 attr_done = true;
             }
-            const size_t sc_smem = (size_t)(bp.nb + 1) * (bp.cap * 2 + 12);  // + the ring for rejected draws
+            const size_t sc_smem = (size_t)(nbl + 1) * (bp.cap * 2 + 12);  // + the ring for rejected / foreign draws
             for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
                 const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
                 const int64_t nw = r1 - r0;
@@ -1000,7 +1023,8 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
                 ba.status = status;
                 ba.lists = lists;
                 ba.nlines = nlines;
-                ba.nb = bp.nb;
+                ba.nb = nbl;
+                ba.b_lo = b_lo;
                 ba.cap = bp.cap;
                 ba.cap_lines = sp.cap_lines;
                 ba.nseg = sp.nseg;
@@ -1014,15 +1038,15 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
                 HistArgs h{};
                 h.lists = lists;
                 h.nlines = nlines;
-                h.nb = bp.nb;
+                h.nb = nbl;
                 h.cap_lines = sp.cap_lines;
                 h.nseg = sp.nseg;
                 h.freq = reinterpret_cast<unsigned char*>(freq) + (size_t)(r0 - rep_lo) * ldf * esz[freq_dtype];
                 h.ldf = ldf;
-                h.ndat = ndat;
+                h.ndat = ncol;   // columns are relative to col_lo (a multiple of the bucket size)
                 {
                     ProfScope prof("bucket_hist", st);
-                    const dim3 grid((unsigned)bp.nb, (unsigned)nw);
+                    const dim3 grid((unsigned)nbl, (unsigned)nw);
                     if (freq_dtype == TXB_U16) k_bucket_hist<uint16_t><<<grid, BK_THREADS, hist_smem, st>>>(h);
                     else                       k_bucket_hist<uint8_t><<<grid, BK_THREADS, hist_smem, st>>>(h);
                 }
@@ -1030,6 +1054,11 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
             }
             bucketed = true;
         }
+    }
+    if (!bucketed && partial) {
+        set_error("txb_sampler_freq_cols: a column range needs the bucketed histogram (uint8 / uint16 table, >= %d "
+                  "samples, scratch beyond the sampler head); build the full table and slice it instead", 8 * BK_HSIZE);
+        return TXB_ERR_UNSUPPORTED;
     }
     if (!bucketed && (rc = zero_table()) != TXB_OK) return rc;
     if (!bucketed) switch (freq_dtype) {
@@ -1043,11 +1072,32 @@ extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep
         const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
         const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
         const unsigned rows = (unsigned)(rep_hi - rep_lo);
-        if (freq_dtype == TXB_U16) k_freq_rowsum_check<2><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
-        else                       k_freq_rowsum_check<1><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status);
+        const int64_t len = rowsum ? sum_cols * (int64_t)esz[freq_dtype] : -1;
+        if (freq_dtype == TXB_U16) k_freq_rowsum_check<2><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status, rowsum, len);
+        else                       k_freq_rowsum_check<1><<<rows, 1024, 0, st>>>(f, row_bytes, nsamp, status, rowsum, len);
         TXB_CUDA_LAUNCH_CHECK("k_freq_rowsum_check");
     }
     return TXB_OK;
+}
+
+extern "C" int txb_sampler_freq(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                                int64_t rep_lo, int64_t rep_hi, void* freq, int freq_dtype, int64_t ldf,
+                                int64_t* raw_used, int* status, int prepared, void* workspace,
+                                size_t ws_bytes, void* stream) {
+    return sampler_freq_impl(rng, ndat, nrep, nsamp, rep_lo, rep_hi, 0, ndat, freq, freq_dtype, ldf, raw_used,
+                             nullptr, 0, status, prepared, workspace, ws_bytes, stream);
+}
+
+extern "C" int txb_sampler_freq_cols(const txb_pcg64* rng, int64_t ndat, int64_t nrep, int64_t nsamp,
+                                     int64_t rep_lo, int64_t rep_hi, int64_t col_lo, int64_t col_hi, void* freq,
+                                     int freq_dtype, int64_t ldf, int64_t* rowsum, int64_t sum_cols, int* status,
+                                     int prepared, void* workspace, size_t ws_bytes, void* stream) {
+    TXB_CHECK_ARG(rowsum != nullptr && status != nullptr, "txb_sampler_freq_cols: rowsum and status are required");
+    TXB_CHECK_ARG(sum_cols >= 0 && sum_cols <= col_hi - col_lo, "txb_sampler_freq_cols: sum_cols out of range");
+    TXB_CHECK_ARG(freq_dtype == TXB_U8 || freq_dtype == TXB_U16, "txb_sampler_freq_cols: uint8 / uint16 tables only");
+    return sampler_freq_impl(rng, ndat, nrep, nsamp, rep_lo, rep_hi, col_lo, col_hi, freq, freq_dtype, ldf, nullptr,
+                             reinterpret_cast<long long*>(rowsum), sum_cols, status, prepared, workspace, ws_bytes,
+                             stream);
 }
 
 extern "C" size_t txb_sampler_resample_workspace_bytes(int64_t ndat, int order, int64_t nrep, int64_t nsamp,

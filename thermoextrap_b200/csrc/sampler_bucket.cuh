@@ -54,6 +54,7 @@ struct BucketArgs {
     int nseg;
     int64_t seg_len;      // draws per segment
     int64_t rep_lo;       // first replicate of the window
+    int b_lo;             // first bucket kept (draws of other buckets go to the sink ring): a rank's column range
 };
 
 // exclusive block scan for BK_THREADS threads
@@ -175,8 +176,10 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         }
     };
     auto append = [&](uint32_t v) {
-        const int b = (int)bk_bucket<GEOM>(v);
-        const uint16_t loc = bk_local<GEOM>(v, (uint32_t)b);
+        const uint32_t rb = bk_bucket<GEOM>(v) - (uint32_t)e.b_lo;
+        if (rb >= (uint32_t)nb) return;  // outside this call's column range
+        const int b = (int)rb;
+        const uint16_t loc = bk_local<GEOM>(v, rb + (uint32_t)e.b_lo);
         const unsigned slot = atomicAdd(tail + b, 1u);
         if (slot - head[b] < cap) {
             rings[(size_t)b * cap + (slot & (cap - 1))] = loc;
@@ -238,12 +241,14 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
             uint32_t bk[NSLOT];
 #pragma unroll
             for (int k = 0; k < NSLOT; ++k) {
-                bk[k] = (mask & (1u << k)) ? bk_bucket<GEOM>(val[k]) : (uint32_t)nb;
+                // bucket relative to the kept range; below b_lo it wraps to a huge value -> sink, like a rejected draw
+                const uint32_t rb = bk_bucket<GEOM>(val[k]) - (uint32_t)e.b_lo;
+                bk[k] = ((mask & (1u << k)) && rb < (uint32_t)nb) ? rb : (uint32_t)nb;
                 slot[k] = atomicAdd(tail + bk[k], 1u);
             }
 #pragma unroll
             for (int k = 0; k < NSLOT; ++k)
-                rings[bk[k] * cap + (slot[k] & (cap - 1))] = bk_local<GEOM>(val[k], bk[k]);
+                rings[bk[k] * cap + (slot[k] & (cap - 1))] = bk_local<GEOM>(val[k], bk[k] + (uint32_t)e.b_lo);
         } else {
             int tot;
             const int c = __popc(mask) + (pre_acc ? 1 : 0);

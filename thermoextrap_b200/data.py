@@ -235,7 +235,7 @@ class DataValuesBase(AbstractData):
             msg = "object is already resampled"
             raise ValueError(msg)
         sampler = cm.factory_sampler(sampler, data=self._xv, dim=self.rec_dim)
-        if sampler.nsamp != len(self):
+        if sampler.nsamp != cm.global_rows(len(self)):
             msg = f"indices.sizes[{self.rec_dim}]={sampler.nsamp} must equal {len(self)=}"
             raise ValueError(msg)
         meta = self.meta.resample(

@@ -152,20 +152,25 @@ def reduce_sums(x, u, order: int, w=None, pivot=None):
 
 
 def finalize_sums(pivot, S0, S1, order: int, x_is_u: bool = False, val_shape=()) -> torch.Tensor:
-    """Pivot sums -> comoments ``[*val, 2, order+1]`` (``S0`` carries order+1 powers when ``x_is_u``)."""
+    """Pivot sums -> comoments ``[(nrep,) *val, 2, order+1]`` (``S0`` carries order+1 powers when ``x_is_u``).
+    ``S0[(nrep,) nu, ks+1]``, ``S1[(nrep,) nchan, order+1]``: a leading replicate axis is carried through."""
     global launch_count
     lib = _lib.load()
     dev = device()
+    lead = tuple(S0.shape[:-2])
+    nrep = int(np.prod(lead, dtype=np.int64)) if lead else 1
     nu = S0.shape[-2]
     nchan = S1.shape[-2] if S1 is not None else nu
-    out = torch.empty((nchan, 2, order + 1), dtype=torch.float64, device=dev)
+    S0 = S0.contiguous()
+    S1 = None if S1 is None else S1.contiguous()
+    out = torch.empty((nrep, nchan, 2, order + 1), dtype=torch.float64, device=dev)
     mode = MODE_X_IS_U if x_is_u else MODE_COMOMENTS
     with torch.cuda.device(dev):
-        st = lib.txb_finalize_f64(S0.data_ptr(), _ptr(S1), pivot.data_ptr(), 1, nchan, nu, order, mode,
+        st = lib.txb_finalize_f64(S0.data_ptr(), _ptr(S1), pivot.data_ptr(), nrep, nchan, nu, order, mode,
                                   out.data_ptr(), _stream_ptr())
     check(st, "txb_finalize_f64")
     launch_count += 1
-    return out.reshape(*val_shape, 2, order + 1)
+    return out.reshape(*lead, *val_shape, 2, order + 1)
 
 
 def indices_to_freq(indices, ndat: int | None = None, dtype: torch.dtype = torch.int64) -> torch.Tensor:
@@ -458,6 +463,118 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
         return sampler_freq(plan, dtype=dtype, reps=reps, buckets=False, out=out)
     _sampler_flags(status, "txb_sampler_freq")
     return buf[:, : plan.ndat]
+
+
+FREQ_BUCKET = 65520  # TXB_FREQ_BUCKET: column ranges of txb_sampler_freq_cols start at multiples of this
+
+
+def sampler_freq_cols(plan: SamplerPlan, col_lo: int, col_hi: int, reps=None, dtype: torch.dtype = torch.uint8,
+                      out: torch.Tensor | None = None, sum_cols: int | None = None):
+    """Columns ``[col_lo, col_hi)`` of the plan's frequency table (one rank's sample shard) for the replicate
+    window ``reps``: ``(freq[hi - lo, col_hi - col_lo], rowsum[hi - lo] int64)`` where ``rowsum`` covers the first
+    ``sum_cols`` columns (default all).  ``col_lo`` must be a multiple of :data:`FREQ_BUCKET`; tables too small
+    for the bucketed histogram are built whole and sliced."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    lo, hi = _window(plan, reps)
+    if col_lo % FREQ_BUCKET or not 0 <= col_lo < col_hi <= plan.ndat:
+        msg = f"column range [{col_lo}, {col_hi}) must start at a multiple of {FREQ_BUCKET} inside [0, {plan.ndat})"
+        raise ValueError(msg)
+    esz = torch.empty((), dtype=dtype).element_size()
+    ncol = col_hi - col_lo
+    sum_cols = ncol if sum_cols is None else int(sum_cols)
+    if plan.ndat < 8 * FREQ_BUCKET or esz >= 4:
+        full = sampler_freq(plan, dtype=dtype, reps=(lo, hi))
+        sub = full[:, col_lo:col_hi]
+        return sub, sub[:, :sum_cols].sum(dim=1, dtype=torch.int64)
+    ldf = -(-ncol * esz // 16) * 16 // esz
+    buf = torch.empty((hi - lo, ldf), dtype=dtype, device=dev) if out is None else out[: hi - lo]
+    if buf.shape[1] != ldf or not buf.is_contiguous() or buf.dtype != dtype:
+        msg = f"out must be a contiguous [>= {hi - lo}, {ldf}] tensor of {dtype}"
+        raise ValueError(msg)
+    rowsum = torch.zeros(hi - lo, dtype=torch.int64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        want = lib.txb_sampler_freq_workspace_bytes(plan.ndat, plan.nrep, plan.nsamp, hi - lo)
+        held = _workspaces.get((dev.index or 0, torch.cuda.current_stream().cuda_stream))
+        free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
+        ws = plan.workspace(min(want, free // 3), dev)
+        st = lib.txb_sampler_freq_cols(C.byref(plan.state), plan.ndat, plan.nrep, plan.nsamp, lo, hi, col_lo, col_hi,
+                                       buf.data_ptr(), _FREQ_DTYPES[dtype], ldf, rowsum.data_ptr(), sum_cols,
+                                       status.data_ptr(), _lib.SAMPLER_PREPARED, ws.data_ptr(), ws.numel(),
+                                       _stream_ptr())
+    check(st, "txb_sampler_freq_cols")
+    launch_count += 3
+    flag = int(status.item())
+    if flag & 24:
+        raise _lib.TxbError("txb_sampler_freq_cols: a bucket list / ring overflowed its margin (report this)")
+    return buf[:, :ncol], rowsum
+
+
+def resample_sums(x, u, freq: torch.Tensor, order: int, pivot: torch.Tensor, w=None):
+    """K2 without the re-centring: additive pivot sums ``(S0[nrep, 1, order+1], S1[nrep, nchan, order+1])`` of
+    ``x[nsamp, nchan]``, ``u[nsamp]`` about ``pivot = [cx[nchan], cu]`` reweighted by ``freq[nrep, nsamp]``.  Sums
+    about a common pivot add across sample shards (``all_reduce``); :func:`finalize_sums` re-centres the total."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    if x is None or ldu != 0:
+        msg = "resample_sums needs x[nsamp, *val] and u[nsamp]"
+        raise ValueError(msg)
+    if freq.ndim != 2 or freq.shape[1] != nsamp or freq.stride(1) != 1 or freq.dtype not in _FREQ_DTYPES:
+        msg = f"freq must be an integer [nrep, {nsamp}] table with unit column stride"
+        raise ValueError(msg)
+    nrep, ldf = freq.shape[0], freq.stride(0)
+    S0 = torch.empty((nrep, 1, order + 1), dtype=torch.float64, device=dev)
+    S1 = torch.empty((nrep, nchan, order + 1), dtype=torch.float64, device=dev)
+    ws = _workspace(lib.txb_resample_workspace_bytes(nsamp, nchan, order, nrep), dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_resample_sums_f64(_ptr(x), _ptr(u), _ptr(w), nsamp, nchan, nchan, 0, order, pivot.data_ptr(),
+                                       freq.data_ptr(), _FREQ_DTYPES[freq.dtype], nrep, ldf, S0.data_ptr(),
+                                       S1.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_resample_sums_f64")
+    launch_count += 2
+    return S0, S1, val_shape
+
+
+def sampler_resample_sums_rows(plan: SamplerPlan, x_local, u_local, order: int, row_lo: int, pivot, w=None,
+                               table_bytes: int | None = None, next_row_lo: int | None = None):
+    """Sample-sharded K6 + K2: this rank holds rows ``[row_lo, row_lo + n_local)`` of the plan's sample set.
+    For every replicate window: frequency columns of those rows (:func:`sampler_freq_cols`), contraction against
+    the local rows about the common ``pivot``.  Returns ``(S0[nrep, 1, k+1], S1[nrep, nchan, k+1], val_shape,
+    rowsum[nrep])`` of this shard; the caller ``all_reduce``s the sums, and the ``rowsum``s (int64) too: they
+    must total ``plan.nsamp`` in every replicate (the narrow table's overflow check).  ``next_row_lo`` is the first
+    row of the next rank (``None``: this is the last rank): the table of a rank starts at the bucket boundary at or
+    below its first row, so consecutive ranks overlap there and each counts columns up to the next one's table."""
+    dev = device()
+    xs, us = _as_f64(x_local, dev), _as_f64(u_local, dev)
+    ws_ = None if w is None else _as_f64(w, dev)
+    n_local = us.shape[0]
+    row_hi = row_lo + n_local
+    col_lo = row_lo // FREQ_BUCKET * FREQ_BUCKET
+    ncol = row_hi - col_lo
+    next_col = plan.ndat if next_row_lo is None else next_row_lo // FREQ_BUCKET * FREQ_BUCKET
+    sum_cols = max(0, min(ncol, next_col - col_lo))
+    if table_bytes is None:
+        table_bytes = free_table_bytes()
+    ldf = -(-ncol // 16) * 16
+    win = max(128, int(table_bytes // ldf) // 128 * 128)
+    big = plan.ndat >= 8 * FREQ_BUCKET
+    table = torch.empty((min(win, plan.nrep), ldf), dtype=torch.uint8, device=dev) if big else None
+    nchan = int(np.prod(xs.shape[1:], dtype=np.int64)) if xs.ndim > 1 else 1
+    S0 = torch.empty((plan.nrep, 1, order + 1), dtype=torch.float64, device=dev)
+    S1 = torch.empty((plan.nrep, nchan, order + 1), dtype=torch.float64, device=dev)
+    rowsum = torch.empty(plan.nrep, dtype=torch.int64, device=dev)
+    val_shape: tuple = ()
+    for lo in range(0, plan.nrep, win):
+        hi = min(plan.nrep, lo + win)
+        freq, rs = sampler_freq_cols(plan, col_lo, row_hi, reps=(lo, hi), out=table, sum_cols=sum_cols)
+        rowsum[lo:hi] = rs
+        s0, s1, val_shape = resample_sums(xs, us, freq[:, row_lo - col_lo :], order, pivot, w=ws_)
+        S0[lo:hi], S1[lo:hi] = s0, s1
+    return S0, S1, val_shape, rowsum
 
 
 def check_deferred(statuses: list) -> None:
