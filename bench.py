@@ -1,19 +1,26 @@
-"""Headline benchmark: BASELINE.json config 2 on N B200s (one process per GPU).
+"""Headline benchmark: north_star's target job, ONE job sharded over N B200s (one process per GPU).
 
-workload ("step") = one pass of thermoextrap's hot path over one batch of synthetic samples:
-    K1  order-8 comoment reduction of 1e7 (x, u) samples      (DataCentralMomentsVals.from_vals)
-    K6  the reference sampler's index stream, nrep=1000        (numpy PCG64, regenerated on device)
-    K2  1000-replicate bootstrap of the comoments              (.resample(sampler={"nrep": 1000}))
-    K7  derivative expressions + Taylor predict per replicate  (beta.factory_extrapmodel().predict)
+workload ("step") = one pass of thermoextrap's hot path over one batch of synthetic samples
+(BASELINE.json north_star: order 6, 1e8 samples x 64 observable channels, 1000 bootstrap replicates
+ = one state point of BASELINE config 3):
+    K1  order-6 comoment reduction of x[1e8, 64], u[1e8]         (DataCentralMomentsVals.from_vals)
+    K6  the reference sampler's index stream, nrep = 1000        (numpy PCG64, regenerated on the device)
+    K2  1000-replicate bootstrap of the comoments                (.resample(sampler={"nrep": 1000}))
+    K7  derivative expressions + Taylor predict per replicate    (beta.factory_extrapmodel().predict)  [e2e only]
 
-metric: bootstrap replicates/s (whole job, all ranks).  ``value`` times K1+K6+K2 with samples
-resident in HBM; ``e2e`` times the public API call chain from pinned HOST arrays to HOST
-predictions (H2D + every kernel + K7 + D2H inside the timed region).
+metric: bootstrap replicates/s of the WHOLE job.  N > 1 is STRONG scaling: the same job, K1 sample-sharded
+(all_reduce of pivot sums), the sampler's counting pass split over ranks (integer all_reduce), replicates
+sharded (each rank bootstraps nrep / N replicates of the ONE numpy table), slabs all_gathered.
+``value`` times K1 + K6 + K2 with the samples resident in HBM; ``e2e`` times the public API call chain from pinned
+HOST arrays to HOST predictions (H2D + every kernel + K7 + D2H inside the timed region; with N > 1 every rank
+uploads its 1/N row shard and the shards are exchanged over NVLink).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config target|c2]
 
-``--impl reference`` times the reference's CPU implementation of the same path (numba port of
-cmomy's push algorithm + live numpy sampler, oracle/cmomy_port.py) on the host cores.
+``--config c2`` = BASELINE config 2 (order 8, 1e7 samples, scalar x, nrep 1000: the round-1 headline); its
+record also rides along in the default line (``configs``), with configs 1, 4, 5 (N = 1 only, ``--no-extras`` skips).
+``--impl reference`` times the reference's CPU implementation of the same path (numba port of cmomy's push
+algorithm + live numpy sampler, oracle/cmomy_port.py) on the host cores, on a bounded sample of the workload.
 """
 
 from __future__ import annotations
@@ -23,7 +30,6 @@ import ctypes as C
 import json
 import os
 import statistics
-import subprocess
 import sys
 import threading
 import time
@@ -35,57 +41,105 @@ if str(ROOT) not in sys.path:
 
 METRIC = "bootstrap_replicates_per_s"
 UNIT = "replicates/s"
-NSAMP, ORDER, NREP = 10_000_000, 8, 1000
 BETA0, BETAS = 1.0, [0.9, 0.95, 1.05, 1.1]
+SHAPES = {
+    "target": dict(nsamp=100_000_000, nchan=64, order=6, nrep=1000),
+    "c2": dict(nsamp=10_000_000, nchan=0, order=8, nrep=1000),
+}
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--nsamp", type=int, default=NSAMP, help=argparse.SUPPRESS)
-    ap.add_argument("--nrep", type=int, default=NREP, help=argparse.SUPPRESS)
-    ap.add_argument("--order", type=int, default=ORDER, help=argparse.SUPPRESS)
-    ap.add_argument("--cpu-seconds", type=float, default=15.0, help=argparse.SUPPRESS)
-    ap.add_argument("--no-wide", action="store_true", help="skip the extra wide-x target section (N=1 only)")
-    return ap.parse_args()
+    ap.add_argument("--config", default="target", choices=sorted(SHAPES))
+    ap.add_argument("--nsamp", type=int, default=None, help=argparse.SUPPRESS)
+    ap.add_argument("--nchan", type=int, default=None, help=argparse.SUPPRESS)
+    ap.add_argument("--nrep", type=int, default=None, help=argparse.SUPPRESS)
+    ap.add_argument("--order", type=int, default=None, help=argparse.SUPPRESS)
+    ap.add_argument("--cpu-seconds", type=float, default=6.0, help=argparse.SUPPRESS)
+    ap.add_argument("--e2e-steps", type=int, default=3, help="timed end-to-end steps (each moves the whole sample set over PCIe)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the per-config records (N = 1 only)")
+    ap.add_argument("--no-wide", action="store_true", help=argparse.SUPPRESS)  # round-1 flag, accepted
+    a = ap.parse_args()
+    for k, v in SHAPES[a.config].items():
+        if getattr(a, k) is None:
+            setattr(a, k, v)
+    return a
 
 
 def workload_name(a) -> str:
+    if a.nchan:
+        return (f"north_star target: order-{a.order} comoment reduction + {a.nrep}-replicate bootstrap of "
+                f"{a.nsamp:.0e} samples x {a.nchan} observable channels with the reference sampler's (numpy PCG64) "
+                "index stream (one state point of BASELINE config 3)")
     return (f"C2: beta extrapolation order {a.order}, {a.nsamp:.0e} samples, scalar x, "
             f"bootstrap nrep={a.nrep} with the reference sampler's (numpy PCG64) index stream")
 
 
-def make_samples(n: int, seed: int):
-    """u ~ N(175, 5.3^2), x = 1e-3 u + N(0, 0.02^2)  (notebook statistics)."""
+def config_of(a) -> dict:
+    """Identical for both arms (the driver compares them)."""
+    return {"workload": workload_name(a), "order": a.order, "nsamp": a.nsamp, "nchan": a.nchan, "nrep": a.nrep,
+            "l2": "inputs larger than L2 (samples 51 GB / 160 MB per step; frequency table regenerated every step)"}
+
+
+def make_samples_host(n: int, c: int, seed: int):
+    """u ~ N(175, 5.3^2), x_c = a_c u + N(0, 0.02^2), a_c in [0.5e-3, 2e-3]  (notebook statistics)."""
     import numpy as np
 
     rng = np.random.default_rng(seed)
     u = rng.normal(175.0, 5.3, n)
-    x = 1e-3 * u + rng.normal(0.0, 0.02, n)
+    if not c:
+        return 1e-3 * u + rng.normal(0.0, 0.02, n), u
+    slope = np.linspace(0.5e-3, 2e-3, c)
+    return u[:, None] * slope[None, :] + rng.normal(0.0, 0.02, (n, c)), u
+
+
+def make_samples_device(n: int, c: int, seed: int, dev):
+    """Same distribution, generated on the device (torch Philox) -- identical on every rank for one seed."""
+    import torch
+
+    g = torch.Generator(device=dev).manual_seed(seed)
+    u = torch.empty(n, dtype=torch.float64, device=dev).normal_(175.0, 5.3, generator=g)
+    if not c:
+        x = torch.empty(n, dtype=torch.float64, device=dev).normal_(0.0, 0.02, generator=g)
+        x.add_(u, alpha=1e-3)
+        return x, u
+    slope = torch.linspace(0.5e-3, 2e-3, c, dtype=torch.float64, device=dev)
+    x = torch.empty((n, c), dtype=torch.float64, device=dev)
+    step = 1 << 22
+    for i in range(0, n, step):  # chunked: no second 51 GB temporary
+        xs = x[i : i + step]
+        xs.normal_(0.0, 0.02, generator=g)
+        xs.addcmul_(u[i : i + step, None], slope[None, :])
     return x, u
 
 
-# --------------------------------------------------------------------------- CPU baseline
-def cpu_reference_rate(a, seconds: float):
-    """Reference path on the host cores, bounded sample: full-width samples, few replicates."""
+# --------------------------------------------------------------------------- CPU baseline / reference arm
+def cpu_reference_step(a, seconds: float):
+    """The reference path on the host cores on a BOUNDED sample of the workload: ``n_sub`` of the ``nsamp`` samples
+    (all channels), ``r`` replicates.  One replicate of the full workload costs ``nsamp / n_sub`` sample-replicates,
+    so ``value = r * (n_sub / nsamp) / t`` in replicates/s of the full-size job."""
     import numba
     import numpy as np
 
     from oracle import cmomy_port as cp
 
-    x, u = make_samples(a.nsamp, 0)
+    cores = numba.get_num_threads()
+    n_sub = min(a.nsamp, 1_000_000 if a.nchan else 10_000_000)
+    x, u = make_samples_host(n_sub, a.nchan, 0)
     cp.bootstrap_reference_path(x[:1000], u[:1000], a.order, 2, np.random.default_rng(0))  # JIT
     cp.reduce_vals(x[:1000], u[:1000], a.order)
-    cores = numba.get_num_threads()
-    # calibrate: one replicate per thread, then size the sample for ~`seconds`
+    # calibrate the replicate count for ~`seconds` per step (wide x parallelises over replicate x channel)
+    r0 = 1 if a.nchan else cores
     t0 = time.perf_counter()
-    cp.bootstrap_reference_path(x, u, a.order, cores, np.random.default_rng(1))
-    t1 = time.perf_counter() - t0
-    nrep = max(cores, int(seconds / t1) * cores)
-    nrep = min(nrep, a.nrep)
+    cp.bootstrap_reference_path(x, u, a.order, r0, np.random.default_rng(1))
+    t1 = (time.perf_counter() - t0) / r0
+    nrep = int(max(1, min(a.nrep, seconds / t1)))
+    if not a.nchan:
+        nrep = max(cores, nrep // cores * cores)
 
     def step():
         t0 = time.perf_counter()
@@ -93,28 +147,31 @@ def cpu_reference_rate(a, seconds: float):
         cp.bootstrap_reference_path(x, u, a.order, nrep, np.random.default_rng(1))
         return time.perf_counter() - t0
 
-    return step, nrep, cores
+    sample = (f"{n_sub} of {a.nsamp} samples x {max(a.nchan, 1)} channel(s) x {nrep} of {a.nrep} replicates per step: "
+              "K1 push reduce + numpy choice table + indices_to_freq + K2 freq-weighted push (numba port of cmomy, "
+              f"prange over {'replicate x channel' if a.nchan else 'replicates'}, {cores} threads); rate scaled to "
+              "full-width replicates: value = nrep_step * (n_sub / nsamp) / t")
+    return step, nrep * (n_sub / a.nsamp), cores, sample
 
 
 def run_reference(a) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    step, nrep, cores = cpu_reference_rate(a, a.cpu_seconds)
-    for _ in range(min(a.warmup, 1)):
+    step, units, cores, sample = cpu_reference_step(a, a.cpu_seconds)
+    warm = max(a.warmup, 3)
+    for _ in range(warm):
         step()
     ts = [step() for _ in range(max(1, a.steps))]
     t = sum(ts) / len(ts)
-    value = nrep / t
-    sample = (f"{a.nsamp} samples x {nrep} of {a.nrep} replicates per step: K1 push reduce + numpy "
-              f"choice table + indices_to_freq + K2 freq-weighted push (numba, prange over replicates)")
+    value = units / t
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
-        "steps": len(ts), "warmup": min(a.warmup, 1), "ms_per_step": t * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a), "order": a.order, "nsamp": a.nsamp, "nrep": a.nrep,
-                   "replicates_per_step": nrep},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "steps": len(ts), "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": config_of(a),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "best_value": units / min(ts)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -174,15 +231,121 @@ class ClockSampler:
                 "reasons": reasons}
 
 
+def measured_peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    out = {"hbm_gbs": 6650.0, "bf16_tflops": None, "source": "fallback (B200_PROFILING.md 6.65 TB/s)"}
+    if p.exists():
+        try:
+            d = json.loads(p.read_text())
+            out = {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": d.get("bf16_tflops"),
+                   "bf16_tflops_sustained": d.get("bf16_tflops_sustained"), "source": "measured (MEASURED_PEAKS.json)"}
+        except (KeyError, ValueError):
+            pass
+    return out
+
+
+def fp64_peak_tflops(tile: int = -1) -> float:
+    """fp64 peak measured in this run (MEASURED_PEAKS.json has no fp64 figure): DFMA micro-benchmark, or with
+    ``tile=2`` the DMMA m8n8k4 tensor form (both ~37 TFLOP/s on a B200)."""
+    import torch
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    scratch = torch.zeros(8, dtype=torch.float64, device="cuda")
+    fl = C.c_double()
+    best = 0.0
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if tile < 0:
+            lib.txb_fp64_peak_launch(20000, 8, scratch.data_ptr(), C.byref(fl), None)
+        else:
+            lib.txb_fp64_tile_peak_launch(20000, 4, tile, scratch.data_ptr(), C.byref(fl), None)
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, fl.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
+
+
+def timed_ms(fn, reps: int = 3, warm: int = 1):
+    import torch
+
+    for _ in range(warm):
+        fn()
+    best, out = None, None
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1)
+        best = t if best is None else min(best, t)
+    return best, out
+
+
 # --------------------------------------------------------------------------- B200 arm
+class Job:
+    """Device-resident form of one step on this rank (N = 1: plain kernels; N > 1: the sharded forms)."""
+
+    def __init__(self, a, world, rank, dev):
+        import numpy as np
+
+        from thermoextrap_b200 import kernels as K
+        from thermoextrap_b200 import parallel as par
+
+        self.a, self.world, self.rank, self.K, self.par, self.np = a, world, rank, K, par, np
+        # every rank holds the whole sample set (replicate sharding); generated from ONE seed on every rank
+        self.x, self.u = make_samples_device(a.nsamp, a.nchan, 100, dev)
+        self.lo, self.hi = par.shard_range(a.nsamp, rank, world)
+        self.pending: list = []
+
+    def step(self):
+        a, K, par = self.a, self.K, self.par
+        rng = self.np.random.default_rng(1)
+        if self.world == 1:
+            c = K.reduce_vals(self.x, self.u, a.order)
+            if a.nchan:
+                b = K.sampler_resample_wide(rng, self.x, self.u, a.nrep, a.order)
+            else:
+                b = K.sampler_resample(rng, self.x, self.u, a.nrep, a.order, sync_rng=False, status_out=self.pending)
+            return c, b
+        c = par.reduce_vals_sharded(self.x[self.lo : self.hi], self.u[self.lo : self.hi], a.order)
+        b = par.bootstrap_sharded(rng, self.x, self.u, a.nrep, a.order)
+        return c, b
+
+    def check(self):
+        self.K.check_deferred(self.pending)
+
+
+def kernel_times(lib, job, steps: int, tags) -> dict:
+    """Device time of each kernel family over `steps` more steps, one family bracketed at a time (CUDA events on
+    the launching stream inside libtxb; the hook adds two event records per launch)."""
+    from thermoextrap_b200 import _lib
+
+    out = {}
+    for tag in tags:
+        lib.txb_profile_begin(tag.encode())
+        for _ in range(steps):
+            job.step()
+        ms, nl = C.c_double(), C.c_int()
+        _lib.check(lib.txb_profile_end(C.byref(ms), C.byref(nl)), "txb_profile_end")
+        if nl.value:
+            out[tag] = {"ms_per_step": ms.value / steps, "launches_per_step": nl.value / steps}
+        job.check()
+    return out
+
+
 def run_b200(a) -> None:
     import numpy as np
     import torch
     import torch.distributed as dist
 
+    import thermoextrap_b200 as xt
     from thermoextrap_b200 import _lib, backend
     from thermoextrap_b200 import kernels as K
-    import thermoextrap_b200 as xt
+    from thermoextrap_b200 import parallel as par
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -195,21 +358,7 @@ def run_b200(a) -> None:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     clocks = ClockSampler(local) if rank == 0 else None
-
-    # replicates are independent: rank r bootstraps its own nrep replicates of its own
-    # sample set (weak scaling, no data-path collective)
-    x_np, u_np = make_samples(a.nsamp, seed=100 + rank)
-    xh = torch.from_numpy(x_np).pin_memory()
-    uh = torch.from_numpy(u_np).pin_memory()
-    xd, ud = xh.to(dev), uh.to(dev)
-    rng = np.random.default_rng(1 + rank)
-
-    pending: list = []  # device status words of the timed steps, verified in one go after the region
-
-    def step_device():
-        c = K.reduce_vals(xd, ud, a.order)
-        b = K.sampler_resample(rng, xd, ud, a.nrep, a.order, sync_rng=False, status_out=pending)
-        return c, b
+    wide = bool(a.nchan)
 
     def barrier():
         torch.cuda.synchronize()
@@ -217,300 +366,318 @@ def run_b200(a) -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(a.warmup, 3)):
-        step_device()
+    job = Job(a, world, rank, dev)
+    warm = max(a.warmup, 3)
+    for _ in range(warm):
+        job.step()
     barrier()
-
     if clocks is not None:  # NVML start-up perturbs the GPU: wait until samples are flowing
         t_wait = time.perf_counter()
         while not clocks.rows and time.perf_counter() - t_wait < 5.0:
             time.sleep(0.05)
-    # every rank: the wait above idles the GPU, bring the clocks back up before timing (collectives
-    # must be entered by ALL ranks -- a barrier inside the rank-0 branch deadlocks N > 1)
-    step_device()
-    step_device()
+    job.step()  # every rank: the wait above idles the GPU, bring the clocks back up before timing
     barrier()
     if clocks is not None:
         clocks.rows.clear()
-    K.check_deferred(pending)  # warm-up steps
+    job.check()
     launches0 = K.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
     for _ in range(a.steps):
-        step_device()
+        comom, boot = job.step()
     ev1.record()
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
-    K.check_deferred(pending)   # raises if any timed step overflowed a bucket list / ring (one sync, after timing)
+    job.check()   # raises if any timed step overflowed a bucket list / ring (one sync, after timing)
     launches = K.launch_count - launches0
-    # per-kernel device time of the bootstrap's kernels: same loop again, one family bracketed at a time
-    # (events on the launching stream; the profile hook adds two event records per launch)
-    kernels = {}
-    for tag in ("sampler_count", "bucket_scatter", "bucket_consume", "sampler_gather"):
-        lib.txb_profile_begin(tag.encode())
-        for _ in range(a.steps):
-            step_device()
-        ms, nl = C.c_double(), C.c_int()
-        _lib.check(lib.txb_profile_end(C.byref(ms), C.byref(nl)), "txb_profile_end")
-        if nl.value:
-            kernels[tag] = {"ms_per_step": ms.value / a.steps, "launches_per_step": nl.value / a.steps}
-        K.check_deferred(pending)
+    clock_info = clocks.stop() if clocks else None
 
-    # K1 alone (samples/s) and its kernel time, outside the headline region
-    lib.txb_profile_begin(b"reduce")
-    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    r0.record()
-    for _ in range(a.steps):
-        K.reduce_vals(xd, ud, a.order)
-    r1.record()
+    # size-independent checks of the last step (no oracle can run at this size): every replicate holds exactly
+    # nsamp draws; the replicate means scatter around the sample mean with the standard error sigma / sqrt(n)
+    nv = max(a.nchan, 1)
+    bt = boot.reshape(a.nrep, nv, 2, a.order + 1)
+    ct = comom.reshape(nv, 2, a.order + 1)
+    assert bool((bt[:, :, 0, 0] == float(a.nsamp)).all()), "a replicate's total weight differs from nsamp"
+    sig = ((job.x[: 1 << 20].reshape(-1, nv)).var(dim=0) / a.nsamp).sqrt()
+    z = float(((bt[:, :, 1, 0] - ct[None, :, 1, 0]) / sig[None]).abs().max())
+    assert z < 6.5, f"bootstrap means {z:.1f} standard errors from the sample mean"
+
+    # per-kernel device time (outside the headline region)
+    ksteps = max(1, min(a.steps, 2 if wide else a.steps))
+    tags = ("reduce", "sampler_count", "bucket_scatter", "bucket_hist", "resample") if wide else (
+        "reduce", "sampler_count", "bucket_scatter", "bucket_consume", "sampler_gather")
+    kernels = kernel_times(lib, job, ksteps, tags)
+
+    # ---- end to end through the public API: pinned host arrays in, host predictions out.
+    # N > 1: the API runs in N-GPU mode -- every rank owns (and uploads) its 1/N row shard of the samples
+    lo, hi = job.lo, job.hi
+    xh = torch.empty((hi - lo, a.nchan) if wide else (hi - lo,), dtype=torch.float64).pin_memory()
+    uh = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    xh.copy_(job.x[lo:hi])
+    uh.copy_(job.u[lo:hi])
     torch.cuda.synchronize()
-    t_red = r0.elapsed_time(r1) * 1e-3 / a.steps
-    red_ms, red_n = C.c_double(), C.c_int()
-    lib.txb_profile_end(C.byref(red_ms), C.byref(red_n))
-
-    # ---- end to end through the public API: pinned host arrays in, host predictions out
-    xv = xt.DataArray(xh.numpy(), dims=("rec",))
+    del job.x, job.u, comom, boot, bt, ct   # hand the device-resident copy back before the API leg
+    K._workspaces.clear()
+    torch.cuda.empty_cache()
+    xv = xt.DataArray(xh.numpy(), dims=("rec", "val") if wide else ("rec",))
     uv = xt.DataArray(uh.numpy(), dims=("rec",))
+    if world > 1:
+        par.enable()
 
     def step_e2e():
         backend.clear_device_cache()  # every step uploads its own inputs
         data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=a.order, central=True)
         model = xt.beta.factory_extrapmodel(beta=BETA0, data=data)
-        boot = model.resample(sampler={"nrep": a.nrep, "rng": rng})
-        return model.predict(BETAS).values, boot.predict(BETAS).values
+        b = model.resample(sampler={"nrep": a.nrep, "rng": np.random.default_rng(1)})
+        return model.predict(BETAS).values, b.predict(BETAS).values
 
-    for _ in range(max(a.warmup, 3)):
+    e2e_steps = max(1, min(a.steps, a.e2e_steps)) if wide else a.steps
+    for _ in range(2 if wide else warm):
         pred, pred_boot = step_e2e()
     barrier()
     backend.transfer_bytes.update(h2d=0, d2h=0)
     t0 = time.perf_counter()
-    e2e_steps = []
-    for _ in range(a.steps):
+    per = []
+    for _ in range(e2e_steps):
         ts = time.perf_counter()
         pred, pred_boot = step_e2e()
-        e2e_steps.append(time.perf_counter() - ts)
-    torch.cuda.synchronize()
+        per.append(time.perf_counter() - ts)
+    barrier()
     t_e2e = time.perf_counter() - t0
     if rank == 0:
-        print("e2e ms per step: " + " ".join(f"{1e3 * t:.1f}" for t in e2e_steps), file=sys.stderr)
+        print("e2e ms per step: " + " ".join(f"{1e3 * t:.1f}" for t in per), file=sys.stderr)
     h2d, d2h = backend.transfer_bytes["h2d"], backend.transfer_bytes["d2h"]
-    clock_info = clocks.stop() if clocks else None
     assert pred_boot.shape[:2] == (len(BETAS), a.nrep) and np.isfinite(pred_boot).all()
-
-    times = torch.tensor([t_dev, t_e2e, t_red], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    t_dev, t_e2e, t_red = (float(v) for v in times.tolist())
+        par.disable()
+    backend.clear_device_cache()
+
+    stats = torch.tensor([t_dev, t_e2e, float(h2d), float(d2h)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = stats[:2].clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tot = stats[2:].clone()
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        stats = torch.cat([tmax, tot])
+    t_dev, t_e2e, h2d, d2h = (float(v) for v in stats.tolist())
 
     if rank == 0:
-        emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms.value, red_n.value, launches,
-             h2d // a.steps, d2h // a.steps, clock_info)
+        emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d / e2e_steps, d2h / e2e_steps, clock_info, z, dev)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
-def measured_peaks() -> tuple[float, str]:
-    p = ROOT / "MEASURED_PEAKS.json"
-    if p.exists():
-        try:
-            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        except (KeyError, ValueError):
-            pass
-    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
-
-
-def fp64_peak_tflops() -> float:
-    """DFMA micro-benchmark (MEASURED_PEAKS.json has no fp64 figure)."""
-    import torch
-
-    from thermoextrap_b200 import _lib
-
-    lib = _lib.load()
-    scratch = torch.zeros(8, dtype=torch.float64, device="cuda")
-    fl = C.c_double()
-    best = 0.0
-    for _ in range(3):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        lib.txb_fp64_peak_launch(20000, 8, scratch.data_ptr(), C.byref(fl), None)
-        e1.record()
-        torch.cuda.synchronize()
-        best = max(best, fl.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
-    return best
-
-
-# --------------------------------------------------------------------------- north_star target shape
-def wide_target(n: int = 100_000_000, c: int = 64, k: int = 6, nrep: int = 1000, table_gb: float = 0.0) -> dict:
-    """north_star's target on ONE B200: order-``k`` reduction + ``nrep``-replicate bootstrap of ``n`` samples x ``c``
-    channels (one state point of BASELINE config 3): K1 wide reduce, K6 bucketed histogram per replicate window,
-    K2 DMMA contraction.  Synthetic data generated on the device; checked through size-independent properties."""
-    import numpy as np
-    import torch
-
-    from thermoextrap_b200 import kernels as K
-
-    dev = torch.device("cuda", torch.cuda.current_device())
-    g = torch.Generator(device=dev).manual_seed(2)
-    u = torch.empty(n, dtype=torch.float64, device=dev).normal_(175.0, 5.3, generator=g)
-    slope = torch.linspace(0.5e-3, 2e-3, c, dtype=torch.float64, device=dev)
-    x = torch.empty((n, c), dtype=torch.float64, device=dev)
-    step = 1 << 22
-    for i in range(0, n, step):  # chunked: no second 51 GB temporary
-        xs = x[i : i + step]
-        xs.normal_(0.0, 0.02, generator=g)
-        xs.addcmul_(u[i : i + step, None], slope[None, :])
-    torch.cuda.synchronize()
-
-    def timed(fn, reps=3):
-        best, out = None, None
-        for _ in range(reps):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            out = fn()
-            e1.record()
-            torch.cuda.synchronize()
-            t = e0.elapsed_time(e1)
-            best = t if best is None else min(best, t)
-        return best, out
-
-    K.reduce_vals(x[: 1 << 20], u[: 1 << 20], k)  # warm-up
-    red_ms, base = timed(lambda: K.reduce_vals(x, u, k))
-    red_bytes = 8.0 * n * (c + 1)
-
-    rng = np.random.default_rng(1)
-    t0 = time.perf_counter()
-    plan = K.SamplerPlan(rng, nrep, n)
-    torch.cuda.synchronize()
-    plan_ms = (time.perf_counter() - t0) * 1e3
-
-    timing: dict = {}
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    boot = K.sampler_resample_wide(plan, x, u, order=k, table_bytes=int(table_gb * 1e9) or None, timing=timing)
-    e1.record()
-    torch.cuda.synchronize()
-    boot_ms = e0.elapsed_time(e1)
-
-    # size-independent checks: every replicate holds exactly nsamp draws; the replicate means scatter
-    # around the sample mean with the standard error sigma/sqrt(n)
-    w0 = boot[:, :, 0, 0]
-    assert bool((w0 == float(n)).all()), "a replicate's total weight differs from nsamp"
-    xm, xvar = base[:, 1, 0], x[: 1 << 20].var(dim=0)
-    z = ((boot[:, :, 1, 0] - xm[None]) / (xvar / n).sqrt()[None]).abs().max().item()
-    assert z < 6.5, f"bootstrap means {z:.1f} standard errors from the sample mean"
-    del x, u
-
-    flops = 2.0 * (k + 1) * (c + 1) * n * nrep
-    peak_hbm, src = measured_peaks()
-    peak64 = fp64_peak_tflops()
-    total_ms = red_ms + plan_ms + boot_ms
-    return {
-        "workload": f"order-{k} reduction + {nrep}-replicate bootstrap of {n:.0e} samples x {c} channels (1 B200)",
-        "total_ms": total_ms, "samples_per_s_reduce": n / red_ms * 1e3, "replicates_per_s": nrep / (plan_ms + boot_ms) * 1e3,
-        "reduce": {"ms": red_ms, "GBps": red_bytes / red_ms / 1e6, "frac_hbm": red_bytes / red_ms / 1e6 / peak_hbm,
-                   "peak_source": src},
-        "sampler_plan_ms": plan_ms,
-        "bootstrap": {"ms": boot_ms, "freq_ms": timing["freq_ms"], "contract_ms": timing["contract_ms"],
-                      "windows": timing["windows"], "draws_per_s_freq": nrep * n / timing["freq_ms"] * 1e3,
-                      "contract_tflops": flops / timing["contract_ms"] / 1e9, "fp64_peak_tflops": peak64,
-                      "contract_frac_fp64": flops / timing["contract_ms"] / 1e9 / peak64,
-                      "whole_bootstrap_frac_fp64": flops / boot_ms / 1e9 / peak64,
-                      "whole_job_frac_fp64": flops / total_ms / 1e9 / peak64},
-        "checks": {"weights_exact": True, "max_z_of_replicate_means": z},
-        "gpu": torch.cuda.get_device_name(0),
-    }
-
-
-#: algorithmic HBM bytes per bootstrap draw of each kernel family (DESIGN.md section 4)
 ALG_BYTES_PER_DRAW = {"sampler_gather": 16.0, "bucket_scatter": 2.0, "bucket_consume": 2.0, "sampler_count": 0.0}
-#: DRAM bytes per draw measured by `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum over a 64-replicate
-#: launch = 6.4e8 draws; profiles/r01_bucket_kernels_ncu_full_s21.txt, r01_gather_ncu_full.txt) -> roofline.traffic
+#: DRAM bytes per draw measured by `ncu --set full` (profiles/r01_bucket_kernels_ncu_full_s21.txt, r01_gather_ncu_full.txt)
 NCU_DRAM_BYTES_PER_DRAW = {"bucket_scatter": (0.001503 + 1.255659) * 1e9 / 6.4e8,
                            "bucket_consume": (1.550797 + 0.009994) * 1e9 / 6.4e8,
                            "sampler_count": 0.0, "sampler_gather": 60.0}
-KERNEL_NAMES = {
-    "sampler_gather": "k_sampler<MODE_GATHER> (fused PCG64 sampler + HBM gather + power sums)",
-    "bucket_scatter": "k_bucket_scatter (PCG64 sampler + shared-memory write-combining partition by sample bucket)",
-    "bucket_consume": "k_bucket_consume (per-bucket shared-memory gather + fp64 power sums)",
-    "sampler_count": "k_sampler_count (PCG64 sampler, accepted draws per iteration)",
-}
 
 
-def emit(a, world, t_dev, t_e2e, t_red, kernels, red_ms, red_n, launches, h2d, d2h, clock_info) -> None:
+def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_info, z, dev) -> None:
     import torch
 
-    peak, peak_src = measured_peaks()
-    draws = a.nrep * a.nsamp
+    peaks = measured_peaks()
     step_ms = t_dev / a.steps * 1e3
-    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])  # dominant kernel of the step
-    k_s = kernels[top]["ms_per_step"] * 1e-3 / kernels[top]["launches_per_step"]
-    draws_per_launch = draws / kernels[top]["launches_per_step"]
-    achieved = ALG_BYTES_PER_DRAW[top] * draws_per_launch / k_s / 1e9
-    flops = 4.0 * (a.order + 1) * draws  # 2 (k+1) FMA per draw, scalar x (SURVEY.md 8d)
+    nv = max(a.nchan, 1)
+    wide = bool(a.nchan)
+    flops = 2.0 * (a.order + 1) * (nv + 1) * a.nsamp * a.nrep   # 2 (k+1) (C_u + C_x) per (rep, sample)
     fp64_peak = fp64_peak_tflops()
-    fp64_ms = kernels.get("bucket_consume", kernels.get("sampler_gather"))["ms_per_step"]
-    red_s = red_ms * 1e-3 / max(red_n, 1)
+    shares = {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kernels.items()}
+    if wide:
+        rs = kernels.get("resample", {"ms_per_step": float("nan"), "launches_per_step": 1})
+        per_launch_s = rs["ms_per_step"] * 1e-3 / rs["launches_per_step"]
+        ach = flops / world / (rs["ms_per_step"] * 1e-3) / 1e12   # this rank contracts nrep / world replicates
+        roofline = {
+            "kernel": "k_resample_mma<6, uint8> (K2: frequency table x shifted power products on the fp64 tensor pipe, "
+                      "DMMA.8x8x4)",
+            "bound": "tensor", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak,
+            "peak_source": "fp64 DFMA / DMMA micro-benchmark of this run (txb_fp64_peak_launch; MEASURED_PEAKS.json "
+                           "carries bf16 only, and tcgen05 has no fp64 kind: mma.sync DMMA is the fp64 tensor path)",
+            "algorithmic_flops_per_launch": flops / world / rs["launches_per_step"],
+            "launch_ms": per_launch_s * 1e3, "launches_per_step": rs["launches_per_step"],
+            "share_of_step": rs["ms_per_step"] / step_ms,
+            "traffic": None,
+            "whole_step_frac_fp64": flops / world / (step_ms * 1e-3) / 1e12 / fp64_peak,
+            "kernels": shares,
+        }
+    else:
+        top = max(kernels, key=lambda k: kernels[k]["ms_per_step"] if k != "reduce" else -1.0)
+        k_s = kernels[top]["ms_per_step"] * 1e-3 / kernels[top]["launches_per_step"]
+        draws_per_launch = a.nrep * a.nsamp / world / kernels[top]["launches_per_step"]
+        fp64_ms = kernels.get("bucket_consume", kernels.get("sampler_gather", {"ms_per_step": float("nan")}))["ms_per_step"]
+        roofline = {
+            "kernel": top, "bound": "issue (integer PCG64 + shared-memory atomics), reported against HBM as the contract asks",
+            "achieved": ALG_BYTES_PER_DRAW[top] * draws_per_launch / k_s / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "frac": ALG_BYTES_PER_DRAW[top] * draws_per_launch / k_s / 1e9 / peaks["hbm_gbs"],
+            "peak_source": peaks["source"], "traffic": NCU_DRAM_BYTES_PER_DRAW[top] * draws_per_launch,
+            "launch_ms": k_s * 1e3, "launches_per_step": kernels[top]["launches_per_step"],
+            "share_of_step": kernels[top]["ms_per_step"] / step_ms,
+            "whole_step_frac_fp64": flops / world / (step_ms * 1e-3) / 1e12 / fp64_peak,
+            "fp64": {"achieved_tflops": flops / world / (fp64_ms * 1e-3) / 1e12, "peak_tflops": fp64_peak},
+            "kernels": shares,
+        }
+    red = kernels.get("reduce")
+    red_bytes = 8.0 * a.nsamp * (nv + 1) / world
+    reduce_rec = None
+    if red:
+        red_s = red["ms_per_step"] * 1e-3
+        reduce_rec = {"samples_per_s": a.nsamp / red_s, "kernel_ms_per_step": red["ms_per_step"],
+                      "GBps_per_gpu": red_bytes / red_s / 1e9, "frac_hbm": red_bytes / red_s / 1e9 / peaks["hbm_gbs"]}
     cpu = None
     if world == 1:
-        step, nrep_cpu, cores = cpu_reference_rate(a, a.cpu_seconds)
-        t_cpu = step()
-        cpu = {
-            "value": nrep_cpu / t_cpu, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{a.nsamp} samples x {nrep_cpu} of {a.nrep} replicates, one pass "
-                      f"({t_cpu:.1f} s): numba port of cmomy push reduce + numpy choice + indices_to_freq + "
-                      "freq-weighted push, prange over replicates",
-        }
+        step, units, cores, sample = cpu_reference_step(a, a.cpu_seconds)
+        ts = [step() for _ in range(3)]
+        cpu = {"value": units / min(ts), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": sample + f"; best of 3 passes ({min(ts):.1f} s)"}
+    sharding = ("one GPU" if world == 1 else
+                f"ONE job over {world} GPUs: K1 sample-sharded (all_reduce of pivot sums), sampler counting pass split "
+                "by thread block (integer all_reduce), replicates sharded (nrep / N per rank), slabs all_gathered")
     line = {
-        "metric": METRIC, "value": a.nrep * world * a.steps / t_dev, "unit": UNIT, "n_gpus": world,
-        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": t_dev / a.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {
-            "workload": workload_name(a), "order": a.order, "nsamp": a.nsamp, "nrep": a.nrep,
-            "sharding": "replicates (each rank: own samples, own nrep replicates; no data-path collective)",
-            "l2": "inputs larger than L2 (160 MB of samples per step; 1e10 regenerated draws)",
-            "step": "K1 reduce_vals + K6 device sampler + K2 bootstrap (+finalize), samples resident in HBM",
-        },
-        "e2e": {"value": a.nrep * world * a.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h), "ms_per_step": t_e2e / a.steps * 1e3,
-                "path": "DataCentralMomentsVals.from_vals -> beta.factory_extrapmodel -> .resample({'nrep','rng'}) -> .predict"},
+        "metric": METRIC, "value": a.nrep * a.steps / t_dev, "unit": UNIT, "n_gpus": world,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": step_ms,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {**config_of(a), "sharding": sharding,
+                   "step": "K1 reduce_vals + K6 device sampler (counting pass + frequency windows) + K2 bootstrap "
+                           "(+finalize), samples resident in HBM; a fresh default_rng(1) table every step"},
+        "e2e": {"value": a.nrep * e2e_steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": t_e2e / e2e_steps * 1e3, "steps": e2e_steps,
+                "path": "DataCentralMomentsVals.from_vals -> beta.factory_extrapmodel -> .resample({'nrep','rng'}) -> "
+                        ".predict, from pinned host arrays" + ("" if world == 1 else
+                        f" (parallel.enable(): each rank uploads its 1/{world} row shard, shards all_gathered over NVLink)")},
         "gpu_launches": int(launches),
-        "roofline": {
-            "kernel": KERNEL_NAMES[top],
-            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "peak_source": peak_src, "traffic": NCU_DRAM_BYTES_PER_DRAW[top] * draws_per_launch,
-            "traffic_unit": "bytes per launch (ncu dram read + write per draw x draws of this launch)",
-            "launch_ms": k_s * 1e3,
-            "launches_per_step": kernels[top]["launches_per_step"],
-            "share_of_step": kernels[top]["ms_per_step"] / step_ms,
-            "note": "the partition kernel is instruction-issue bound (integer PCG64 + shared-memory atomics), "
-                    "not HBM bound; its HBM roofline is reported because the contract asks for the dominant kernel",
-            "kernels": {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kernels.items()},
-            "fp64": {"kernel": "bucket_consume" if "bucket_consume" in kernels else "sampler_gather",
-                     "achieved_tflops": flops / (fp64_ms * 1e-3) / 1e12, "peak_tflops": fp64_peak,
-                     "frac": flops / (fp64_ms * 1e-3) / 1e12 / fp64_peak,
-                     "peak_source": "txb_fp64_peak_launch DFMA micro-benchmark, this run"},
-        },
-        "reduce": {"samples_per_s": a.nsamp * world / t_red, "kernel_ms": red_s * 1e3,
-                   "GBps": 16.0 * a.nsamp / red_s / 1e9, "frac_hbm": 16.0 * a.nsamp / red_s / 1e9 / peak},
+        "samples_per_s_reduce": None if not reduce_rec else reduce_rec["samples_per_s"],
+        "roofline": roofline,
+        "reduce": reduce_rec,
+        "checks": {"weights_exact": True, "max_z_of_replicate_means": z},
         "cpu_baseline": cpu,
         "clocks": clock_info,
         "gpu": torch.cuda.get_device_name(0),
     }
-    if world == 1 and not a.no_wide:
-        # north_star's target shape (wide x: bucketed histogram + DMMA contraction), outside the timed region
-        try:
-            from thermoextrap_b200 import backend as _backend
-            from thermoextrap_b200 import kernels as _kernels
-
-            _backend.clear_device_cache()   # hand the headline's buffers back before the 51 GB sample set
-            _kernels._workspaces.clear()
-            torch.cuda.empty_cache()
-            free = torch.cuda.mem_get_info()[0]
-            line["wide_target"] = wide_target(100_000_000 if free > 100e9 else 10_000_000)
-        except Exception as exc:  # noqa: BLE001  (never lose the headline line to the extra section)
-            line["wide_target"] = {"error": repr(exc)}
+    if world == 1 and not a.no_extras:
+        line["configs"] = extra_configs(a, dev)
     print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- the other BASELINE configs (N = 1)
+def extra_configs(a, dev) -> dict:
+    """BASELINE configs 1, 2, 4, 5 as short records beside the headline (each bounded to seconds; outside the
+    timed region).  Config 3 (5 states x nrep 1e4 of the headline shape, ~50x the headline job) runs with
+    tools/config3.py and is recorded under profiles/."""
+    import torch
+
+    from thermoextrap_b200 import backend
+    from thermoextrap_b200 import kernels as K
+
+    out = {}
+    for name, fn in (("c1", config_c1), ("c2", config_c2), ("c4", config_c4), ("c5", config_c5)):
+        if name == a.config:
+            continue
+        try:
+            backend.clear_device_cache()
+            K._workspaces.clear()
+            torch.cuda.empty_cache()
+            out[name] = fn(dev)
+        except Exception as exc:  # noqa: BLE001  (never lose the headline line to an extra record)
+            out[name] = {"error": repr(exc)}
+    return out
+
+
+def config_c1(dev) -> dict:
+    """Ideal-gas beta extrapolation through the public API: order 6, 1e5 samples, scalar x."""
+    import numpy as np
+
+    import thermoextrap_b200 as xt
+    from thermoextrap_b200 import backend
+
+    beta0, order, betas = 5.6, 6, np.array([5.1, 5.5, 5.7, 6.1])
+    xdata, udata = xt.idealgas.generate_data((100_000, 1000), beta0, 1.0, rng=np.random.default_rng(0))
+    xv, uv = xt.DataArray(xdata, dims=("rec",)), xt.DataArray(udata, dims=("rec",))
+
+    def job():
+        backend.clear_device_cache()
+        data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+        return xt.beta.factory_extrapmodel(beta=beta0, data=data).predict(betas).values
+
+    job()
+    ts = []
+    for _ in range(10):
+        t0 = time.perf_counter()
+        pred = job()
+        ts.append(time.perf_counter() - t0)
+    true, _ = xt.idealgas.x_beta_extrap(order, beta0, betas, 1.0)
+    return {"workload": "C1: ideal-gas beta extrapolation, order 6, 1e5 samples, scalar x, from_vals + "
+                        "factory_extrapmodel + predict through the public API (host arrays in, host out)",
+            "ms_per_call": min(ts) * 1e3, "samples_per_s": 1e5 / min(ts),
+            "max_abs_err_vs_analytic": float(np.max(np.abs(pred - true)))}
+
+
+def config_c2(dev) -> dict:
+    """BASELINE config 2 (the round-1 headline): order 8, 1e7 samples, scalar x, nrep 1000."""
+    import argparse as _ap
+
+    from thermoextrap_b200 import _lib
+
+    b = _ap.Namespace(nsamp=10_000_000, nchan=0, order=8, nrep=1000, steps=5, warmup=3)
+    job = Job(b, 1, 0, dev)
+    for _ in range(3):
+        job.step()
+    job.check()
+    ms, _ = timed_ms(lambda: [job.step() for _ in range(5)], reps=2, warm=0)
+    job.check()
+    kern = kernel_times(_lib.load(), job, 3, ("reduce", "sampler_count", "bucket_scatter", "bucket_consume", "sampler_gather"))
+    step_ms = ms / 5
+    flops = 4.0 * 9 * 1e7 * 1000
+    return {"workload": workload_name(b), "ms_per_step": step_ms, "replicates_per_s": 1000 / step_ms * 1e3,
+            "samples_per_s_reduce": None if "reduce" not in kern else 1e7 / (kern["reduce"]["ms_per_step"] * 1e-3),
+            "whole_step_frac_fp64": flops / (step_ms * 1e-3) / 1e12 / fp64_peak_tflops(),
+            "kernels": {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kern.items()}}
+
+
+def config_c4(dev) -> dict:
+    """lnPi width: K1 on uv[rec = 1e6, n = 2000] (x_is_u, order 4) and the extrapolation through
+    lnpi.factory_extrapmodel_lnPi on the reduced moments."""
+    import numpy as np
+    import torch
+
+    import thermoextrap_b200 as xt
+    from thermoextrap_b200 import kernels as K
+
+    n, c, k = 1_000_000, 2000, 4
+    u2 = torch.empty((n, c), dtype=torch.float64, device=dev)
+    col = torch.arange(1, c + 1, device=dev, dtype=torch.float64)
+    for i in range(0, n, 1 << 16):
+        blk = u2[i : i + (1 << 16)]
+        blk.normal_(0.0, 1.0)
+        blk.mul_(0.9 * col.sqrt()).sub_(4.8 * col)
+    ms, out = timed_ms(lambda: K.reduce_vals(None, u2, k, x_is_u=True), reps=5, warm=2)
+    peaks = measured_peaks()
+    gbs = 8.0 * n * c / ms / 1e6
+    # the model: comoments -> DataCentralMoments(x_is_u) -> lnPi extrapolation at 5 betas
+    com = out.cpu().numpy()                                    # [n=2000, 2, k+1]
+    t0 = time.perf_counter()
+    data = xt.DataCentralMoments.from_data(xt.DataArray(np.concatenate([com[:, 0, :], com[:, 1, -1:]], axis=-1),
+                                                        dims=("n", "umom")), x_is_u=True, central=True)
+    lnpi0 = xt.DataArray(-0.5 * (np.arange(c) - c / 2.0) ** 2 / c, dims=("n",))
+    meta = xt.lnpi.lnPiDataCallback(lnpi0, xt.DataArray(np.array([-2.63]), dims=("comp",)), dims_n=["n"], dims_comp="comp")
+    model = xt.lnpi.factory_extrapmodel_lnPi(beta=1.0, data=data.new_like(meta=meta))
+    pred = model.predict([0.9, 0.95, 1.0, 1.05, 1.1]).values
+    t_model = time.perf_counter() - t0
+    assert pred.shape == (5, c) and np.isfinite(pred).all()
+    del u2
+    return {"workload": "C4: lnPi macrostate extrapolation, order 4, 1e6 frames x 2000 macrostate channels",
+            "reduce_ms": ms, "frames_per_s": n / ms * 1e3, "GBps": gbs, "frac_hbm": gbs / peaks["hbm_gbs"],
+            "algorithmic_bytes": 8.0 * n * c, "model_predict_ms": t_model * 1e3}
+
+
+def config_c5(dev) -> dict:
+    """Volume extrapolation, order 1, 1e9 samples STREAMED from pinned host memory in 2^26-sample chunks through a
+    double-buffered H2D ring (volume.factory_extrapmodel's data: <x>, <W>, <xW>, <dxdq>)."""
+    from thermoextrap_b200 import streaming
+
+    return streaming.bench_volume_stream(total=1_000_000_000, chunk=1 << 26, dev=dev, peaks=measured_peaks())
 
 
 def main() -> None:

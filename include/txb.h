@@ -89,6 +89,17 @@ int txb_reduce_vals_f64(const double* x, const double* u, const double* w, int64
                         int64_t nchan, int64_t ldx, int64_t ldu, int order, int mode, double* out,
                         void* workspace, size_t ws_bytes, void* stream);
 
+/* ---- K1, planar channels: x_0[nsamp] .. x_{C-1}[nsamp] as SEPARATE arrays (1 <= C <= 4) next to u[nsamp].
+ * The volume path (reference volume.py:92-134: VolumeDataCallback.dxdq mean; :137-209 factory_extrapmodel's
+ * DataValues.from_vals raw moments) needs <x>, <W>, <xW>, <dxdq> from three per-sample streams; one pass over
+ * all of them (24 B / sample at C = 2) instead of two K1 passes that both read W.  Additive pivot sums about
+ * pivot = [cx_0 .. cx_{C-1}, cu]:  S0[order+1] = sum du^j,  S1[C][order+1] = sum (x_c - cx_c) du^j; feed them
+ * to txb_finalize_f64 (nchan = C, nu = 1).  Arrays must be 16-byte aligned (cp.async.bulk staging).          */
+size_t txb_reduce_planar_workspace_bytes(int nplanes, int order);
+int txb_reduce_sums_planar_f64(const double* const* x_planes, int nplanes, const double* u, int64_t nsamp,
+                               int order, const double* pivot, double* S0, double* S1, void* workspace,
+                               size_t ws_bytes, void* stream);
+
 /* ---- K6: indices -> freq -------------------------------------------------
  * replaces cmomy's indices_to_freq inside factory_sampler
  * (data.py:420-421, 1028-1037, 1344-1352, 1782-1789).  Integer, bit-exact.

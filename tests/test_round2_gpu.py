@@ -1,0 +1,191 @@
+"""Round-2 kernels and paths on the real device, against the oracle (``-m gpu``).
+
+Tolerance: integers bit-exact; fp64 ``|a - b| <= 1e-10 * max(|b|, sigma_x^i sigma_u^j)`` (north_star's rtol
+with the SURVEY.md 8c scale: odd central moments are ~ 0, plain rtol is ill-posed there).
+"""
+
+import numpy as np
+import pytest
+
+from oracle import comoments as oc
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def K():
+    from thermoextrap_b200 import kernels
+
+    return kernels
+
+
+def close(got, ref, scale, tol=TOL):
+    got, ref = np.asarray(got), np.asarray(ref)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    err = np.abs(got - ref) / np.maximum(np.abs(ref), scale)
+    assert err.max() <= tol, f"max scaled error {err.max():.3e}"
+
+
+# ------------------------------------------------------------------ planar K1 (volume path, config 5)
+@pytest.mark.parametrize("n,nplanes,order", [(5000, 1, 1), (100_003, 2, 1), (1_000_000, 2, 3), (300_001, 4, 6), (777, 3, 2)])
+def test_reduce_planar_matches_oracle(K, n, nplanes, order):
+    """txb_reduce_sums_planar_f64 -> txb_finalize_f64 == two-pass longdouble comoments of the stacked planes."""
+    rng = np.random.default_rng(n)
+    u = rng.normal(0.3, 1.1, n)
+    planes = [rng.uniform(0, 1, n) + 0.1 * (c + 1) * u for c in range(nplanes)]
+    pivot, S0, S1 = K.reduce_sums_planar(planes, u, order)
+    out = K.finalize_sums(pivot, S0, S1, order).cpu().numpy()
+    x = np.stack(planes, axis=1)
+    ref = oc.comoments_two_pass(x, u, order)
+    close(out, ref, oc.tolerance_scale(x, u, order))
+    # same thing as the interleaved wide kernel
+    wide = K.reduce_vals(x, u, order).cpu().numpy()
+    close(out, wide, oc.tolerance_scale(x, u, order), tol=1e-11)
+
+
+def test_volume_stream_equals_resident_model_with_drifting_chunks(K):
+    """volume.factory_extrapmodel_stream (double-buffered H2D ring, per-chunk pivots, Chan/Pebay merge) ==
+    volume.factory_extrapmodel on the concatenated samples, with chunk means that drift by many sigma
+    (the case a first-chunk pivot would lose digits on) and ragged chunk sizes."""
+    import thermoextrap_b200 as xt
+
+    rng = np.random.default_rng(3)
+    sizes = [40_000, 65_536, 1, 30_001, 123_457]
+    xs, qs, ws = [], [], []
+    for i, m in enumerate(sizes):
+        w = rng.normal(50.0 * i, 1.0, m)          # mean drifts by 50 sigma per chunk
+        x = rng.uniform(0, 1, m) + 0.1 * w
+        xs.append(x), qs.append(0.5 * x + 0.01 * rng.normal(size=m)), ws.append(w)
+    x, q, w = np.concatenate(xs), np.concatenate(qs), np.concatenate(ws)
+    volume, vols = 2.0, [1.5, 2.0, 2.6]
+    ref_model = xt.volume.factory_extrapmodel(volume=volume, uv=xt.xrwrap_uv(w), xv=xt.DataArray(x, dims=("rec",)),
+                                              dxdqv=xt.DataArray(q, dims=("rec",)), ndim=3, order=1)
+    stream_model = xt.volume.factory_extrapmodel_stream(volume, zip(xs, qs, ws), ndim=3)
+    a, b = stream_model.predict(vols).values, ref_model.predict(vols).values
+    # closed form (volume.py:73-77) in longdouble as the oracle
+    xl, ql, wl = (np.asarray(v, dtype=np.longdouble) for v in (x, q, w))
+    d0 = xl.mean()
+    d1 = (-d0 * wl.mean() + (xl * wl).mean() + ql.mean()) / (volume * 3)
+    oracle = np.array([float(d0 + d1 * (v - volume)) for v in vols])
+    scale = float(abs(d0) + (abs(d0 * wl.mean()) + abs((xl * wl).mean()) + abs(ql.mean())) / (volume * 3))
+    close(a, oracle, scale)
+    close(b, oracle, scale)
+    with pytest.raises(NotImplementedError):
+        stream_model.resample(sampler={"nrep": 3})
+    # value dims go through the wide kernels
+    xs2 = [np.stack([v, 2 * v], axis=1) for v in xs]
+    qs2 = [np.stack([v, -v], axis=1) for v in qs]
+    m2 = xt.volume.factory_extrapmodel_stream(volume, zip(xs2, qs2, ws), ndim=3)
+    p2 = m2.predict(vols).values
+    assert p2.shape == (3, 2)
+    close(p2[:, 0], oracle, scale)
+
+
+# ------------------------------------------------------------------ column-range frequency table (sample sharding)
+@pytest.mark.parametrize("ndat,nrep,cuts", [(700_000, 5, [0, 131_040, 400_000, 700_000]), (1_000_003, 3, [0, 500_001, 1_000_003])])
+def test_sampler_freq_cols_bit_exact(K, ndat, nrep, cuts):
+    """txb_sampler_freq_cols: the columns of one row range of numpy's table, bit-exact, and row sums that add up
+    to nsamp over a partition of the rows (the overflow check of the sample-sharded bootstrap)."""
+    import torch
+
+    g = np.random.default_rng(9)
+    plan = K.SamplerPlan(g, nrep, ndat)
+    ref = oc.indices_to_freq(np.random.default_rng(9).choice(ndat, (nrep, ndat)), ndat)
+    total = torch.zeros(nrep, dtype=torch.int64, device="cuda")
+    for r in range(len(cuts) - 1):
+        row_lo, row_hi = cuts[r], cuts[r + 1]
+        col_lo = row_lo // K.FREQ_BUCKET * K.FREQ_BUCKET
+        nxt = ndat if r == len(cuts) - 2 else cuts[r + 1] // K.FREQ_BUCKET * K.FREQ_BUCKET
+        f, rs = K.sampler_freq_cols(plan, col_lo, row_hi, sum_cols=max(0, min(row_hi, nxt) - col_lo))
+        assert np.array_equal(f.cpu().numpy().astype(np.int64), ref[:, col_lo:row_hi])
+        total += rs
+    assert total.tolist() == [ndat] * nrep
+
+
+def test_sample_sharded_sums_equal_whole(K):
+    """Pivot sums of row shards (each with the frequency columns of its own rows) add up to the sums of the
+    whole sample set: the single-process form of parallel.bootstrap_sample_sharded."""
+    import torch
+
+    rng = np.random.default_rng(4)
+    n, nv, order, nrep = 600_000, 8, 4, 6
+    u = rng.normal(175.0, 5.3, n)
+    x = 1e-3 * u[:, None] + rng.normal(0.0, 0.02, (n, nv))
+    plan = K.SamplerPlan(np.random.default_rng(21), nrep, n)
+    idx = np.random.default_rng(21).choice(n, (nrep, n))
+    pivot, _, _, _ = K.reduce_sums(x[:1024], u[:1024], 1)
+    cuts = [0, 200_000, 333_333, 600_000]
+    tot0 = tot1 = rows = None
+    for r in range(3):
+        nxt = None if r == 2 else cuts[r + 1]
+        S0, S1, val_shape, rs = K.sampler_resample_sums_rows(plan, x[cuts[r]:cuts[r + 1]], u[cuts[r]:cuts[r + 1]], order,
+                                                             cuts[r], pivot, next_row_lo=nxt)
+        tot0 = S0 if tot0 is None else tot0 + S0
+        tot1 = S1 if tot1 is None else tot1 + S1
+        rows = rs if rows is None else rows + rs
+    assert rows.tolist() == [n] * nrep
+    out = K.finalize_sums(pivot, tot0, tot1, order, val_shape=val_shape).cpu().numpy()
+    ref = oc.resample_vals_gather(x, u, order, idx)
+    close(out, ref, oc.tolerance_scale(x, u, order)[None])
+    whole = K.sampler_resample_wide(plan, x, u, order=order).cpu().numpy()
+    close(out, whole, oc.tolerance_scale(x, u, order)[None], tol=1e-11)
+    del torch
+
+
+# ------------------------------------------------------------------ C2's real width against the oracle
+@pytest.mark.parametrize("variant", ["plain", "weighted", "x_is_u"])
+def test_bucketed_bootstrap_at_config2_width_matches_oracle(K, variant):
+    """The headline scalar path (k_bucket_scatter + k_bucket_consume) at BASELINE config 2's own width -- 1e7 samples,
+    order 8 -- for 3 replicates of numpy's table, against the longdouble gather-then-reduce oracle."""
+    n, order, nrep = 10_000_000, 8, 3
+    rng = np.random.default_rng(0)
+    u = rng.normal(175.0, 5.3, n)
+    x = 1e-3 * u + rng.normal(0.0, 0.02, n)
+    w = rng.random(n) + 0.5 if variant == "weighted" else None
+    xis = variant == "x_is_u"
+    idx = np.random.default_rng(5).choice(n, (nrep, n))
+    status: list = []
+    out = K.sampler_resample(np.random.default_rng(5), None if xis else x, u, nrep, order, w=w, x_is_u=xis,
+                             sync_rng=False, status_out=status)
+    flag = int(status[0].item())
+    assert flag & 32 and not flag & 24, f"bucketed path did not run cleanly (status {flag})"
+    ref = oc.resample_vals_gather(u if xis else x, u, order, idx, w=w)
+    close(out.cpu().numpy().reshape(ref.shape), ref, oc.tolerance_scale(u if xis else x, u, order))
+
+
+# ------------------------------------------------------------------ ADVICE r1 fixes in the C ABI
+def test_poly_predict_many_alphas_and_pow_zero(K):
+    rng = np.random.default_rng(1)
+    coefs = rng.normal(size=(4, 3))
+    d = np.linspace(-0.3, 0.3, 70_000)   # > 65535: the grid's y dimension is strided
+    out = K.poly_predict(coefs, d).cpu().numpy()
+    ref = sum(coefs[p][None, :] * d[:, None] ** p for p in range(4))
+    np.testing.assert_allclose(out, ref, rtol=1e-12, atol=1e-15)
+    # factor power 0 evaluates to 1 (not to the variable)
+    v = rng.normal(size=(2, 5))
+    got = K.eval_exprs(v, [0, 1], [2.5], [0, 2], [0, 1], [0, 2]).cpu().numpy()
+    np.testing.assert_allclose(got[0], 2.5 * v[1] ** 2, rtol=1e-14)
+
+
+def test_binomials_per_device(K):
+    """finalize on a second device in the same process must not run with unset binomials."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU")
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    rng = np.random.default_rng(0)
+    data = rng.normal(size=(3, 2, 2, 4))
+    data[..., 0, 0] = 10.0
+    outs = []
+    for d in (0, 1):
+        with torch.cuda.device(d):
+            t = torch.as_tensor(data, device=f"cuda:{d}")
+            o = torch.empty((2, 2, 4), dtype=torch.float64, device=f"cuda:{d}")
+            _lib.check(lib.txb_reduce_data_f64(t.data_ptr(), 3, 2, 3, o.data_ptr(), None), "txb_reduce_data_f64")
+            torch.cuda.synchronize(d)
+            outs.append(o.cpu().numpy())
+    np.testing.assert_array_equal(outs[0], outs[1])

@@ -151,6 +151,39 @@ def reduce_sums(x, u, order: int, w=None, pivot=None):
     return pivot, S0, S1, val_shape
 
 
+def reduce_sums_planar(planes, u, order: int, pivot=None):
+    """K1 pivot sums of PLANAR channels: ``planes`` = 1..4 separate ``x_c[nsamp]`` device arrays next to
+    ``u[nsamp]``; every stream is read once (the volume path's ``(x, dxdq, W)``: 24 B / sample).  Returns
+    ``(pivot[C + 1], S0[1, order+1], S1[C, order+1])`` for :func:`finalize_sums`."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    planes = [_as_f64(p, dev) for p in planes]
+    u = _as_f64(u, dev)
+    n, c = u.shape[0], len(planes)
+    if not 1 <= c <= 4 or any(p.shape != (n,) for p in planes):
+        msg = f"reduce_sums_planar needs 1..4 planes of shape ({n},)"
+        raise ValueError(msg)
+    with torch.cuda.device(dev):
+        if pivot is None:
+            pivot = torch.empty(c + 1, dtype=torch.float64, device=dev)
+            tmp = torch.empty(2, dtype=torch.float64, device=dev)
+            for i, p in enumerate(planes):   # strided-subsample means: [cx_i, cu]
+                check(lib.txb_pivot_f64(p.data_ptr(), u.data_ptr(), n, 1, 1, 0, tmp.data_ptr(), _stream_ptr()),
+                      "txb_pivot_f64")
+                pivot[i : i + 1].copy_(tmp[:1])
+            pivot[c:].copy_(tmp[1:])
+        S0 = torch.empty((1, order + 1), dtype=torch.float64, device=dev)
+        S1 = torch.empty((c, order + 1), dtype=torch.float64, device=dev)
+        ptrs = (C.c_void_p * c)(*[p.data_ptr() for p in planes])
+        ws = _workspace(lib.txb_reduce_planar_workspace_bytes(c, order), dev)
+        st = lib.txb_reduce_sums_planar_f64(ptrs, c, u.data_ptr(), n, order, pivot.data_ptr(), S0.data_ptr(),
+                                            S1.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr())
+    check(st, "txb_reduce_sums_planar_f64")
+    launch_count += 3 + 2 * c
+    return pivot, S0, S1
+
+
 def finalize_sums(pivot, S0, S1, order: int, x_is_u: bool = False, val_shape=()) -> torch.Tensor:
     """Pivot sums -> comoments ``[(nrep,) *val, 2, order+1]`` (``S0`` carries order+1 powers when ``x_is_u``).
     ``S0[(nrep,) nu, ks+1]``, ``S1[(nrep,) nchan, order+1]``: a leading replicate axis is carried through."""

@@ -122,3 +122,43 @@ def factory_extrapmodel(volume, uv, xv, dxdqv, ndim=3, order=1, alpha_name="volu
     data = DataValues.from_vals(uv=uv, xv=xv, order=order, meta=meta, rec_dim=rec_dim, deriv_dim=None, **kws)
     return ExtrapModel(alpha0=volume, data=data, derivatives=factory_derivatives(), order=order, minus_log=False,
                        alpha_name=alpha_name)
+
+
+@attrs.define
+class VolumeMomentsCallback(DataCallbackABC):
+    """``(<dxdq>, volume, ndim)`` for data that was reduced while streaming (no samples are kept, so there is
+    nothing to resample: the same restriction the reference puts on non-``DataValues`` data, volume.py:121-124)."""
+
+    volume: float = field(validator=attv.instance_of(float))
+    dxdq_mean: DataArray = field(validator=attv.instance_of(DataArray))
+    ndim: int = field(default=3, validator=attv.instance_of(int))
+
+    def check(self, data) -> None:
+        pass
+
+    def resample(self, data, meta_kws, sampler, **kws):  # noqa: ARG002
+        msg = "resampling only possible with DataValues style."
+        raise NotImplementedError(msg)
+
+    def derivs_args(self, data, derivs_args):  # noqa: ARG002
+        return (*tuple(derivs_args), self.dxdq_mean, self.volume, self.ndim)
+
+
+def factory_extrapmodel_stream(volume, chunks, ndim=3, order=1, alpha_name="volume", val_dims="val"):
+    """:func:`factory_extrapmodel` for a sample set that is STREAMED: ``chunks`` yields host triples
+    ``(xv[n(, *val)], dxdqv[n(, *val)], uv[n])`` (``uv = beta * virial``); they go through the double-buffered
+    H2D ring of :mod:`.streaming` and only the order-1 moments stay.  Same model, same ``predict``."""
+    from . import streaming
+    from .data import DataCentralMoments
+
+    if order != 1:
+        msg = "only order=1 is supported"
+        raise ValueError(msg)
+    com, dq, _n = streaming.volume_moments_stream(chunks, order)
+    com, dq = cm._host(com), cm._host(dq)
+    vd = () if com.ndim == 2 else ((val_dims,) if isinstance(val_dims, str) else tuple(val_dims))
+    data = DataCentralMoments.from_data(DataArray(com, dims=(*vd, "xmom", "umom")), central=False,
+                                        meta=VolumeMomentsCallback(volume=float(volume), dxdq_mean=DataArray(dq, dims=vd),
+                                                                   ndim=ndim))
+    return ExtrapModel(alpha0=volume, data=data, derivatives=factory_derivatives(), order=order, minus_log=False,
+                       alpha_name=alpha_name)

@@ -48,8 +48,27 @@ scale = torch.as_tensor(np.abs(ref.cpu().numpy()), device=wide.device).clamp_min
 werr = float(((wide - wide1).abs() / torch.maximum(wide1.abs(), scale)).max())
 assert wide.shape == wide1.shape == (nrep_w, nv, 2, order + 1) and werr < 1e-11, werr
 assert gw.bit_generator.state["state"] == gw1.bit_generator.state["state"]
+# samples sharded bootstrap: every rank keeps the frequency columns of its own rows, pivot sums all_reduced
+ss = par.bootstrap_sample_sharded(np.random.default_rng(78), x[lo:hi], u[lo:hi], nrep_w, order)
+serr = float(((ss - wide1).abs() / torch.maximum(wide1.abs(), scale)).max())
+assert ss.shape == wide1.shape and serr < 1e-11, serr
+# the public API in N-GPU mode: row shards in, full result out on every rank
+import thermoextrap_b200 as xt
+
+par.enable()
+xv = xt.DataArray(x[lo:hi].copy(), dims=("rec", "val"))
+uv = xt.DataArray(u[lo:hi].copy(), dims=("rec",))
+data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+aerr = float(np.max(np.abs(data.dxduave.obj.values - ref.cpu().numpy()) / np.maximum(np.abs(ref.cpu().numpy()), 1e-30)))
+assert aerr < 1e-9, aerr
+bapi = xt.beta.factory_extrapmodel(beta=1.0, data=data).resample(sampler={"nrep": nrep_w, "rng": np.random.default_rng(78)})
+bv = torch.as_tensor(bapi.data.dxduave.obj.values, device=wide.device)
+berr = float(((bv - wide1).abs() / torch.maximum(wide1.abs(), scale)).max())
+assert bv.shape == wide1.shape and berr < 1e-11, berr
+par.disable()
 dist.barrier()
 if rank == 0:
+    print(f"sample-sharded bootstrap max err {serr:.1e}; N-GPU API mode: reduce {aerr:.1e}, bootstrap {berr:.1e}")
     print(f"dist_check ok: world={world} sharded reduce max rel err {err:.2e}; sharded bootstrap == single-GPU "
           f"(scalar and wide, wide max err {werr:.1e}); rng state == numpy")
 dist.destroy_process_group()
