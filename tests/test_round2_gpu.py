@@ -35,7 +35,7 @@ def test_reduce_planar_matches_oracle(K, n, nplanes, order):
     u = rng.normal(0.3, 1.1, n)
     planes = [rng.uniform(0, 1, n) + 0.1 * (c + 1) * u for c in range(nplanes)]
     pivot, S0, S1 = K.reduce_sums_planar(planes, u, order)
-    out = K.finalize_sums(pivot, S0, S1, order).cpu().numpy()
+    out = K.finalize_sums(pivot, S0, S1, order, val_shape=(nplanes,)).cpu().numpy()
     x = np.stack(planes, axis=1)
     ref = oc.comoments_two_pass(x, u, order)
     close(out, ref, oc.tolerance_scale(x, u, order))
@@ -71,7 +71,7 @@ def test_volume_stream_equals_resident_model_with_drifting_chunks(K):
     scale = float(abs(d0) + (abs(d0 * wl.mean()) + abs((xl * wl).mean()) + abs(ql.mean())) / (volume * 3))
     close(a, oracle, scale)
     close(b, oracle, scale)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises((NotImplementedError, ValueError)):   # nothing to resample: no samples, no rec dim
         stream_model.resample(sampler={"nrep": 3})
     # value dims go through the wide kernels
     xs2 = [np.stack([v, 2 * v], axis=1) for v in xs]
@@ -109,13 +109,13 @@ def test_sample_sharded_sums_equal_whole(K):
     import torch
 
     rng = np.random.default_rng(4)
-    n, nv, order, nrep = 600_000, 8, 4, 6
+    n, nv, order, nrep = 900_000, 8, 4, 6
     u = rng.normal(175.0, 5.3, n)
     x = 1e-3 * u[:, None] + rng.normal(0.0, 0.02, (n, nv))
     plan = K.SamplerPlan(np.random.default_rng(21), nrep, n)
     idx = np.random.default_rng(21).choice(n, (nrep, n))
     pivot, _, _, _ = K.reduce_sums(x[:1024], u[:1024], 1)
-    cuts = [0, 200_000, 333_333, 600_000]
+    cuts = [0, 300_000, 533_333, 900_000]
     tot0 = tot1 = rows = None
     for r in range(3):
         nxt = None if r == 2 else cuts[r + 1]

@@ -537,6 +537,10 @@ def sampler_freq_cols(plan: SamplerPlan, col_lo: int, col_hi: int, reps=None, dt
                                        buf.data_ptr(), _FREQ_DTYPES[dtype], ldf, rowsum.data_ptr(), sum_cols,
                                        status.data_ptr(), _lib.SAMPLER_PREPARED, ws.data_ptr(), ws.numel(),
                                        _stream_ptr())
+    if st == 2:  # TXB_ERR_UNSUPPORTED: this table does not qualify for the bucketed histogram -> whole table, sliced
+        full = sampler_freq(plan, dtype=dtype, reps=(lo, hi))
+        sub = full[:, col_lo:col_hi]
+        return sub, sub[:, :sum_cols].sum(dim=1, dtype=torch.int64)
     check(st, "txb_sampler_freq_cols")
     launch_count += 3
     flag = int(status.item())
@@ -594,8 +598,7 @@ def sampler_resample_sums_rows(plan: SamplerPlan, x_local, u_local, order: int, 
         table_bytes = free_table_bytes()
     ldf = -(-ncol // 16) * 16
     win = max(128, int(table_bytes // ldf) // 128 * 128)
-    big = plan.ndat >= 8 * FREQ_BUCKET
-    table = torch.empty((min(win, plan.nrep), ldf), dtype=torch.uint8, device=dev) if big else None
+    table = torch.empty((min(win, plan.nrep), ldf), dtype=torch.uint8, device=dev)
     nchan = int(np.prod(xs.shape[1:], dtype=np.int64)) if xs.ndim > 1 else 1
     S0 = torch.empty((plan.nrep, 1, order + 1), dtype=torch.float64, device=dev)
     S1 = torch.empty((plan.nrep, nchan, order + 1), dtype=torch.float64, device=dev)

@@ -103,7 +103,7 @@ def volume_moments_stream(chunks: Iterable, order: int = 1, timing: dict | None 
         nsamp += int(w.shape[0])
         if x.ndim == 1:
             pivot, S0, S1 = K.reduce_sums_planar([x, q], w, order)
-            com = K.finalize_sums(pivot, S0, S1, order)               # [2, 2, order+1]: plane 0 = x, plane 1 = dxdq
+            com = K.finalize_sums(pivot, S0, S1, order, val_shape=(2,))  # [2, 2, order+1]: plane 0 = x, plane 1 = dxdq
             blocks_x.append(com[0])
             blocks_q.append(com[1])
         else:
