@@ -89,6 +89,20 @@ int txb_reduce_vals_f64(const double* x, const double* u, const double* w, int64
                         int64_t nchan, int64_t ldx, int64_t ldu, int order, int mode, double* out,
                         void* workspace, size_t ws_bytes, void* stream);
 
+/* txb_reduce_vals_static_f64: txb_reduce_vals_f64 WITHOUT a workspace argument and without any allocation.
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch is a file-scope
+ * `static __device__` array of TXB_STATIC_SCRATCH_BYTES (16 MiB) inside the library, held by every GPU that
+ * loads the library until the process exits; shapes whose txb_reduce_workspace_bytes() exceeds it are rejected
+ * with TXB_ERR_WORKSPACE (16 MiB covers scalar x at any order and 64 channels at order 6; 2000 channels do not
+ * fit).  Same kernels, same results as txb_reduce_vals_f64.  All calls on a device share the array (it keeps the
+ * last call's contents; nothing needs clearing, every word read is written earlier in the same call): calls that
+ * OVERLAP on the GPU -- two streams, two host threads -- race; serialise them per device.               */
+enum { TXB_STATIC_SCRATCH_BYTES = 16 << 20 };
+int txb_reduce_vals_static_f64(const double* x, const double* u, const double* w, int64_t nsamp,
+                               int64_t nchan, int64_t ldx, int64_t ldu, int order, int mode, double* out,
+                               void* stream);
+
 /* ---- K1, planar channels: x_0[nsamp] .. x_{C-1}[nsamp] as SEPARATE arrays (1 <= C <= 4) next to u[nsamp].
  * The volume path (reference volume.py:92-134: VolumeDataCallback.dxdq mean; :137-209 factory_extrapmodel's
  * DataValues.from_vals raw moments) needs <x>, <W>, <xW>, <dxdq> from three per-sample streams; one pass over

@@ -51,6 +51,7 @@ SIGNATURES = {
         _int,
         [_p, _p, _p, _i64, _i64, _int, _int, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p],
     ),
+    "txb_reduce_vals_static_f64": (_int, [_p, _p, _p, _i64, _i64, _i64, _i64, _int, _int, _p, _p]),
     "txb_reduce_planar_workspace_bytes": (_sz, [_int, _int]),
     "txb_reduce_sums_planar_f64": (_int, [_p, _int, _p, _i64, _int, _p, _p, _p, _p, _sz, _p]),
     "txb_sampler_workspace_bytes": (_sz, [_i64, _i64]),
