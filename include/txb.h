@@ -314,6 +314,14 @@ int txb_fp64_tile_peak_launch(int iters, int blocks_per_sm, int tile, double* sc
 int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double* scratch, double* ops,
                                 void* stream);
 
+/* Which wide-x (> 4 channels) contraction kernel txb_resample_* launches: 0 = register-tiled DFMA,
+ * 1 = k_resample_mma (DMMA, round 1), 2 = k_resample_mma2 (default: operand generation overlapped with the
+ * DMMAs, u-moment row folded into channel tile 0), 3 = k_resample_mma2 with the separate u-moment pass.
+ * Same results within rounding; exists so tests and bench.py can A/B the forms in one process (also
+ * TXB_RESAMPLE_MMA in the environment).  Returns the previous setting; other values only query.  No
+ * counterpart in the reference (data.py:1803-1810 has one cmomy.resample_vals).                     */
+int txb_set_resample_kernel(int version);
+
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",
  * "sampler_count", "sampler_gather"; "reduce_ring" = only the copy-engine-staged reduce

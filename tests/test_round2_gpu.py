@@ -189,3 +189,43 @@ def test_binomials_per_device(K):
             torch.cuda.synchronize(d)
             outs.append(o.cpu().numpy())
     np.testing.assert_array_equal(outs[0], outs[1])
+
+
+# ------------------------------------------------------------------ wide-x contraction kernels, every form
+@pytest.mark.parametrize("version", [0, 1, 2, 3])
+@pytest.mark.parametrize("dtype", ["uint8", "uint16", "int32", "int64"])
+@pytest.mark.parametrize("n,nv,nrep,order,kind", [
+    (1500, 17, 150, 1, "x"), (2111, 64, 130, 6, "x"), (1203, 33, 70, 7, "xw"), (1500, 5, 129, 6, "x"),
+    (900, 16, 9, 8, "x"), (640, 70, 20, 10, "xw"), (1500, 20, 140, 5, "upc"), (777, 9, 66, 7, "upc"),
+])
+def test_wide_contraction_kernel_forms_match_oracle(K, version, dtype, n, nv, nrep, order, kind):
+    """``txb_set_resample_kernel``: the DFMA tile (0), k_resample_mma (1), k_resample_mma2 with the u-moment row
+    folded into channel tile 0 (2, the default) and with the separate u-moment pass (3) all meet the gather
+    oracle: ragged replicate / channel / sample tiles, weights, orders on both sides of the fold limit (7), the
+    per-channel-u form, every table dtype."""
+    import torch
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    rng = np.random.default_rng(21)
+    u = rng.normal(175.0, 5.3, n)
+    x = u[:, None] * np.linspace(0.5e-3, 2e-3, nv)[None, :] + rng.normal(0.0, 0.02, (n, nv))
+    idx = rng.choice(n, (nrep, n), replace=True)
+    freq = K.indices_to_freq(idx, n, dtype=getattr(torch, dtype))
+    sub = sorted({0, 1, nrep // 2, nrep - 2, nrep - 1})
+    prev = lib.txb_set_resample_kernel(version)
+    try:
+        assert lib.txb_set_resample_kernel(-1) == version
+        if kind == "upc":
+            uu = u[:, None] + 50.0 * x
+            out = K.resample_vals(None, uu, freq, order, x_is_u=True).cpu().numpy()
+            ref = oc.resample_vals_gather(uu, uu, order, idx[sub])
+            close(out[sub], ref, oc.tolerance_scale(uu, uu, order))
+            return
+        w = rng.random(n) if kind == "xw" else None
+        out = K.resample_vals(x, u, freq, order, w=w).cpu().numpy()
+        ref = oc.resample_vals_gather(x, u, order, idx[sub], w=w)
+        close(out[sub], ref, oc.tolerance_scale(x, u, order))
+    finally:
+        lib.txb_set_resample_kernel(prev)

@@ -3,6 +3,8 @@
 
 namespace txb {
 
+int g_rs_mma_version = -1;
+
 // ---------------------------------------------------------------- K6
 // freq[r, idx[r, j]] += 1.  Integer work, bit-exact.  Narrow tables are
 // incremented through a 32-bit atomicAdd on the containing word; the old
@@ -99,13 +101,20 @@ extern "C" int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t
     return TXB_OK;
 }
 
+extern "C" int txb_set_resample_kernel(int version) {
+    const int prev = rs_mma_version();
+    if (version >= 0 && version <= 3) g_rs_mma_version = version;
+    return prev;
+}
+
 static size_t rs_partials_doubles(int64_t nsamp, int64_t nchan, int order, int64_t nrep) {
     (void)nsamp;
     const int64_t kp = order + 1;
     const int64_t ch = nchan < 1 ? 1 : nchan;
     // scalar pass: nslab * nrep * 2 (K+1);  wide pass: nslab * nrep * nchan * (K+1)
     const int64_t sc = rs_max_slabs(nrep, 1) * nrep * 2 * kp;
-    const int64_t wd = rs_max_slabs(nrep, (ch + 15) / 16) * nrep * ch * kp;
+    // wide pass: S1 partials + (k_resample_mma2's folded u-moment row) nslab * nrep * (K+1)
+    const int64_t wd = rs_max_slabs(nrep, (ch + 15) / 16) * nrep * (ch + 1) * kp;
     return (size_t)(sc > wd ? sc : wd);
 }
 

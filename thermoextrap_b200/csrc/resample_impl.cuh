@@ -1,6 +1,7 @@
 // Host-side planning + launch of k_resample for one frequency element type.
 #pragma once
 #include "resample_mma_scalar.cuh"
+#include "resample_mma2.cuh"
 #include <cstdlib>
 
 namespace txb {
@@ -70,15 +71,18 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
     return rc;
 }
 
-// wide x on the fp64 tensor cores (k_resample_mma); TXB_RESAMPLE_MMA=0 selects the DFMA tile instead
-inline bool rs_use_mma() {
-    static int v = -1;
-    if (v < 0) {
+// wide x on the fp64 tensor cores.  TXB_RESAMPLE_MMA = 0: DFMA tile; 1: k_resample_mma (round 1);
+// 2 (default): k_resample_mma2 (operand generation overlapped with the DMMAs, S0 folded in);
+// 3: k_resample_mma2 without the S0 fold (separate scalar pass, for A/B timing)
+extern int g_rs_mma_version;   // resample.cu; txb_set_resample_kernel overrides the environment
+inline int rs_mma_version() {
+    if (g_rs_mma_version < 0) {
         const char* e = getenv("TXB_RESAMPLE_MMA");
-        v = (e && e[0] == '0') ? 0 : 1;
+        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 2;
     }
-    return v == 1;
+    return g_rs_mma_version;
 }
+inline bool rs_use_mma() { return rs_mma_version() != 0; }
 
 template <int K, typename FT>
 int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
@@ -108,6 +112,56 @@ int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st)
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma");
     return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
+}
+
+// second form: S0 (when `fold`, orders <= 7, comoment mode) comes out of the same launch
+template <int K, typename FT>
+int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, bool fold, cudaStream_t st) {
+    using C = Rm2Cfg<K, FT>;
+    const RsPlan p = rs_plan(a.nsamp, a.nchan, a.nrep, C::RT, C::ST, C::CT);
+    const bool upc = a.ldu != 0;
+    const int64_t n = a.nrep * a.nchan * (K + 1);
+    const int64_t n0 = a.nrep * (K + 1);
+    fold = fold && C::S0F && !upc;
+    a.ws0 = upc ? ws : ws + p.nslab * n;   // folded S0 partials sit behind the S1 partials
+    a.ws1 = ws;
+    a.slab_len = p.slab_len;
+    const int es = FreqElem<FT>::ES;
+    a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(k_resample_mma2<K, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)C::SMEM) != cudaSuccess) {
+            set_error("k_resample_mma2: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
+            cudaGetLastError();
+            return TXB_ERR_CUDA;
+        }
+        attr_done = true;
+    }
+    const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
+    {
+        ProfScope prof("resample", st);
+        k_resample_mma2<K, FT><<<grid, C::NT, C::SMEM, st>>>(a, fold ? 1 : 0);
+    }
+    TXB_CUDA_LAUNCH_CHECK("k_resample_mma2");
+    int rc = launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
+    if (rc == TXB_OK && fold) rc = launch_sum_parts(a.ws0, p.nslab, n0, S0, st);
+    return rc;
+}
+
+// wide dispatch for > 4 channels.  `s0_done` tells the caller whether S0 still needs the scalar pass.
+template <int K, typename FT>
+int rs_launch_wide_mma(const RsArgs& a, double* S0, double* S1, double* ws, bool want_fold, bool& s0_done,
+                       cudaStream_t st) {
+    s0_done = false;
+    const int v = rs_mma_version();
+    if (v >= 2) {
+        const bool fold = want_fold && v == 2 && Rm2Cfg<K, FT>::S0F;
+        s0_done = fold;
+        return rs_launch_mma2<K, FT>(a, S0, S1, ws, fold, st);
+    }
+    if (v == 1) return rs_launch_mma<K, FT>(a, S0, S1, ws, st);
+    return rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);
 }
 
 // scalar x on DMMA: always for 4- and 8-byte tables (the kernel then waits on the table, not on the FMA
@@ -183,15 +237,18 @@ int resample_sums_ft(const double* x, const double* u, const double* w, int64_t 
             } else if (ldu == 0) {                                                                   \
                 RsArgs b = a;                                                                        \
                 b.x = nullptr; b.nchan = 1; b.ldx = 0; b.pivot = pivot + nchan;                      \
-                rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);                                \
-                if (rc == TXB_OK)                                                                    \
-                    rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                \
-                         : rs_use_mma() ? rs_launch_mma<K, FT>(a, S0, S1, ws, st)                    \
-                                        : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);           \
+                bool s0_done = false;                                                                \
+                if (nchan <= 4) {                                                                    \
+                    rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);                            \
+                    if (rc == TXB_OK) rc = rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st);          \
+                } else {                                                                             \
+                    rc = rs_launch_wide_mma<K, FT>(a, S0, S1, ws, true, s0_done, st);                \
+                    if (rc == TXB_OK && !s0_done) rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);\
+                }                                                                                    \
             } else {                                                                                 \
+                bool s0_done = false;                                                                \
                 rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                    \
-                     : rs_use_mma() ? rs_launch_mma<K, FT>(a, S0, S1, ws, st)                        \
-                                    : rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);               \
+                                : rs_launch_wide_mma<K, FT>(a, S0, S1, ws, false, s0_done, st);      \
             }                                                                                        \
         });                                                                                          \
         return rc;                                                                                   \
