@@ -322,6 +322,12 @@ int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double*
  * counterpart in the reference (data.py:1803-1810 has one cmomy.resample_vals).                     */
 int txb_set_resample_kernel(int version);
 
+/* Threads per CTA of the draw-partition kernel (k_bucket_scatter) behind txb_sampler_resample_f64 and
+ * txb_sampler_freq: 1024 (default; 4 LCG steps per thread and iteration) or 512 (8 steps, round 1).  Identical
+ * output (the lists hold the same draws); exists to A/B the forms in one process (also TXB_SCATTER_THREADS).
+ * Returns the previous setting; other values only query.  No counterpart in the reference.             */
+int txb_set_scatter_threads(int nthreads);
+
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",
  * "sampler_count", "sampler_gather"; "reduce_ring" = only the copy-engine-staged reduce

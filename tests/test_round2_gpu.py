@@ -229,3 +229,40 @@ def test_wide_contraction_kernel_forms_match_oracle(K, version, dtype, n, nv, nr
         close(out[sub], ref, oc.tolerance_scale(x, u, order))
     finally:
         lib.txb_set_resample_kernel(prev)
+
+
+# ------------------------------------------------------------------ partition kernel: 512- and 1024-thread forms
+def test_scatter_thread_forms_agree(K):
+    """``txb_set_scatter_threads``: the 1024-thread partition kernel (4 LCG steps per thread, the default) and the
+    512-thread form (8 steps) walk the same 4096-step iterations of numpy's stream: frequency tables bit-identical
+    (and equal to numpy's own table), scalar bootstrap sums equal to rounding (list order differs)."""
+    import torch
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    prev = lib.txb_set_scatter_threads(-1)
+    try:
+        ndat, nrep = 2_000_003, 4
+        ref = oc.indices_to_freq(np.random.default_rng(17).choice(ndat, size=(nrep, ndat), replace=True), ndat)
+        n2, order = 4_200_000, 6
+        rng = np.random.default_rng(3)
+        u = rng.normal(175.0, 5.3, n2)
+        x = 1e-3 * u + rng.normal(0.0, 0.02, n2)
+        got = {}
+        for nth in (512, 1024):
+            lib.txb_set_scatter_threads(nth)
+            assert lib.txb_set_scatter_threads(-1) == nth
+            f = K.sampler_freq(np.random.default_rng(17), nrep, ndat, ndat, dtype=torch.uint8)
+            assert np.array_equal(f.cpu().numpy().astype(np.int64), ref), f"{nth}-thread table differs from numpy's"
+            status: list = []
+            b = K.sampler_resample(np.random.default_rng(5), x, u, 3, order, sync_rng=False, status_out=status)
+            flag = int(status[0].item())
+            assert flag & 32 and not flag & 24, f"bucketed path did not run cleanly (status {flag})"
+            got[nth] = b.cpu().numpy()
+        idx = np.random.default_rng(5).choice(n2, (3, n2))
+        ref_b = oc.resample_vals_gather(x, u, order, idx)
+        for nth in (512, 1024):
+            close(got[nth].reshape(ref_b.shape), ref_b, oc.tolerance_scale(x, u, order))
+    finally:
+        lib.txb_set_scatter_threads(prev)

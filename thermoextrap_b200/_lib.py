@@ -80,6 +80,7 @@ SIGNATURES = {
     "txb_perturb_workspace_bytes": (_sz, [_i64, _i64, _int]),
     "txb_perturb_predict_f64": (_int, [_p, _p, _i64, _i64, _i64, _p, _int, _p, _p, _sz, _p]),
     "txb_set_resample_kernel": (_int, [_int]),
+    "txb_set_scatter_threads": (_int, [_int]),
     "txb_profile_begin": (_int, [C.c_char_p]),
     "txb_profile_end": (_int, [C.POINTER(C.c_double), C.POINTER(_int)]),
     "txb_fp64_peak_launch": (_int, [_int, _int, _p, C.POINTER(C.c_double), _p]),

@@ -48,6 +48,7 @@ struct SamplerArgs {
     int64_t steps_per_block;      // multiple of 512 * SMP_T (both thread geometries tile it)
     Affine iter_jump;             // (SMP_THREADS - 1) * SMP_T steps
     Affine iter_jump2;            // (BK_THREADS - 1) * SMP_T steps (512-thread kernels)
+    Affine iter_jump3;            // (1024 - 1) * SMP_T / 2 steps (1024-thread partition kernel)
     Affine pow2[SMP_NPOW];        // 2^i steps
 };
 
@@ -526,6 +527,16 @@ inline Affine mk_affine(u128 a, u128 c) {
     return Affine{(uint64_t)(a >> 64), (uint64_t)a, (uint64_t)(c >> 64), (uint64_t)c};
 }
 
+// threads of the partition kernel: 1024 unless TXB_SCATTER_THREADS=512 / txb_set_scatter_threads(512)
+int g_scatter_threads = -1;
+inline int scatter_threads() {
+    if (g_scatter_threads < 0) {
+        const char* e = getenv("TXB_SCATTER_THREADS");
+        g_scatter_threads = (e && atoi(e) == 512) ? 512 : 1024;
+    }
+    return g_scatter_threads;
+}
+
 struct Plan {
     SamplerArgs a;
     int nblocks;
@@ -584,6 +595,8 @@ int make_plan(const txb_pcg64* rng, int64_t ndat, int64_t count, int64_t nsamp, 
     a.iter_jump = mk_affine(ja, jc);
     lcg_jump(inc, (uint64_t)(BK_THREADS - 1) * SMP_T, ja, jc);
     a.iter_jump2 = mk_affine(ja, jc);
+    lcg_jump(inc, (uint64_t)(2 * BK_THREADS - 1) * (SMP_T / 2), ja, jc);
+    a.iter_jump3 = mk_affine(ja, jc);
     u128 ca = mk128(PCG_MULT_HI, PCG_MULT_LO), cc = inc;
     for (int i = 0; i < SMP_NPOW; ++i) {
         a.pow2[i] = mk_affine(ca, cc);
@@ -911,6 +924,12 @@ int launch_consume(const ConsumeArgs& c, bool has_x, bool has_w, int gy, cudaStr
 
 }  // namespace
 
+extern "C" int txb_set_scatter_threads(int nthreads) {
+    const int prev = scatter_threads();
+    if (nthreads == 512 || nthreads == 1024) g_scatter_threads = nthreads;
+    return prev;
+}
+
 extern "C" size_t txb_sampler_freq_workspace_bytes(int64_t ndat, int64_t nrep, int64_t nsamp, int64_t nrep_out) {
     const txb_pcg64 dummy = {0, 0, 0, 1, 0, 0};
     Plan p;
@@ -1002,6 +1021,8 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
             if (!attr_done) {
                 if (cudaFuncSetAttribute(k_bucket_scatter<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess ||
+                    cudaFuncSetAttribute(k_bucket_scatter<1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess ||
                     cudaFuncSetAttribute(k_bucket_hist<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          BK_HSIZE) != cudaSuccess ||
                     cudaFuncSetAttribute(k_bucket_hist<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1032,7 +1053,10 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
                 ba.rep_lo = r0;
                 {
                     ProfScope prof("bucket_scatter", st);
-                    k_bucket_scatter<1><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
+                    if (scatter_threads() == 1024)
+                        k_bucket_scatter<1, 1024><<<dim3((unsigned)sp.nseg, (unsigned)nw), 1024, sc_smem, st>>>(p.a, ba);
+                    else
+                        k_bucket_scatter<1><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
                 }
                 TXB_CUDA_LAUNCH_CHECK("k_bucket_scatter<1>");
                 HistArgs h{};
@@ -1184,6 +1208,8 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
         static bool attr_done = false;
         if (!attr_done) {
             if (cudaFuncSetAttribute(k_bucket_scatter<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess ||
+                cudaFuncSetAttribute(k_bucket_scatter<0, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      BK_MAXNB * (BK_MINCAP * 2 + 12)) != cudaSuccess) {
                 set_error("k_bucket_scatter: shared memory opt-in failed");
                 cudaGetLastError();
@@ -1210,7 +1236,10 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             ba.rep_lo = r0;
             {
                 ProfScope prof("bucket_scatter", st);
-                k_bucket_scatter<0><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
+                if (scatter_threads() == 1024)
+                    k_bucket_scatter<0, 1024><<<dim3((unsigned)sp.nseg, (unsigned)nw), 1024, sc_smem, st>>>(p.a, ba);
+                else
+                    k_bucket_scatter<0><<<dim3((unsigned)sp.nseg, (unsigned)nw), BK_THREADS, sc_smem, st>>>(p.a, ba);
             }
             TXB_CUDA_LAUNCH_CHECK("k_bucket_scatter");
             ConsumeArgs c{};

@@ -57,7 +57,8 @@ struct BucketArgs {
     int b_lo;             // first bucket kept (draws of other buckets go to the sink ring): a rank's column range
 };
 
-// exclusive block scan for BK_THREADS threads
+// exclusive block scan for NTH threads
+template <int NTH>
 __device__ __forceinline__ int bk_block_scan(int v, int* sm_warp, int& total) {
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     int inc = v;
@@ -71,7 +72,7 @@ __device__ __forceinline__ int bk_block_scan(int v, int* sm_warp, int& total) {
     __syncthreads();
     int base = 0, tot = 0;
 #pragma unroll
-    for (int k = 0; k < BK_THREADS / 32; ++k) {
+    for (int k = 0; k < NTH / 32; ++k) {
         const int w = sm_warp[k];
         if (k < wrp) base += w;
         tot += w;
@@ -80,10 +81,14 @@ __device__ __forceinline__ int bk_block_scan(int v, int* sm_warp, int& total) {
     return base + inc - v;
 }
 
-template <int GEOM>
-__global__ void __launch_bounds__(BK_THREADS, 1)
+// NTH = 512 (8 LCG steps per thread and iteration) or 1024 (4 steps): the same 4096-step iterations either
+// way, so the position table of the counting pass serves both.  The 1024-thread form halves the registers
+// a thread needs for its draws (<= 64, the cap of a 1024-thread CTA) and doubles the warps that hide the
+// shared-memory atomic latency (ncu on the 512-thread form: 25 % warps active, 38 % issue-active).
+template <int GEOM, int NTH = BK_THREADS>
+__global__ void __launch_bounds__(NTH, 1)
     k_bucket_scatter(const __grid_constant__ SamplerArgs a, const BucketArgs e) {
-    constexpr int T = SMP_T;
+    constexpr int T = SMP_T * BK_THREADS / NTH;
     constexpr int NSLOT = 2 * T;
     extern __shared__ __align__(16) unsigned char bk_smem[];
     const int nb = e.nb;
@@ -95,7 +100,7 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     unsigned* tail = reinterpret_cast<unsigned*>(bk_smem + (size_t)nbp * cap * 2);  // [nb + 1]
     unsigned* head = tail + nbp;                                                    // [nb + 1]
     unsigned* lines = head + nbp;                                                   // [nb + 1] lines written
-    __shared__ int sm_warp[BK_THREADS / 32];
+    __shared__ int sm_warp[NTH / 32];
     __shared__ long long sm_j0;
 
     const int seg = blockIdx.x;
@@ -106,7 +111,7 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     if (B > rep_begin + a.nsamp) B = rep_begin + a.nsamp;
     const int64_t list0 = (r * nb) * e.nseg + seg;  // + b * nseg
 
-    for (int b = threadIdx.x; b < nbp; b += BK_THREADS) tail[b] = 0u, head[b] = 0u, lines[b] = 0u;
+    for (int b = threadIdx.x; b < nbp; b += NTH) tail[b] = 0u, head[b] = 0u, lines[b] = 0u;
     if (threadIdx.x == 0) {
         // last iteration whose first output position is <= A
         int64_t lo = 0, hi = e.niter - 1;
@@ -118,13 +123,13 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     }
     __syncthreads();
     if (A >= B) {  // empty segment
-        for (int b = threadIdx.x; b < nb; b += BK_THREADS) e.nlines[list0 + (int64_t)b * e.nseg] = 0u;
+        for (int b = threadIdx.x; b < nb; b += NTH) e.nlines[list0 + (int64_t)b * e.nseg] = 0u;
         return;
     }
     const int64_t j0 = sm_j0;
     uint64_t hi = a.s_hi, lo = a.s_lo;
     {
-        uint64_t q = ((uint64_t)j0 * BK_THREADS + threadIdx.x) * T;
+        uint64_t q = ((uint64_t)j0 * NTH + threadIdx.x) * T;
         for (int i = 0; q != 0 && i < SMP_NPOW; ++i, q >>= 1)
             if (q & 1) affine_apply(hi, lo, a.pow2[i]);
     }
@@ -154,7 +159,7 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
     };
     // every bucket ring is drained by one fixed thread: full lines always, the remainder when `all`
     auto drain = [&](bool all) {
-        for (int b = threadIdx.x; b < nb; b += BK_THREADS) {
+        for (int b = threadIdx.x; b < nb; b += NTH) {
             unsigned t = tail[b], h = head[b];
             if (t - h > cap) {
                 // more arrivals than the ring holds (> 6 sigma).  The checked append writes those as
@@ -252,7 +257,7 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         } else {
             int tot;
             const int c = __popc(mask) + (pre_acc ? 1 : 0);
-            int64_t pos = P + bk_block_scan(c, sm_warp, tot);
+            int64_t pos = P + bk_block_scan<NTH>(c, sm_warp, tot);
             if (pre_acc) {
                 if (pos >= A && pos < B) append(pre_val);
                 ++pos;
@@ -267,12 +272,12 @@ __global__ void __launch_bounds__(BK_THREADS, 1)
         }
         __syncthreads();
         drain(false);
-        affine_apply(hi, lo, a.iter_jump2);
+        affine_apply(hi, lo, NTH == BK_THREADS ? a.iter_jump2 : a.iter_jump3);
         generate();  // iteration j + 1 (one unused set at the end of the block's range)
         __syncthreads();
     }
     drain(true);
-    for (int b = threadIdx.x; b < nb; b += BK_THREADS) {
+    for (int b = threadIdx.x; b < nb; b += NTH) {
         const unsigned nl = lines[b];
         e.nlines[list0 + (int64_t)b * e.nseg] = nl < (unsigned)e.cap_lines ? nl : (unsigned)e.cap_lines;
     }
