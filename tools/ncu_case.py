@@ -39,6 +39,26 @@ elif which == "resample_i64":  # scalar x from the reference's own int64 frequen
     nr = 256
     f64 = K.sampler_freq(np.random.default_rng(1), nr, 2_000_000, dtype=torch.uint8).to(torch.int64)
     K.resample_vals(x[:2_000_000], u[:2_000_000], f64, 8)
+elif which == "target":  # python tools/ncu_case.py target [nsamp nrep]: K6 table window + K2 contraction, both forms
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    nw, rw = (int(v) for v in (sys.argv[2:4] if len(sys.argv) > 3 else (100_000_000, 128)))
+    del x
+    uw = torch.randn(nw, dtype=torch.float64, device="cuda") * 5.3 + 175
+    xw = torch.empty((nw, 64), dtype=torch.float64, device="cuda")
+    for i in range(0, nw, 1 << 22):
+        xw[i : i + (1 << 22)].normal_(0.0, 0.02)
+        xw[i : i + (1 << 22)].addcmul_(uw[i : i + (1 << 22), None], torch.linspace(0.5e-3, 2e-3, 64, dtype=torch.float64, device="cuda")[None])
+    plan = K.SamplerPlan(np.random.default_rng(1), rw, nw)
+    lib.txb_set_scatter_threads(512)
+    f8 = K.sampler_freq(plan, dtype=torch.uint8)
+    lib.txb_set_scatter_threads(1024)
+    f8 = K.sampler_freq(plan, dtype=torch.uint8, out=f8.new_empty((rw, f8.stride(0))) if f8.stride(0) != nw else None)
+    lib.txb_set_resample_kernel(1)
+    K.resample_vals(xw, uw, f8, 6)
+    lib.txb_set_resample_kernel(2)
+    K.resample_vals(xw, uw, f8, 6)
 elif which == "perturb":
     xw = torch.randn((4_000_000, 64), dtype=torch.float64, device="cuda")
     K.perturb_predict(xw, u[:4_000_000] * 0.01, np.linspace(-0.4, 0.5, 8))

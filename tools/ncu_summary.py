@@ -23,7 +23,34 @@ KEYS = [
     "smsp__average_warp_latency_issue_stalled_lg_throttle.ratio",
     "smsp__average_warp_latency_issue_stalled_mio_throttle.ratio",
     "smsp__average_warp_latency_issue_stalled_wait.ratio",
+    "smsp__average_warp_latency_issue_stalled_dispatch_stall.ratio",
+    "smsp__average_warp_latency_issue_stalled_no_instruction.ratio",
+    "smsp__average_warp_latency_issue_stalled_not_selected.ratio",
+    "smsp__average_warp_latency_issue_stalled_membar.ratio",
+    "smsp__average_warp_latency_issue_stalled_tex_throttle.ratio",
+    "smsp__average_warp_latency_issue_stalled_branch_resolving.ratio",
+    "smsp__average_warp_latency_issue_stalled_selected.ratio",
+    # tensor / fp64 / integer pipe utilisation (DMMA issues on the fp64 tensor path)
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_op_dmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor_op_dmma.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor_op_dmma.sum",
+    "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_uniform.avg.pct_of_peak_sustained_active",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.avg.pct_of_peak_sustained_elapsed",
+    "smsp__inst_executed_op_shared_atom.sum",
+    "smsp__inst_executed_op_shared_ld.sum",
+    "smsp__inst_executed_op_shared_st.sum",
 ]
+# any further pipe / tensor counters the report carries (names differ between ncu versions)
+EXTRA_SUBSTR = ("pipe_tensor", "dmma")
 
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
@@ -34,5 +61,8 @@ for vals in rows[2:]:
     d = dict(zip(hdr, zip(units, vals)))
     for k in KEYS:
         if k in d:
+            print(f"{k:75s} {d[k][1]:>20s} {d[k][0]}")
+    for k in hdr:
+        if k not in KEYS and any(sub in k for sub in EXTRA_SUBSTR) and k in d:
             print(f"{k:75s} {d[k][1]:>20s} {d[k][0]}")
     print()
