@@ -302,6 +302,31 @@ int txb_perturb_predict_f64(const double* x, const double* u, int64_t nsamp, int
                             int64_t ldx, const double* dalpha, int nalpha, double* out,
                             void* workspace, size_t ws_bytes, void* stream);
 
+/* ---- K7 device-resident: comoment records -> beta derivatives -> Taylor prediction, one launch ----------
+ * Replaces, for the four numeric beta families, the chain  data.derivs_args (data.py:945-962) ->
+ * funcs[i](*args) (models.py:371) -> minus_log (:373-374) -> / i! (:376-377) -> Taylor sum (:535-565)
+ * with GENERATED device functions (csrc/beta_derivs_gen.cuh, built by csrc/gen_beta_derivs.py from the
+ * recurrences of beta.py:32-266) reading the bootstrap kernels' output where it lies.
+ *   comom   [nelem, 2, kdim] central comoment records in cmomy's layout ([0,1] = <u>, [0,n] = <du^n>,
+ *           [1,0] = <x>, [1,n] = <dx du^n>), kdim >= order + 1
+ *   family  0 x_ave central, 1 u_ave central, 2 x_ave raw, 3 u_ave raw (raw: converted in registers).  The u_ave
+ *           families expect x_is_u records (x == u, beta.py:633-646): <du^n> is read as <dx du^(n-1)>
+ *   flags   1 = -log transform (SymMinusLog), 2 = divide by i! (mode 3 only; modes 0-2 always do)
+ *   mode    0 sum -> out[nalpha, nelem]; 1 cumsum / 2 terms -> out[nalpha, order+1, nelem];
+ *           3 derivatives only -> out[order+1, nelem] (dalpha unused)
+ *   dalpha  [nalpha] device doubles (alpha - alpha0).  order <= 10 (TXB_ERR_UNSUPPORTED above).     */
+int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim, int family, int order, int flags,
+                         int mode, const double* dalpha, int nalpha, double* out, void* stream);
+/* out[a, e] = (accumulate ? out[a, e] : 0) + sum_t W[a, t] D[t, e]: InterpModel.predict (models.py:909-932)
+ * with W = alpha powers x inverse Hermite matrix folded on the host ([nalpha, nt], nt <= 512) and D = one
+ * state's normalised derivatives [nt, nelem], both on the device.                                   */
+int txb_combine_f64(const double* W, int nalpha, int nt, const double* D, int64_t nelem, int accumulate,
+                    double* out, void* stream);
+/* mean[a, b], var[a, b] over r of in[na, nrep, nb] (ddof delta degrees of freedom; xarray's default is 0):
+ * stack.to_mean_var (stack.py:157-182) over the replicate axis of derivative arrays, on the device.   */
+int txb_mean_var_f64(const double* in, int64_t na, int64_t nrep, int64_t nb, int ddof, double* mean,
+                     double* var, void* stream);
+
 /* ---- measurement helper: fp64 FMA peak micro-benchmark (bench.py roofline) ---
  * scratch: >= 1 device double; *flops (HOST pointer) = flop count of the launch. */
 int txb_fp64_peak_launch(int iters, int blocks_per_sm, double* scratch, double* flops, void* stream);
@@ -315,8 +340,8 @@ int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double*
                                 void* stream);
 
 /* Which wide-x (> 4 channels) contraction kernel txb_resample_* launches: 0 = register-tiled DFMA,
- * 1 = k_resample_mma (DMMA, round 1), 2 = k_resample_mma2 (default: operand generation overlapped with the
- * DMMAs, u-moment row folded into channel tile 0), 3 = k_resample_mma2 with the separate u-moment pass.
+ * 1 = k_resample_mma (DMMA, round 1), 2 = k_resample_mma2 (operand generation overlapped with the DMMAs,
+ * 4-sample table loads; 8 warps), 3 = k_resample_mma2 with 16 warps (the default).
  * Same results within rounding; exists so tests and bench.py can A/B the forms in one process (also
  * TXB_RESAMPLE_MMA in the environment).  Returns the previous setting; other values only query.  No
  * counterpart in the reference (data.py:1803-1810 has one cmomy.resample_vals).                     */

@@ -199,10 +199,9 @@ def test_binomials_per_device(K):
     (900, 16, 9, 8, "x"), (640, 70, 20, 10, "xw"), (1500, 20, 140, 5, "upc"), (777, 9, 66, 7, "upc"),
 ])
 def test_wide_contraction_kernel_forms_match_oracle(K, version, dtype, n, nv, nrep, order, kind):
-    """``txb_set_resample_kernel``: the DFMA tile (0), k_resample_mma (1), k_resample_mma2 with the u-moment row
-    folded into channel tile 0 (2, the default) and with the separate u-moment pass (3) all meet the gather
-    oracle: ragged replicate / channel / sample tiles, weights, orders on both sides of the fold limit (7), the
-    per-channel-u form, every table dtype."""
+    """``txb_set_resample_kernel``: the DFMA tile (0), k_resample_mma (1) and k_resample_mma2 with 8 warps (2) and
+    16 warps (3) all meet the gather oracle: ragged replicate / channel / sample tiles, weights, both replicate
+    tile sizes (orders <= 8 / > 8), the per-channel-u form, every table dtype."""
     import torch
 
     from thermoextrap_b200 import _lib

@@ -113,8 +113,7 @@ static size_t rs_partials_doubles(int64_t nsamp, int64_t nchan, int order, int64
     const int64_t ch = nchan < 1 ? 1 : nchan;
     // scalar pass: nslab * nrep * 2 (K+1);  wide pass: nslab * nrep * nchan * (K+1)
     const int64_t sc = rs_max_slabs(nrep, 1) * nrep * 2 * kp;
-    // wide pass: S1 partials + (k_resample_mma2's folded u-moment row) nslab * nrep * (K+1)
-    const int64_t wd = rs_max_slabs(nrep, (ch + 15) / 16) * nrep * (ch + 1) * kp;
+    const int64_t wd = rs_max_slabs(nrep, (ch + 15) / 16) * nrep * ch * kp;
     return (size_t)(sc > wd ? sc : wd);
 }
 

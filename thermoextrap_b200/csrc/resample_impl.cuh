@@ -72,13 +72,14 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
 }
 
 // wide x on the fp64 tensor cores.  TXB_RESAMPLE_MMA = 0: DFMA tile; 1: k_resample_mma (round 1);
-// 2 (default): k_resample_mma2 (operand generation overlapped with the DMMAs, S0 folded in);
-// 3: k_resample_mma2 without the S0 fold (separate scalar pass, for A/B timing)
+// 2: k_resample_mma2 (operand generation overlapped with the DMMAs), 8 warps; 3 (default): the same with 16
+// warps -- measured at 1e8 x 64, order 6, uint8 table, 256 replicates (profiles/r02_exp_mma_forms.json):
+// form 1 31.4, form 2 31.2, form 3 32.1 TFLOP/s
 extern int g_rs_mma_version;   // resample.cu; txb_set_resample_kernel overrides the environment
 inline int rs_mma_version() {
     if (g_rs_mma_version < 0) {
         const char* e = getenv("TXB_RESAMPLE_MMA");
-        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 2;
+        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 3;
     }
     return g_rs_mma_version;
 }
@@ -114,23 +115,21 @@ int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st)
     return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
 }
 
-// second form: S0 (when `fold`, orders <= 7, comoment mode) comes out of the same launch
-template <int K, typename FT>
-int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, bool fold, cudaStream_t st) {
-    using C = Rm2Cfg<K, FT>;
+// second form (operand generation overlapped with the DMMAs); WM = 4: 8 warps, WM = 8: 16 warps
+template <int K, typename FT, int WM>
+int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
+    using C = Rm2Cfg<K, FT, WM>;
     const RsPlan p = rs_plan(a.nsamp, a.nchan, a.nrep, C::RT, C::ST, C::CT);
     const bool upc = a.ldu != 0;
     const int64_t n = a.nrep * a.nchan * (K + 1);
-    const int64_t n0 = a.nrep * (K + 1);
-    fold = fold && C::S0F && !upc;
-    a.ws0 = upc ? ws : ws + p.nslab * n;   // folded S0 partials sit behind the S1 partials
+    a.ws0 = ws;
     a.ws1 = ws;
     a.slab_len = p.slab_len;
     const int es = FreqElem<FT>::ES;
     a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
     static bool attr_done = false;
     if (!attr_done) {
-        if (cudaFuncSetAttribute(k_resample_mma2<K, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(k_resample_mma2<K, FT, WM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)C::SMEM) != cudaSuccess) {
             set_error("k_resample_mma2: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
             cudaGetLastError();
@@ -141,25 +140,18 @@ int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, bool fold, cuda
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
         ProfScope prof("resample", st);
-        k_resample_mma2<K, FT><<<grid, C::NT, C::SMEM, st>>>(a, fold ? 1 : 0);
+        k_resample_mma2<K, FT, WM><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma2");
-    int rc = launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
-    if (rc == TXB_OK && fold) rc = launch_sum_parts(a.ws0, p.nslab, n0, S0, st);
-    return rc;
+    return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
 }
 
-// wide dispatch for > 4 channels.  `s0_done` tells the caller whether S0 still needs the scalar pass.
+// wide dispatch for > 4 channels
 template <int K, typename FT>
-int rs_launch_wide_mma(const RsArgs& a, double* S0, double* S1, double* ws, bool want_fold, bool& s0_done,
-                       cudaStream_t st) {
-    s0_done = false;
+int rs_launch_wide_mma(const RsArgs& a, double* S0, double* S1, double* ws, cudaStream_t st) {
     const int v = rs_mma_version();
-    if (v >= 2) {
-        const bool fold = want_fold && v == 2 && Rm2Cfg<K, FT>::S0F;
-        s0_done = fold;
-        return rs_launch_mma2<K, FT>(a, S0, S1, ws, fold, st);
-    }
+    if (v == 3) return rs_launch_mma2<K, FT, 8>(a, S0, S1, ws, st);
+    if (v == 2) return rs_launch_mma2<K, FT, 4>(a, S0, S1, ws, st);
     if (v == 1) return rs_launch_mma<K, FT>(a, S0, S1, ws, st);
     return rs_launch<K, RS_WIDE, 8, FT>(a, S0, S1, ws, st);
 }
@@ -237,18 +229,13 @@ int resample_sums_ft(const double* x, const double* u, const double* w, int64_t 
             } else if (ldu == 0) {                                                                   \
                 RsArgs b = a;                                                                        \
                 b.x = nullptr; b.nchan = 1; b.ldx = 0; b.pivot = pivot + nchan;                      \
-                bool s0_done = false;                                                                \
-                if (nchan <= 4) {                                                                    \
-                    rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);                            \
-                    if (rc == TXB_OK) rc = rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st);          \
-                } else {                                                                             \
-                    rc = rs_launch_wide_mma<K, FT>(a, S0, S1, ws, true, s0_done, st);                \
-                    if (rc == TXB_OK && !s0_done) rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);\
-                }                                                                                    \
+                rc = rs_launch_scalar<K, FT>(b, S0, nullptr, ws, st);                                \
+                if (rc == TXB_OK)                                                                    \
+                    rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                \
+                                    : rs_launch_wide_mma<K, FT>(a, S0, S1, ws, st);                  \
             } else {                                                                                 \
-                bool s0_done = false;                                                                \
                 rc = nchan <= 4 ? rs_launch<K, RS_WIDE, 2, FT>(a, S0, S1, ws, st)                    \
-                                : rs_launch_wide_mma<K, FT>(a, S0, S1, ws, false, s0_done, st);      \
+                                : rs_launch_wide_mma<K, FT>(a, S0, S1, ws, st);                      \
             }                                                                                        \
         });                                                                                          \
         return rc;                                                                                   \

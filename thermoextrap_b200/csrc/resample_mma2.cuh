@@ -10,27 +10,28 @@
 //      order over K is free, and a lane then needs FOUR CONSECUTIVE table entries per group -- one 32-bit
 //      shared-memory load per fragment row instead of four byte loads (P pitch is odd so the B-fragment
 //      loads of this order stay conflict-free);
-//   3. the u-moment row S0[r, j] = sum_s F w du^j rides along as one more 8-column fragment of channel
-//      tile 0 (orders <= 7): the separate scalar pass over the whole table disappears.
+//   3. WM (warps along replicates) is a template parameter: 4 (8 warps, 4 x (K+1) fragments each) or 8 (16
+//      warps, 2 x (K+1) fragments each, <= 128 registers) -- ncu on the first form shows the warps stalled on
+//      `wait` and `math_pipe_throttle` in equal parts with only two warps per scheduler to cover each other.
+// (Folding the u-moment row S0 in as an extra fragment of channel tile 0 was tried and removed: the warp-uniform
+//  branch around its mma.sync put a WARPSYNC into every k-step and cost 13 %; the separate scalar pass is 2 %.)
 #pragma once
 #include "resample_mma.cuh"
 
 namespace txb {
 
-template <int K, typename FT>
+template <int K, typename FT, int WM_>
 struct Rm2Cfg {
     static constexpr int ES = FreqElem<FT>::ES;
     static constexpr int VS = 16 / ES;
-    static constexpr int NT = 256;
-    static constexpr int WM = 4, WN = 2;
-    static constexpr int MT = (K + 1 <= 9) ? 4 : 2;
+    static constexpr int WM = WM_, WN = 2;
+    static constexpr int NT = WM * WN * 32;
+    static constexpr int RT = (K + 1 <= 9) ? 128 : 64;    // replicate tile, as k_resample_mma
+    static constexpr int MT = RT / (WM * 8);              // 8-replicate fragments per warp
     static constexpr int NTL = K + 1;
-    static constexpr int RT = WM * MT * 8;
     static constexpr int CT = 16;
     static constexpr int NCOL = CT * (K + 1);
-    static constexpr bool S0F = (K + 1 <= 8);             // S0 columns fit one 8-wide fragment
-    static constexpr int NCOLX = NCOL + (S0F ? 8 : 0);
-    static constexpr int PP = NCOLX + 5;                  // odd pitch (NCOLX is even): see header note 2
+    static constexpr int PP = NCOL + 5;                   // odd pitch (NCOL is even): see header note 2
     static constexpr size_t SMEM64 = (size_t)3 * RT * (64 * ES + 16) + 2 * (size_t)64 * PP * 8;
     static constexpr int ST = SMEM64 <= 200 * 1024 ? 64 : 32;
     static constexpr int NGRP = ST / 16;                  // 16-sample groups per stage
@@ -41,7 +42,10 @@ struct Rm2Cfg {
     static constexpr int P_DBL = ST * PP;
     static constexpr size_t SMEM = (size_t)NSTAGE * A_BYTES + 2 * (size_t)P_DBL * 8;
     static_assert(NCOL == WN * NTL * 8, "column tile must split into 8-wide fragments");
-    static_assert(ST * CT / NT == NGRP, "one P piece per 16-sample group");
+    static constexpr int NPIECE = ST * CT / NT;           // P elements per thread and stage
+    static constexpr int PROWS = NT / CT;                 // samples covered by one piece
+    static constexpr int GPP = NGRP / NPIECE;             // 16-sample groups per piece
+    static_assert(MT >= 1 && NPIECE >= 1 && NPIECE * GPP == NGRP, "tile / thread geometry");
     static_assert((PP & 1) == 1, "P pitch must be odd");
 };
 
@@ -78,12 +82,12 @@ template <int I> __device__ __forceinline__ uint32_t apack_get(const APack<8>& a
     return I == 0 ? a.w0.x : I == 1 ? a.w0.z : I == 2 ? a.w1.x : a.w1.z;
 }
 
-template <int K, typename FT>
-__global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const int fold_s0) {
-    using C = Rm2Cfg<K, FT>;
+template <int K, typename FT, int WM>
+__global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
+    using C = Rm2Cfg<K, FT, WM>;
     constexpr int ES = C::ES, VS = C::VS, NT = C::NT, MT = C::MT, NTL = C::NTL, RT = C::RT, CT = C::CT;
     constexpr int PP = C::PP, ST = C::ST, NG = C::NG, PITCH = C::PITCH, NSTAGE = C::NSTAGE, NGRP = C::NGRP;
-    constexpr int NCOL = C::NCOL;
+    constexpr int NPIECE = C::NPIECE, PROWS = C::PROWS, GPP = C::GPP;
 
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned char* sA = smem;
@@ -99,9 +103,6 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
     const int nstage = (int)((s_end - s_begin + ST - 1) / ST);
     const bool has_x = a.x != nullptr, has_w = a.w != nullptr;
     const bool upc = a.ldu != 0;
-    // the u-moment fragment: channel tile 0 only, the four warps of column half 0 (one per scheduler)
-    const bool s0_tile = C::S0F && fold_s0 != 0 && !upc && blockIdx.x == 0;
-    const bool do_s0 = s0_tile && wn == 0;
 
     const unsigned char* fbase = reinterpret_cast<const unsigned char*>(a.freq);
     auto issue_A = [&](int it) {
@@ -134,21 +135,21 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
         cp_async_commit();
     };
 
-    // P operands: this thread regenerates channel cl of samples (tid / 16 + 16 q), q = 0 .. NGRP-1
+    // P operands: this thread regenerates channel cl of samples (tid / 16 + PROWS q), q = 0 .. NPIECE-1
     const int cl = tid % CT, sl0 = tid / CT;
     const int64_t my_c = c_base + cl;
     const bool c_ok = my_c < a.nchan;
     const double piv_c = c_ok ? a.pivot[my_c] : 0.0;          // cx[c] (comoments) or cu[c] (x_is_u wide)
     const double piv_u = upc ? 0.0 : a.pivot[a.nchan];
-    double px[NGRP], pu[NGRP], pwt[NGRP];
+    double px[NPIECE], pu[NPIECE], pwt[NPIECE];
     auto prefetch_P = [&](int it) {
         const int64_t s0 = s_begin + (int64_t)it * ST;
 #pragma unroll
-        for (int q = 0; q < NGRP; ++q) {
+        for (int q = 0; q < NPIECE; ++q) {
             // rows past the slab end carry weight 0 (every column of the row is then 0); channels past nchan
-            // carry dx = 0 (x := its pivot) -- but keep u and w of the SAMPLE: the u-moment columns need them
+            // carry dx = 0 (x := its pivot)
             px[q] = piv_c, pu[q] = 0.0, pwt[q] = 0.0;
-            const int64_t s = s0 + sl0 + 16 * q;
+            const int64_t s = s0 + sl0 + PROWS * q;
             if (s < s_end && it < nstage) {
                 pwt[q] = has_w ? __ldg(a.w + s) : 1.0;
                 if (upc) {
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
         }
     };
     auto write_piece = [&](int it, int q) {
-        double* row = sP + (size_t)(it & 1) * C::P_DBL + (size_t)(sl0 + 16 * q) * PP;
+        double* row = sP + (size_t)(it & 1) * C::P_DBL + (size_t)(sl0 + PROWS * q) * PP;
         double du, lead;
         if (upc) {   // cols (c, j) = w du_c^j
             du = pu[q] - piv_c;
@@ -170,16 +171,12 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
             du = pu[q] - piv_u;
             lead = pwt[q] * (px[q] - piv_c);
         }
-        double p = lead, qq = pwt[q], s0v = 0.0;
+        double p = lead;
 #pragma unroll
         for (int j = 0; j <= K; ++j) {
             row[cl * (K + 1) + j] = p;
-            if (j == cl) s0v = qq;
             p *= du;
-            qq *= du;
         }
-        // u-moment columns NCOL + j = w du^j: thread cl < 8 stores column cl (zero for cl > K)
-        if (C::S0F && s0_tile && cl < 8) row[NCOL + cl] = s0v;
     };
 
     double acc[MT][NTL][2];
@@ -187,16 +184,13 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
     for (int m = 0; m < MT; ++m)
 #pragma unroll
         for (int n = 0; n < NTL; ++n) acc[m][n][0] = 0.0, acc[m][n][1] = 0.0;
-    double acc0[MT][2];
-#pragma unroll
-    for (int m = 0; m < MT; ++m) acc0[m][0] = 0.0, acc0[m][1] = 0.0;
 
     // ---- prologue: A stages 0 and 1 in flight, P(0) written, P(1) operands in registers
 #pragma unroll
     for (int p = 0; p < NSTAGE - 1; ++p) issue_A(p);
     prefetch_P(0);
 #pragma unroll
-    for (int q = 0; q < NGRP; ++q) write_piece(0, q);
+    for (int q = 0; q < NPIECE; ++q) write_piece(0, q);
     prefetch_P(1);
     cp_async_wait<NSTAGE - 2>();
     __syncthreads();
@@ -210,7 +204,7 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
         const double* bufP = sP + (size_t)(it & 1) * C::P_DBL + (size_t)(4 * fk) * PP;
 
         APack<ES> aw[MT];
-        double bf[NTL], bs = 0.0;
+        double bf[NTL];
         auto fetch_a = [&](int g) {
 #pragma unroll
             for (int m = 0; m < MT; ++m) aw[m] = apack_load<ES>(bufA + (size_t)(m * 8) * PITCH + g * 16 * ES);
@@ -219,7 +213,6 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
             const double* rowp = bufP + (size_t)(g * 16 + i) * PP;
 #pragma unroll
             for (int n = 0; n < NTL; ++n) bf[n] = rowp[b_col0 + n * 8];
-            if (do_s0) bs = rowp[NCOL + fg];
         };
         fetch_a(0);
         fetch_b(0, 0);
@@ -232,7 +225,6 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 double af[MT], bc[NTL];
-                const double bsc = bs;
 #pragma unroll
                 for (int m = 0; m < MT; ++m) {
                     const uint32_t v = i == 0 ? apack_get<0>(ac[m]) : i == 1 ? apack_get<1>(ac[m])
@@ -247,13 +239,9 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
                 for (int m = 0; m < MT; ++m)
 #pragma unroll
                     for (int n = 0; n < NTL; ++n) dmma884(acc[m][n][0], acc[m][n][1], af[m], bc[n]);
-                if (do_s0) {
-#pragma unroll
-                    for (int m = 0; m < MT; ++m) dmma884(acc0[m][0], acc0[m][1], af[m], bsc);
-                }
             }
             // operands of the NEXT stage, into the other P buffer (last read in stage it - 1)
-            write_piece(it + 1, g);
+            if ((g + 1) % GPP == 0) write_piece(it + 1, g / GPP);
         }
         prefetch_P(it + 2);
         cp_async_wait<NSTAGE - 2>();
@@ -276,13 +264,6 @@ __global__ void __launch_bounds__(256, 1) k_resample_mma2(const RsArgs a, const 
                 const int ch = col / (K + 1), j = col % (K + 1);
                 const int64_t c = c_base + ch;
                 if (c < a.nchan) dstp[((slab * a.nrep + rr) * a.nchan + c) * (K + 1) + j] = acc[m][n][h];
-            }
-        }
-        if (do_s0) {
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int j = 2 * fk + h;
-                if (j <= K) a.ws0[(slab * a.nrep + rr) * (K + 1) + j] = acc0[m][h];
             }
         }
     }

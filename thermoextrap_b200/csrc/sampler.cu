@@ -843,7 +843,7 @@ SegPlan seg_plan(const BucketPlan& b, int64_t nsamp, int ks, int64_t nwin) {
     const double ms = b.m * (double)s.seg_len / (double)nsamp;
     s.cap_lines = (int)((ms + 10.0 * sqrt(ms) + 32.0) / BK_LINE) + 3;
     s.per_rep_bytes = (size_t)b.nb * (sizeof(unsigned) * s.nseg + 2 * sizeof(double) * (ks + 1) +
-                                      (size_t)s.nseg * s.cap_lines * BK_LINE * 2) + 64;
+                                      (size_t)s.nseg * s.cap_lines * BK_LINE * 2) + 64 + 16;   // + a row-sum accumulator
     return s;
 }
 
@@ -988,7 +988,7 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
     e.pos_hi = rep_hi * nsamp;
     // ---- bucketed histogram (narrow tables, scratch beyond the head): partition the draws by sample
     // bucket in shared memory, then count every (bucket, replicate) in a shared-memory histogram
-    bool bucketed = false;
+    bool bucketed = false, rowsum_folded = false;
     if (esz[freq_dtype] < 4 && !(prepared & TXB_SAMPLER_NO_BUCKETS) && nsamp < (1ll << 31)) {
         const BucketPlan bp = hist_bucket_plan(p, ndat, nsamp);
         const size_t used = align_up(p.head_bytes + 256, 256);
@@ -1034,6 +1034,13 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
                 attr_done = true;
             }
             const size_t sc_smem = (size_t)(nbl + 1) * (bp.cap * 2 + 12);  // + the ring for rejected / foreign draws
+            // whole-table calls fold the overflow check into the histogram's store loop (no second pass over
+            // the table); column-range calls keep k_freq_rowsum_check, which also reports the partial row sums
+            const size_t lists_bytes = (size_t)wrep * nbl * sp.nseg * sp.cap_lines * BK_LINE * 2;
+            unsigned long long* rowacc = (!partial && status)
+                ? reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(lists) + align_up(lists_bytes, 16))
+                : nullptr;
+            rowsum_folded = rowacc != nullptr;
             for (int64_t r0 = rep_lo; r0 < rep_hi; r0 += wrep) {
                 const int64_t r1 = r0 + wrep < rep_hi ? r0 + wrep : rep_hi;
                 const int64_t nw = r1 - r0;
@@ -1068,6 +1075,12 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
                 h.freq = reinterpret_cast<unsigned char*>(freq) + (size_t)(r0 - rep_lo) * ldf * esz[freq_dtype];
                 h.ldf = ldf;
                 h.ndat = ncol;   // columns are relative to col_lo (a multiple of the bucket size)
+                h.rowacc = rowacc;
+                if (rowacc && cudaMemsetAsync(rowacc, 0, sizeof(unsigned long long) * (size_t)nw, st) != cudaSuccess) {
+                    set_error("txb_sampler_freq: cudaMemsetAsync(rowacc) failed");
+                    cudaGetLastError();
+                    return TXB_ERR_CUDA;
+                }
                 {
                     ProfScope prof("bucket_hist", st);
                     const dim3 grid((unsigned)nbl, (unsigned)nw);
@@ -1075,6 +1088,10 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
                     else                       k_bucket_hist<uint8_t><<<grid, BK_THREADS, hist_smem, st>>>(h);
                 }
                 TXB_CUDA_LAUNCH_CHECK("k_bucket_hist");
+                if (rowacc) {
+                    k_rowacc_verify<<<(unsigned)((nw + 255) / 256), 256, 0, st>>>(rowacc, nw, (long long)nsamp, status);
+                    TXB_CUDA_LAUNCH_CHECK("k_rowacc_verify");
+                }
             }
             bucketed = true;
         }
@@ -1092,7 +1109,7 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
         default:      k_sampler<MODE_HIST, 1, false, false, uint8_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e); break;
     }
     TXB_CUDA_LAUNCH_CHECK("k_sampler<hist>");
-    if (status && esz[freq_dtype] < 4) {  // narrow lanes are bumped without a return value: verify the row sums
+    if (status && esz[freq_dtype] < 4 && !rowsum_folded) {  // narrow lanes are bumped without a return value: verify the row sums
         const unsigned char* f = reinterpret_cast<const unsigned char*>(freq);
         const int64_t row_bytes = ldf * (int64_t)esz[freq_dtype];
         const unsigned rows = (unsigned)(rep_hi - rep_lo);

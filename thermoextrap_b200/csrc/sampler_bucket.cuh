@@ -357,6 +357,7 @@ struct HistArgs {
     int nb, cap_lines, nseg;
     void* freq;        // row 0 = first replicate of this window
     int64_t ldf, ndat;
+    unsigned long long* rowacc;   // [replicates of the window] sum of the stored lanes (overflow check), or NULL
 };
 
 // K6 frequency table from the bucket lists: one CTA per (bucket, replicate) counts the bucket's draws in
@@ -401,17 +402,44 @@ __global__ void __launch_bounds__(BK_THREADS) k_bucket_hist(const HistArgs c) {
     (void)left;
     const int nword = (n_here * ES + 3) / 4;
     unsigned char* dst = reinterpret_cast<unsigned char*>(c.freq) + (r * c.ldf + s0) * ES;
+    // sum of the lanes as stored: a lane that wrapped loses 2^BITS from it, so the row total equals the number
+    // of draws iff no lane overflowed (the test k_freq_rowsum_check makes in a second pass over the table)
+    auto lanes = [](unsigned w) -> unsigned {
+        return ES == 1 ? __dp4a(w, 0x01010101u, 0u) : (w & 0xffffu) + (w >> 16);
+    };
+    unsigned acc = 0;
     if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
         const int nq = nword / 4;
         uint4* d4 = reinterpret_cast<uint4*>(dst);
         const uint4* h4 = reinterpret_cast<const uint4*>(h);
-        for (int i = threadIdx.x; i < nq; i += BK_THREADS) d4[i] = h4[i];
+        for (int i = threadIdx.x; i < nq; i += BK_THREADS) {
+            const uint4 q = h4[i];
+            d4[i] = q;
+            acc += lanes(q.x) + lanes(q.y) + lanes(q.z) + lanes(q.w);
+        }
         unsigned* d1 = reinterpret_cast<unsigned*>(dst);
-        for (int i = nq * 4 + threadIdx.x; i < nword; i += BK_THREADS) d1[i] = h[i];
+        for (int i = nq * 4 + threadIdx.x; i < nword; i += BK_THREADS) {
+            d1[i] = h[i];
+            acc += lanes(h[i]);
+        }
     } else {
         unsigned* d1 = reinterpret_cast<unsigned*>(dst);
-        for (int i = threadIdx.x; i < nword; i += BK_THREADS) d1[i] = h[i];
+        for (int i = threadIdx.x; i < nword; i += BK_THREADS) {
+            d1[i] = h[i];
+            acc += lanes(h[i]);
+        }
     }
+    if (c.rowacc) {
+        acc = __reduce_add_sync(0xffffffffu, acc);
+        if ((threadIdx.x & 31) == 0 && acc) atomicAdd(c.rowacc + r, (unsigned long long)acc);
+    }
+}
+
+// rowacc[r] (accumulated by k_bucket_hist) must equal the draws of a replicate: else a narrow lane overflowed
+__global__ void k_rowacc_verify(const unsigned long long* __restrict__ rowacc, int64_t nrows, long long expect,
+                                int* __restrict__ status) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < nrows && rowacc[r] != (unsigned long long)expect) atomicOr(status, 2);
 }
 
 }  // namespace txb

@@ -453,13 +453,17 @@ def sampler_indices(src, nrep: int | None = None, nsamp: int | None = None, ndat
 
 def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: int | None = None,
                  dtype: torch.dtype = torch.uint8, reps=None, buckets: bool = True,
-                 scratch_bytes: int | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+                 scratch_bytes: int | None = None, out: torch.Tensor | None = None,
+                 status_out: list | None = None) -> torch.Tensor:
     """Frequency table of the same stream, histogrammed on the device without the index table.
 
     uint8 / uint16 tables are built by partitioning the draws by sample bucket and counting in shared
     memory when scratch allows (``scratch_bytes``, default up to a third of the free memory; replicates
     go in as many windows as that needs); ``buckets=False`` forces global atomics.  ``out`` (optional,
     ``[>= hi - lo, ldf]`` of ``dtype`` with 16-byte rows) is filled instead of a new allocation.
+    ``status_out`` (a list) defers the status check: the device status word is appended instead of being
+    read back (no host sync); the caller inspects it later (bit 2: a count overflowed ``dtype``; bits 8 | 16:
+    a bucket list / ring overflowed) and redoes the window if needed.
     """
     global launch_count
     lib = _lib.load()
@@ -492,6 +496,9 @@ def sampler_freq(src, nrep: int | None = None, nsamp: int | None = None, ndat: i
                                   ws_bytes, _stream_ptr())
     check(st, "txb_sampler_freq")
     launch_count += 2
+    if status_out is not None:
+        status_out.append(status)
+        return buf[:, : plan.ndat]
     if buckets and int(status.item()) & 24:  # a bucket list / ring overflowed its margin: redo with atomics
         return sampler_freq(plan, dtype=dtype, reps=reps, buckets=False, out=out)
     _sampler_flags(status, "txb_sampler_freq")
@@ -730,49 +737,78 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     if table_bytes is None:
         table_bytes = free_table_bytes()
     ldf = -(-ndat // 16) * 16
-    out = None
-    dtype = torch.uint8
     first, last = _window(plan, reps)
-    lo = first
     ev = [] if timing is not None else None
-    table = None  # one allocation serves every window (no 10-GB-class alloc / free per window)
+    win = max(128, int(table_bytes // ldf) // 128 * 128)
+    # one uint8 table serves every window.  The windows are issued back to back with NO host synchronisation:
+    # each window's status word stays on the device and all of them are read once at the end.  A window whose
+    # status reports an overflowed count (a sample drawn > 255 times) or an overflowed bucket list is then redone
+    # on the careful path (int32 table / global atomics) -- a < 1e-12 event at bootstrap sizes.
+    table = torch.empty((min(win, last - first), ldf), dtype=torch.uint8, device=dev)
+    # scratch of the bucketed histogram, sized once (no driver query per window)
+    lib = _lib.load()
+    want = lib.txb_sampler_freq_workspace_bytes(plan.ndat, plan.nrep, plan.nsamp, table.shape[0])
+    held = _workspaces.get((dev.index or 0, torch.cuda.current_stream().cuda_stream))
+    free = torch.cuda.mem_get_info(dev)[0] + (held.numel() if held is not None else 0)
+    scratch = max(0, min(want, free // 2) - plan.head.numel())
+    out = None
+    pending: list = []
+    spans: list = []
+    lo = first
     while lo < last:
-        esz = torch.empty((), dtype=dtype).element_size()
-        win = max(128, int(table_bytes // (ldf * esz)) // 128 * 128)
         hi = min(last, lo + win)
-        if table is None or table.dtype != dtype:
-            table = None
-            table = torch.empty((min(win, last - lo), -(-ndat * esz // 16) * 16 // esz), dtype=dtype, device=dev)
         marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if ev is not None else None
         if marks:
             marks[0].record()
-        try:
-            freq = sampler_freq(plan, dtype=dtype, reps=(lo, hi), out=table)
-        except OverflowError:
-            if dtype == torch.int32:
-                raise
-            dtype = torch.int32  # a sample drawn > 255 times in one replicate: widen and redo this window
-            continue
+        freq = sampler_freq(plan, dtype=torch.uint8, reps=(lo, hi), out=table, status_out=pending,
+                            scratch_bytes=scratch)
         if marks:
             marks[1].record()
         part = resample_vals(xs, us, freq, order, w=w, x_is_u=x_is_u)
         if marks:
             marks[2].record()
             ev.append(marks)
-        del freq
+        spans.append((lo, hi))
         if lo == first and hi == last:
             out = part
-            break
-        if out is None:
-            out = torch.empty((last - first, *part.shape[1:]), dtype=torch.float64, device=dev)
-        out[lo - first : hi - first] = part
+        else:
+            if out is None:
+                out = torch.empty((last - first, *part.shape[1:]), dtype=torch.float64, device=dev)
+            out[lo - first : hi - first] = part
         lo = hi
+    flags = torch.cat(pending).cpu().tolist()   # the one synchronisation of the call
+    del table
+    for (lo, hi), flag in zip(spans, flags):
+        if flag & 4:
+            raise _lib.TxbError("txb_sampler_freq: raw-draw range estimate too short (report this)")
+        if flag & (2 | 24):
+            part = _resample_window_careful(plan, xs, us, order, w, x_is_u, lo, hi, overflow=bool(flag & 2))
+            out[lo - first : hi - first] = part
     if ev is not None:
         torch.cuda.synchronize(dev)
         timing["freq_ms"] = sum(m[0].elapsed_time(m[1]) for m in ev)
         timing["contract_ms"] = sum(m[1].elapsed_time(m[2]) for m in ev)
         timing["windows"] = len(ev)
     return out
+
+
+def _resample_window_careful(plan, xs, us, order, w, x_is_u, lo, hi, overflow: bool) -> torch.Tensor:
+    """Redo one replicate window of :func:`sampler_resample_wide` whose fast pass flagged a problem: an int32
+    table when a uint8 count overflowed, global atomics when a bucket list / ring overflowed."""
+    dtype = torch.int32 if overflow else torch.uint8
+    step = max(1, min(hi - lo, int(free_table_bytes() // (plan.ndat * (4 if overflow else 1) + 64))))
+    parts = []
+    for a in range(lo, hi, step):
+        b = min(hi, a + step)
+        try:
+            freq = sampler_freq(plan, dtype=dtype, reps=(a, b), buckets=False)
+        except OverflowError:
+            if dtype == torch.int32:
+                raise
+            freq = sampler_freq(plan, dtype=torch.int32, reps=(a, b), buckets=False)
+        parts.append(resample_vals(xs, us, freq, order, w=w, x_is_u=x_is_u))
+        del freq
+    return torch.cat(parts)
 
 
 def _tails(data, dev):
