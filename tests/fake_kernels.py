@@ -242,3 +242,47 @@ def perturb_predict(x, u, dalpha):
     from oracle import perturb as op
 
     return _t(op.perturb_predict(_np(x), _np(u), dalpha))
+
+
+# ------------------------------------------------------------------ K7 device-resident stand-ins
+BETA_FAMILIES = {("x_ave", True): 0, ("u_ave", True): 1, ("x_ave", False): 2, ("u_ave", False): 3}
+BETA_MAX_ORDER = 8   # what the oracle's golden expressions cover
+PREDICT_DERIVS = 3
+
+
+def beta_predict(comom, order, family, dalpha=None, minus_log=False, mode=0, norm=False):
+    from oracle import derivs as od
+
+    c = _np(comom)
+    if minus_log and order > 5:   # beyond the golden -log expressions: restate the recurrence (host-logic tests only)
+        import math
+
+        d = od.beta_derivs(c, order, family).astype(np.longdouble)
+        g = np.empty_like(d)
+        g[0] = np.log(d[0])
+        for n in range(1, order + 1):
+            s = d[n].copy()
+            for k in range(1, n):
+                s -= math.comb(n - 1, k) * d[k] * g[n - k]
+            g[n] = s / d[0]
+        der = (-g).astype(np.float64)
+        fact = np.array([math.factorial(i) for i in range(order + 1)], dtype=np.float64)[:, None]
+        if mode == PREDICT_DERIVS:
+            return _t(der / fact if norm else der)
+        return poly_predict(_t(der / fact), dalpha, mode)
+    if mode == PREDICT_DERIVS:
+        return _t(od.beta_derivs(c, order, family, minus_log=minus_log, norm=norm))
+    return _t(od.beta_predict(c, order, family, dalpha, minus_log=minus_log, mode=mode))
+
+
+def combine(W, D, out=None):
+    res = np.asarray(_np(W), dtype=np.float64) @ _np(D)
+    if out is not None:
+        out += _t(res)
+        return out
+    return _t(res)
+
+
+def mean_var(arr, ddof=0):
+    a = _np(arr)
+    return _t(a.mean(axis=1)), _t(a.var(axis=1, ddof=ddof))

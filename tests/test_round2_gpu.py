@@ -4,6 +4,8 @@ Tolerance: integers bit-exact; fp64 ``|a - b| <= 1e-10 * max(|b|, sigma_x^i sigm
 with the SURVEY.md 8c scale: odd central moments are ~ 0, plain rtol is ill-posed there).
 """
 
+import math
+
 import numpy as np
 import pytest
 
@@ -265,3 +267,99 @@ def test_scatter_thread_forms_agree(K):
             close(got[nth].reshape(ref_b.shape), ref_b, oc.tolerance_scale(x, u, order))
     finally:
         lib.txb_set_scatter_threads(prev)
+
+
+# ------------------------------------------------------------------ K7 generated device functions vs the oracle
+def _records(seed, nelem, k, x_is_u=False):
+    """Central comoment records [nelem, 2, k+1] of genuinely different sample sets (one per element)."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((nelem, 2, k + 1))
+    for e in range(nelem):
+        u = rng.normal(1.0 + 0.1 * e, 0.4, 500)
+        x = u if x_is_u else 3.0 + 0.5 * u + 0.2 * u * u + rng.normal(0.0, 0.1, 500)
+        out[e] = oc.comoments_two_pass(x, u, k)[0] if np.ndim(x) > 1 else oc.comoments_two_pass(x, u, k).reshape(2, k + 1)
+    return out
+
+
+@pytest.mark.parametrize("family", [0, 1, 2, 3])
+@pytest.mark.parametrize("order", [0, 1, 3, 6, 8])
+def test_beta_fused_derivs_and_predict_match_oracle(K, family, order):
+    """txb_beta_predict_f64 (generated device functions) against oracle/derivs.py, which lambdifies the REFERENCE's
+    expression strings (tests/golden/exprs.json): derivatives, normalised coefficients, and the three Taylor modes.
+    Scale: sum over the polynomial's |coef| |moment| products (the terms cancel)."""
+    from oracle import derivs as od
+    from test_fused_k7 import _term_scales
+
+    rec = _records(40 + family, 37, order + 1, x_is_u=family in (1, 3))   # records carry one moment more than needed
+    S = _term_scales(rec, family, order)
+    ref = od.beta_derivs(rec, order, family)
+    got = K.beta_predict(rec, order, family, mode=K.PREDICT_DERIVS).cpu().numpy()
+    close(got, ref, S)
+    fact = np.array([math.factorial(i) for i in range(order + 1)], dtype=float)[:, None]
+    close(K.beta_predict(rec, order, family, mode=K.PREDICT_DERIVS, norm=True).cpu().numpy(), ref / fact, S / fact)
+    dal = np.array([-0.3, 0.05, 0.4])
+    w = np.abs(dal)[:, None] ** np.arange(order + 1)[None, :] / fact[:, 0][None, :]
+    terms = w[:, :, None] * S[None]
+    for mode, sc in ((K.PREDICT_SUM, terms.sum(1)), (K.PREDICT_CUMSUM, np.cumsum(terms, 1)), (K.PREDICT_TERMS, terms)):
+        close(K.beta_predict(rec, order, family, dal, mode=mode).cpu().numpy(),
+              od.beta_predict(rec, order, family, dal, mode=mode), sc)
+
+
+@pytest.mark.parametrize("family", [0, 2])
+@pytest.mark.parametrize("order", [1, 3, 5])
+def test_beta_fused_minus_log_matches_reference_expressions(K, family, order):
+    """The in-kernel -log recurrence against the reference's SymMinusLog expressions (golden, orders <= 5)."""
+    from oracle import derivs as od
+    from test_fused_k7 import _term_scales
+
+    rec = _records(50 + family, 29, order)
+    ref = od.beta_derivs(rec, order, family, minus_log=True)
+    got = K.beta_predict(rec, order, family, minus_log=True, mode=K.PREDICT_DERIVS).cpu().numpy()
+    S = np.maximum.accumulate(_term_scales(rec, family, order), 0) * 2.0**order / np.abs(rec[:, 1, 0]).min()
+    close(got, ref, S)
+
+
+def test_beta_fused_orders_9_10_match_the_expression_table_kernel(K):
+    """Orders beyond the golden file: the generated functions against the table interpreter fed with the package's
+    sympy expressions (themselves golden-pinned to order 8 and recurrence-checked beyond, tests/test_beta_codegen.py)."""
+    import thermoextrap_b200 as xtrap
+    from thermoextrap_b200 import models
+    from thermoextrap_b200.core.xr import DataArray
+
+    rng = np.random.default_rng(9)
+    u = rng.normal(1.0, 0.3, 4000)
+    x = 2.0 + 0.4 * u[:, None] + rng.normal(0.0, 0.05, (4000, 3))
+    for central in (True, False):
+        data = xtrap.DataCentralMomentsVals.from_vals(xv=DataArray(x, dims=("rec", "val")), uv=DataArray(u, dims=("rec",)),
+                                                      order=10, central=central)
+        m = xtrap.beta.factory_extrapmodel(beta=1.0, data=data)
+        models.FUSED_K7 = True
+        fast = m.derivs().values
+        try:
+            models.FUSED_K7 = False
+            slow = xtrap.beta.factory_extrapmodel(beta=1.0, data=data).derivs().values
+        finally:
+            models.FUSED_K7 = True
+        from test_fused_k7 import _term_scales
+
+        close(fast, slow, _term_scales(data.values.values, 0 if central else 2, 10))
+
+
+def test_combine_and_mean_var_kernels(K):
+    rng = np.random.default_rng(4)
+    W, D = rng.normal(size=(19, 35)), rng.normal(size=(35, 3001))
+    ref = W.astype(np.longdouble) @ D.astype(np.longdouble)
+    sc = np.abs(W) @ np.abs(D)
+    out = K.combine(W, D)
+    close(out.cpu().numpy(), ref.astype(float), sc)
+    out = K.combine(W, D, out=out)
+    close(out.cpu().numpy(), (2 * ref).astype(float), 2 * sc)
+    arr = rng.normal(5.0, 2.0, (7, 10_000, 64)) * np.logspace(-3, 3, 64)
+    for ddof in (0, 1):
+        mean, var = K.mean_var(arr, ddof=ddof)
+        ld = arr.astype(np.longdouble)
+        close(mean.cpu().numpy(), ld.mean(1).astype(float), np.abs(arr).mean(1))
+        close(var.cpu().numpy(), ld.var(1, ddof=ddof).astype(float), 0.0)
+    one = rng.normal(size=(2, 1, 3))
+    mean, var = K.mean_var(one)
+    assert np.array_equal(mean.cpu().numpy(), one[:, 0]) and not var.cpu().numpy().any()

@@ -18,7 +18,7 @@ import importlib
 
 __version__ = "0.1.0"
 
-_SUBMODULES = ["backend", "beta", "data", "idealgas", "kernels", "lnpi", "models", "parallel", "streaming", "volume",
+_SUBMODULES = ["backend", "beta", "data", "idealgas", "kernels", "lnpi", "models", "parallel", "stack", "streaming", "volume",
                "volume_idealgas"]
 _ATTRS = {
     "data": ["DataCentralMoments", "DataCentralMomentsVals", "DataValues", "DataValuesCentral", "factory_data_values"],

@@ -381,6 +381,21 @@ class CentralMomentsData:
                 msg = f"moment dimension {d!r} not in {obj.dims}"
                 raise ValueError(msg)
         self.obj = obj.transpose(..., *self.mom_dims)
+        # device-resident copy of ``obj.values`` (same shape, dims order ``_dev_dims``) when a kernel of this
+        # package produced the array: the fused K7 kernels read it in place (models.ExtrapModel.predict)
+        self._dev = None
+        self._dev_dims: tuple = ()
+
+    def _set_dev(self, tensor, dims) -> CentralMomentsData:
+        if tensor is not None and tuple(dims) == tuple(self.obj.dims) and tuple(tensor.shape) == tuple(self.obj.shape):
+            self._dev, self._dev_dims = tensor, tuple(dims)
+        return self
+
+    def device_records(self):
+        """The comoment array on the device (contiguous, dims as ``obj.dims``), or None if it only lives on the host."""
+        if self._dev is not None and self._dev_dims == tuple(self.obj.dims):
+            return self._dev
+        return None
 
     # -- protocol ------------------------------------------------------------
     @property
@@ -406,7 +421,7 @@ class CentralMomentsData:
         lead = [d for d in dims if d is Ellipsis or d not in self.mom_dims]
         if Ellipsis not in lead:
             lead.append(...)
-        return self.new_like(self.obj.transpose(*lead, *self.mom_dims))
+        return self.new_like(self.obj.transpose(*lead, *self.mom_dims))._set_dev(self._dev, self._dev_dims)
 
     def _convert(self, kind: int) -> DataArray:
         if self.mom_ndim == 2:
@@ -541,8 +556,11 @@ def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dim
         raise ValueError(msg)
     if u.ndim == 1:
         xd, ud = to_device(np.asarray(x.values, dtype=np.float64)), to_device(np.asarray(u.values, dtype=np.float64))
-        out = _host(K.reduce_vals(xd, ud, k, w=wd) if _dist is None else _dist.reduce_vals(xd, ud, k, w=wd))
-        return CentralMomentsData(DataArray(out, dims=(*rest_dims, *md)), mom_ndim=2, mom_dims=md)
+        dev_out = K.reduce_vals(xd, ud, k, w=wd) if _dist is None else _dist.reduce_vals(xd, ud, k, w=wd)
+        out = _host(dev_out)
+        dims = (*rest_dims, *md)
+        return CentralMomentsData(DataArray(out, dims=dims), mom_ndim=2, mom_dims=md)._set_dev(
+            dev_out.reshape(out.shape), dims)
     if _dist is not None:
         msg = "N-GPU mode supports u[rec] only"
         raise NotImplementedError(msg)
@@ -593,13 +611,16 @@ def wrap_resample_vals(
     wd = None if weight is None else to_device(np.ascontiguousarray(weight.values, dtype=np.float64))
     xd = to_device(np.asarray(x.values, dtype=np.float64))
     ud = to_device(np.asarray(u.values, dtype=np.float64))
-    out = _host(resample_device(xd, ud, wd, sampler, k))
+    dev_out = resample_device(xd, ud, wd, sampler, k)
+    out = _host(dev_out)
     rest_dims = x.dims[1:]
-    res = DataArray(out, dims=(rep_dim, *rest_dims, *md))
+    res0 = DataArray(out, dims=(rep_dim, *rest_dims, *md))
+    res = res0
     if x_in_dims is not None:
         order = [rep_dim if d == dim else d for d in x_in_dims]
         res = res.transpose(*order, *md)
-    return CentralMomentsData(res, mom_ndim=2, mom_dims=md)
+    # keep the kernel's output on the device beside the host copy (same layout unless the caller's dims differ)
+    return CentralMomentsData(res, mom_ndim=2, mom_dims=md)._set_dev(dev_out.reshape(out.shape), res0.dims)
 
 
 # byte budget of one frequency-table window of the wide-x bootstrap (None: a third of free device memory)

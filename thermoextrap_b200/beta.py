@@ -307,7 +307,11 @@ def factory_derivatives(name="x_ave", n=None, d=None, xalpha=False, central=None
     derivs = SymDerivBeta.from_name(name=name, n=n, d=d, xalpha=xalpha, central=central, post_func=post_func,
                                     expand=expand)
     exprs = SymSubs(derivs, subs_all={derivs.beta: "None"}, expand=False, simplify=False)
-    return Derivatives.from_sympy(exprs, args=derivs.args)
+    # the plain beta derivatives of <x> / <u> also exist as generated device functions (kernels.BETA_FAMILIES)
+    family = None
+    if name in {"x_ave", "u_ave"} and not xalpha and post_func is None and n is None and d is None:
+        family = {("x_ave", True): 0, ("u_ave", True): 1, ("x_ave", False): 2, ("u_ave", False): 3}[(name, bool(central))]
+    return Derivatives.from_sympy(exprs, args=derivs.args, family=family)
 
 
 def factory_extrapmodel(beta, data, *, name="x_ave", n=None, d=None, xalpha=None, central=None, order=None,

@@ -952,3 +952,85 @@ def perturb_predict(x, u, dalpha) -> torch.Tensor:
     check(st, "txb_perturb_predict_f64")
     launch_count += 4
     return out.reshape(nalpha, *val_shape)
+
+
+# ------------------------------------------------------------------ K7 device-resident (derivs_fused.cu)
+#: (name, central) -> family index of txb_beta_predict_f64 (the four numeric beta families)
+BETA_FAMILIES = {("x_ave", True): 0, ("u_ave", True): 1, ("x_ave", False): 2, ("u_ave", False): 3}
+BETA_MAX_ORDER = 10
+PREDICT_DERIVS = 3
+
+
+def beta_predict(comom, order: int, family: int, dalpha=None, minus_log: bool = False, mode: int = PREDICT_SUM,
+                 norm: bool = False) -> torch.Tensor:
+    """Comoment records ``comom[..., 2, K+1]`` (device) -> beta derivatives -> Taylor prediction, one launch.
+
+    ``mode`` ``PREDICT_SUM``: ``[nalpha, nelem]``; ``PREDICT_CUMSUM`` / ``PREDICT_TERMS``: ``[nalpha, order+1, nelem]``;
+    ``PREDICT_DERIVS``: the derivatives ``[order+1, nelem]`` (divided by ``i!`` when ``norm``).  ``nelem`` is the
+    product of the leading dims of ``comom``.  Generated device functions: orders <= ``BETA_MAX_ORDER``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    c = _as_f64(comom, dev)
+    if c.ndim < 2 or c.shape[-2] != 2 or not c.is_contiguous():
+        msg = f"comom must be a contiguous [..., 2, K+1] array; got {tuple(c.shape)}"
+        raise ValueError(msg)
+    kdim = c.shape[-1]
+    nelem = c.numel() // (2 * kdim)
+    flags = (1 if minus_log else 0) | (2 if norm else 0)
+    if mode == PREDICT_DERIVS:
+        d, na = None, 0
+        shape = (order + 1, nelem)
+    else:
+        d = _as_f64(np.atleast_1d(np.asarray(dalpha, dtype=np.float64)), dev)
+        na = d.shape[0]
+        shape = (na, nelem) if mode == PREDICT_SUM else (na, order + 1, nelem)
+    out = torch.empty(shape, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_beta_predict_f64(c.data_ptr(), nelem, kdim, family, order, flags, mode, _ptr(d), na,
+                                      out.data_ptr(), _stream_ptr())
+    check(st, "txb_beta_predict_f64")
+    launch_count += 1
+    return out
+
+
+def combine(W, D, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``out[a, e] (+)= sum_t W[a, t] D[t, e]`` on the device; accumulates into ``out`` when it is given."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    Wd = _as_f64(np.ascontiguousarray(W, dtype=np.float64) if isinstance(W, np.ndarray) else W, dev).contiguous()
+    Dd = _as_f64(D, dev).contiguous()
+    na, nt = Wd.shape
+    if Dd.shape[0] != nt:
+        msg = f"W[{na}, {nt}] does not match D{tuple(Dd.shape)}"
+        raise ValueError(msg)
+    nelem = Dd.shape[1]
+    acc = out is not None
+    if out is None:
+        out = torch.empty((na, nelem), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_combine_f64(Wd.data_ptr(), na, nt, Dd.data_ptr(), nelem, 1 if acc else 0, out.data_ptr(),
+                                 _stream_ptr())
+    check(st, "txb_combine_f64")
+    launch_count += 1
+    return out
+
+
+def mean_var(arr, ddof: int = 0):
+    """``(mean[A, B], var[A, B])`` over the middle axis of ``arr[A, R, B]`` (device), one pass (Welford + Chan)."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    a = _as_f64(arr, dev).contiguous()
+    if a.ndim != 3:
+        msg = f"mean_var needs a 3-D [A, R, B] array; got {tuple(a.shape)}"
+        raise ValueError(msg)
+    A, R, B = a.shape
+    mean = torch.empty((A, B), dtype=torch.float64, device=dev)
+    var = torch.empty((A, B), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_mean_var_f64(a.data_ptr(), A, R, B, int(ddof), mean.data_ptr(), var.data_ptr(), _stream_ptr())
+    check(st, "txb_mean_var_f64")
+    launch_count += 1
+    return mean, var

@@ -315,6 +315,9 @@ class Derivatives(MyAttrsMixin):
     funcs: Any = field()
     exprs: Any = field(kw_only=True, default=None)
     args: Sequence | None = field(kw_only=True, default=None)
+    #: index of the generated device function family (``kernels.BETA_FAMILIES``) when these are the plain
+    #: beta derivatives of ``x_ave`` / ``u_ave``: models then evaluate them on the device in one fused launch
+    family: int | None = field(kw_only=True, default=None)
     _cache: dict = field(init=False, repr=False, factory=dict)
 
     @cached.meth
@@ -361,8 +364,8 @@ class Derivatives(MyAttrsMixin):
         return self.derivs(data=data, args=args, order=order, minus_log=minus_log, order_dim=order_dim, norm=True)
 
     @classmethod
-    def from_sympy(cls, exprs, args):
-        return cls(funcs=Lambdify(exprs, args=args), exprs=exprs, args=args)
+    def from_sympy(cls, exprs, args, family=None):
+        return cls(funcs=Lambdify(exprs, args=args), exprs=exprs, args=args, family=family)
 
 
 @lru_cache(10)
@@ -375,6 +378,36 @@ def taylor_series_norm(order, order_dim="order"):
 ################################################################################
 # models
 ################################################################################
+#: evaluate the numeric beta families with the generated device functions (``txb_beta_predict_f64``) straight
+#: from the comoment records the kernels left on the device; False forces the expression-table path
+FUSED_K7 = True
+
+
+def _fused_records(model, order):
+    """``(records, lead_dims, lead_shape, coords)`` when ``model`` qualifies for the fused K7 kernels: plain beta
+    derivatives of ``x_ave`` / ``u_ave`` (``derivatives.family``), comoment data whose array a kernel of this package
+    left on the device, no ``deriv`` dimension, the default ``meta`` callback, order within the generated range."""
+    from .data import DataCallback, DataCentralMomentsBase
+
+    fam = getattr(model.derivatives, "family", None)
+    data = model.data
+    if not FUSED_K7 or fam is None or not isinstance(data, DataCentralMomentsBase):
+        return None
+    if order > min(cm.K.BETA_MAX_ORDER, data.order) or data.xalpha or type(data.meta) is not DataCallback:
+        return None
+    if bool(data.central) != (fam < 2) or bool(data.x_is_u) != (fam in (1, 3)):
+        return None
+    if data.dxduave.mom_ndim != 2 or tuple(data.dxduave.mom_dims) != (data.xmom_dim, data.umom_dim):
+        return None
+    rec = data.dxduave.device_records()
+    if rec is None:
+        return None
+    obj = data.dxduave.obj
+    lead_dims = tuple(obj.dims[:-2])
+    coords = {k: np.asarray(c.values) for k, c in obj.coords.items() if k in lead_dims}
+    return rec, lead_dims, tuple(obj.shape[:-2]), coords
+
+
 def _predict_series(coefs: DataArray, order_dim: str, dvals: np.ndarray, mode: int) -> np.ndarray:
     """``sum_p coefs[p] * d**p`` on the device; returns ``[nd, (np1,) *rest]``."""
     c = coefs.transpose(order_dim, ...)
@@ -399,6 +432,12 @@ class ExtrapModel(MyAttrsMixin):
 
     @cached.meth
     def _derivs(self, order, order_dim, minus_log):
+        fused = _fused_records(self, order) if order_dim is not None else None
+        if fused is not None:
+            rec, lead_dims, lead_shape, coords = fused
+            out = cm._host(cm.K.beta_predict(rec, order, self.derivatives.family, minus_log=bool(minus_log),
+                                             mode=cm.K.PREDICT_DERIVS))
+            return DataArray(out.reshape(order + 1, *lead_shape), dims=(order_dim, *lead_dims), coords=coords or None)
         return self.derivatives.derivs(
             data=self.data, order=order, norm=False, minus_log=minus_log, order_dim=order_dim
         )
@@ -426,7 +465,8 @@ class ExtrapModel(MyAttrsMixin):
             order = self.order
         if alpha_name is None:
             alpha_name = self.alpha_name
-        coefs = self.coefs(order=order, order_dim=order_dim, minus_log=minus_log)
+        if minus_log is None:
+            minus_log = self.minus_log
         alpha = xrwrap_alpha(alpha, name=alpha_name)
         dalpha = alpha - self.alpha0
         if alpha.ndim > 1:
@@ -434,12 +474,23 @@ class ExtrapModel(MyAttrsMixin):
             raise ValueError(msg)
         mode = cm.K.PREDICT_TERMS if no_sum else (cm.K.PREDICT_CUMSUM if cumsum else cm.K.PREDICT_SUM)
         dvals = np.atleast_1d(np.asarray(dalpha.values, dtype=np.float64))
-        vals, rest_dims = _predict_series(coefs, order_dim, dvals, mode)
+        fused = _fused_records(self, order)
+        if fused is not None:
+            # records -> derivatives -> -log -> / i! -> Taylor sum in ONE launch; only the predictions come back
+            rec, rest_dims, lead_shape, fcoords = fused
+            vals = cm._host(cm.K.beta_predict(rec, order, self.derivatives.family, dvals, minus_log=bool(minus_log),
+                                              mode=mode))
+            lead = (len(dvals),) if mode == cm.K.PREDICT_SUM else (len(dvals), order + 1)
+            vals = vals.reshape(*lead, *lead_shape)
+            coords = {alpha_name: np.atleast_1d(np.asarray(alpha.values)), **fcoords}
+        else:
+            coefs = self.coefs(order=order, order_dim=order_dim, minus_log=minus_log)
+            vals, rest_dims = _predict_series(coefs, order_dim, dvals, mode)
+            coords = {alpha_name: np.atleast_1d(np.asarray(alpha.values))}
+            for k, c in coefs.coords.items():
+                if k in rest_dims:
+                    coords[k] = np.asarray(c.values)
         dims = [alpha_name] + ([order_dim] if mode != cm.K.PREDICT_SUM else []) + list(rest_dims)
-        coords = {alpha_name: np.atleast_1d(np.asarray(alpha.values))}
-        for k, c in coefs.coords.items():
-            if k in rest_dims:
-                coords[k] = np.asarray(c.values)
         out = DataArray(vals, dims=dims, coords=coords)
         if dalpha_coords is not None:
             out = out.assign_coords({dalpha_coords: (alpha_name, dvals)})
@@ -605,9 +656,8 @@ class InterpModel(StateCollection):
     """Polynomial through the derivatives of all states (generalised Hermite interpolation)."""
 
     @cached.meth
-    def coefs(self, order=None, order_dim="porder", minus_log=None):
-        if order is None:
-            order = self.order
+    def _mat_inv(self, order) -> np.ndarray:
+        """Inverse of the generalised Hermite matrix, ``[npoly, nstate, order+1]`` (models.py:877-893)."""
         nstate = len(self)
         npoly = nstate * (order + 1)
         from scipy.special import factorial as sp_factorial
@@ -624,8 +674,33 @@ class InterpModel(StateCollection):
                 ok = power >= j
                 pj = np.where(ok, power - j, 0)
                 mat[i * (order + 1) + j] = np.where(ok, (a**pj) * fact / sp_factorial(pj), 0.0)
-        mat_inv = np.linalg.inv(mat).reshape(npoly, nstate, order + 1)
-        mat_inv = DataArray(mat_inv, dims=[order_dim, "state", "order"])
+        return np.linalg.inv(mat).reshape(npoly, nstate, order + 1)
+
+    def _fused_coefs(self, order, minus_log):
+        """Polynomial coefficients ``[npoly, nelem]`` ON THE DEVICE when every state qualifies for the fused K7
+        kernels (same leading dims): per state one launch for the derivatives of all records, one for its share of
+        ``mat_inv . derivs``.  Returns ``(coefs_dev, lead_dims, lead_shape, coords)`` or None."""
+        fused = [_fused_records(m, order) for m in self.states]
+        if any(f is None for f in fused) or len({(f[1], f[2]) for f in fused}) != 1:
+            return None
+        mat_inv = self._mat_inv(order)
+        coefs_dev = None
+        for s, (m, f) in enumerate(zip(self.states, fused)):
+            ml = m.minus_log if minus_log is None else minus_log
+            d = cm.K.beta_predict(f[0], order, m.derivatives.family, minus_log=bool(ml), mode=cm.K.PREDICT_DERIVS)
+            coefs_dev = cm.K.combine(np.ascontiguousarray(mat_inv[:, s, :]), d, out=coefs_dev)
+        return coefs_dev, fused[0][1], fused[0][2], fused[0][3]
+
+    @cached.meth
+    def coefs(self, order=None, order_dim="porder", minus_log=None):
+        if order is None:
+            order = self.order
+        fused = self._fused_coefs(order, minus_log)
+        if fused is not None:
+            coefs_dev, lead_dims, lead_shape, coords = fused
+            vals = cm._host(coefs_dev).reshape(-1, *lead_shape)
+            return DataArray(vals, dims=(order_dim, *lead_dims), coords=coords or None)
+        mat_inv = DataArray(self._mat_inv(order), dims=[order_dim, "state", "order"])
         derivs = concat(
             [m.derivs(order, norm=False, minus_log=minus_log, order_dim="order") for m in self.states], dim="state"
         )
@@ -636,14 +711,21 @@ class InterpModel(StateCollection):
             order = self.order
         if alpha_name is None:
             alpha_name = self.alpha_name
-        coefs = self.coefs(order=order, order_dim=order_dim, minus_log=minus_log)
         alpha = xrwrap_alpha(alpha, name=alpha_name)
         avals = np.atleast_1d(np.asarray(alpha.values, dtype=np.float64))
-        vals, rest_dims = _predict_series(coefs, order_dim, avals, cm.K.PREDICT_SUM)
-        coords = {alpha_name: avals}
-        for k, c in coefs.coords.items():
-            if k in rest_dims:
-                coords[k] = np.asarray(c.values)
+        fused = self._fused_coefs(order, minus_log)
+        if fused is not None:
+            # derivatives, mat_inv . derivs and the polynomial all stay on the device: one D2H of [alpha, *lead]
+            coefs_dev, rest_dims, lead_shape, fcoords = fused
+            vals = cm._host(cm.K.poly_predict(coefs_dev, avals, cm.K.PREDICT_SUM)).reshape(len(avals), *lead_shape)
+            coords = {alpha_name: avals, **fcoords}
+        else:
+            coefs = self.coefs(order=order, order_dim=order_dim, minus_log=minus_log)
+            vals, rest_dims = _predict_series(coefs, order_dim, avals, cm.K.PREDICT_SUM)
+            coords = {alpha_name: avals}
+            for k, c in coefs.coords.items():
+                if k in rest_dims:
+                    coords[k] = np.asarray(c.values)
         out = DataArray(vals, dims=[alpha_name, *rest_dims], coords=coords)
         return out.isel({alpha_name: 0}) if alpha.ndim == 0 else out
 
