@@ -348,7 +348,7 @@ int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double*
 int txb_set_resample_kernel(int version);
 
 /* Threads per CTA of the draw-partition kernel (k_bucket_scatter) behind txb_sampler_resample_f64 and
- * txb_sampler_freq: 1024 (default; 4 LCG steps per thread and iteration) or 512 (8 steps, round 1).  Identical
+ * txb_sampler_freq: 512 (default; 8 LCG steps per thread and iteration) or 1024 (4 steps; measured 2 % slower).  Identical
  * output (the lists hold the same draws); exists to A/B the forms in one process (also TXB_SCATTER_THREADS).
  * Returns the previous setting; other values only query.  No counterpart in the reference.             */
 int txb_set_scatter_threads(int nthreads);

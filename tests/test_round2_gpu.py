@@ -234,8 +234,8 @@ def test_wide_contraction_kernel_forms_match_oracle(K, version, dtype, n, nv, nr
 
 # ------------------------------------------------------------------ partition kernel: 512- and 1024-thread forms
 def test_scatter_thread_forms_agree(K):
-    """``txb_set_scatter_threads``: the 1024-thread partition kernel (4 LCG steps per thread, the default) and the
-    512-thread form (8 steps) walk the same 4096-step iterations of numpy's stream: frequency tables bit-identical
+    """``txb_set_scatter_threads``: the 1024-thread partition kernel (4 LCG steps per thread) and the 512-thread
+    form (8 steps, the default) walk the same 4096-step iterations of numpy's stream: frequency tables bit-identical
     (and equal to numpy's own table), scalar bootstrap sums equal to rounding (list order differs)."""
     import torch
 

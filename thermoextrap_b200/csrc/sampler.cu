@@ -527,12 +527,15 @@ inline Affine mk_affine(u128 a, u128 c) {
     return Affine{(uint64_t)(a >> 64), (uint64_t)a, (uint64_t)(c >> 64), (uint64_t)c};
 }
 
-// threads of the partition kernel: 1024 unless TXB_SCATTER_THREADS=512 / txb_set_scatter_threads(512)
+// threads of the partition kernel: 512 unless TXB_SCATTER_THREADS=1024 / txb_set_scatter_threads(1024).  Measured
+// (profiles/r02_exp_mma_forms.json): 512 threads 100.5 ms, 1024 threads 102.5 ms per 128-replicate window of 1e8 draws;
+// ncu (profiles/r02_target_kernels_ncu_full.txt): the kernel is instruction-bound (ALU 35 % + IMAD 17 % of the pipes,
+// 44 % issue-active), so twice the warps with 18 % more instructions does not pay.
 int g_scatter_threads = -1;
 inline int scatter_threads() {
     if (g_scatter_threads < 0) {
         const char* e = getenv("TXB_SCATTER_THREADS");
-        g_scatter_threads = (e && atoi(e) == 512) ? 512 : 1024;
+        g_scatter_threads = (e && atoi(e) == 1024) ? 1024 : 512;
     }
     return g_scatter_threads;
 }
@@ -834,10 +837,26 @@ struct SegPlan {
 
 SegPlan seg_plan(const BucketPlan& b, int64_t nsamp, int ks, int64_t nwin) {
     SegPlan s{};
-    int64_t nseg = (4 * (int64_t)sm_count() + nwin - 1) / nwin;  // >= 4 CTAs per SM in flight overall
+    // one CTA per SM at a time (the rings fill shared memory): choose the number of segments per replicate so
+    // that the CTA count fills whole waves.  ncu of round 1's rule (>= 4 CTAs per SM overall) showed 640 CTAs
+    // for a 128-replicate window on 148 SMs: 4.3 waves run as 5, 14 % of the kernel idle.  Candidates between
+    // ~8 and ~40 waves (startup -- binary search, 48-step jump, ring clear -- stays < 1 % of a CTA), most
+    // efficient first, fewer segments on ties.
+    const int64_t sms = sm_count();
     const int64_t max_seg = (int64_t)(b.m / (8.0 * BK_LINE));     // keep lists mostly full lines
-    if (nseg > max_seg) nseg = max_seg;
-    if (nseg < 1) nseg = 1;
+    int64_t lo_seg = (8 * sms + nwin - 1) / nwin, hi_seg = (40 * sms + nwin - 1) / nwin;
+    if (lo_seg < 1) lo_seg = 1;
+    if (hi_seg > max_seg) hi_seg = max_seg;
+    if (hi_seg > 255) hi_seg = 255;   // k_bucket_hist keeps the segment sizes in a 256-entry shared array
+    if (lo_seg > hi_seg) lo_seg = hi_seg;
+    if (lo_seg < 1) lo_seg = hi_seg = 1;
+    int64_t nseg = lo_seg;
+    double best = -1.0;
+    for (int64_t c = lo_seg; c <= hi_seg; ++c) {
+        const int64_t ctas = c * nwin, waves = (ctas + sms - 1) / sms;
+        const double eff = (double)ctas / (double)(waves * sms);
+        if (eff > best + 1e-9) best = eff, nseg = c;
+    }
     s.nseg = (int)nseg;
     s.seg_len = (nsamp + nseg - 1) / nseg;
     const double ms = b.m * (double)s.seg_len / (double)nsamp;

@@ -23,13 +23,6 @@ KEYS = [
     "smsp__average_warp_latency_issue_stalled_lg_throttle.ratio",
     "smsp__average_warp_latency_issue_stalled_mio_throttle.ratio",
     "smsp__average_warp_latency_issue_stalled_wait.ratio",
-    "smsp__average_warp_latency_issue_stalled_dispatch_stall.ratio",
-    "smsp__average_warp_latency_issue_stalled_no_instruction.ratio",
-    "smsp__average_warp_latency_issue_stalled_not_selected.ratio",
-    "smsp__average_warp_latency_issue_stalled_membar.ratio",
-    "smsp__average_warp_latency_issue_stalled_tex_throttle.ratio",
-    "smsp__average_warp_latency_issue_stalled_branch_resolving.ratio",
-    "smsp__average_warp_latency_issue_stalled_selected.ratio",
     # tensor / fp64 / integer pipe utilisation (DMMA issues on the fp64 tensor path)
     "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__pipe_tensor_op_dmma_cycles_active.avg.pct_of_peak_sustained_active",
@@ -50,7 +43,7 @@ KEYS = [
     "smsp__inst_executed_op_shared_st.sum",
 ]
 # any further pipe / tensor counters the report carries (names differ between ncu versions)
-EXTRA_SUBSTR = ("pipe_tensor", "dmma")
+EXTRA_SUBSTR = ("subpipe_dmma",)
 
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
@@ -63,6 +56,16 @@ for vals in rows[2:]:
         if k in d:
             print(f"{k:75s} {d[k][1]:>20s} {d[k][0]}")
     for k in hdr:
-        if k not in KEYS and any(sub in k for sub in EXTRA_SUBSTR) and k in d:
+        if k not in KEYS and any(sub in k for sub in EXTRA_SUBSTR) and k in d and ".avg.pct" in k:
             print(f"{k:75s} {d[k][1]:>20s} {d[k][0]}")
+    # warp stall reasons, as average warps stalled per issue-active cycle (top 8)
+    st = {}
+    for k, (_, v) in d.items():
+        if "issue_stalled" in k and k.endswith("_per_issue_active.ratio"):
+            try:
+                st[k] = float(v)
+            except ValueError:
+                pass
+    for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:8]:
+        print(f"{k:75s} {v:20.3f} warps/issue")
     print()
