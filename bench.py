@@ -563,16 +563,16 @@ def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_i
 
 # --------------------------------------------------------------------------- the other BASELINE configs (N = 1)
 def extra_configs(a, dev) -> dict:
-    """BASELINE configs 1, 2, 4, 5 as short records beside the headline (each bounded to seconds; outside the
-    timed region).  Config 3 (5 states x nrep 1e4 of the headline shape, ~50x the headline job) runs with
-    tools/config3.py and is recorded under profiles/."""
+    """BASELINE configs 1-5 as short records beside the headline (each bounded to seconds; outside the timed
+    region).  Config 3 (5 states x nrep 1e4 of the headline shape, ~50x the headline job) rides along at 1/20 of its
+    replicates; the full job on 8 GPUs is tools/config3.py under torchrun, recorded under profiles/."""
     import torch
 
     from thermoextrap_b200 import backend
     from thermoextrap_b200 import kernels as K
 
     out = {}
-    for name, fn in (("c1", config_c1), ("c2", config_c2), ("c4", config_c4), ("c5", config_c5)):
+    for name, fn in (("c1", config_c1), ("c2", config_c2), ("c3", config_c3), ("c4", config_c4), ("c5", config_c5)):
         if name == a.config:
             continue
         try:
@@ -634,6 +634,18 @@ def config_c2(dev) -> dict:
             "samples_per_s_reduce": None if "reduce" not in kern else 1e7 / (kern["reduce"]["ms_per_step"] * 1e-3),
             "whole_step_frac_fp64": flops / (step_ms * 1e-3) / 1e12 / fp64_peak_tflops(),
             "kernels": {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kern.items()}}
+
+
+def config_c3(dev) -> dict:
+    """BASELINE config 3 through the public API (5-state beta InterpModel, order 6, 1e8 x 64 per state) on ONE GPU at
+    nrep = 500 per state -- 1/20 of the config's 1e4 replicates, the only thing reduced (tools/config3.py)."""
+    sys.path.insert(0, str(ROOT / "tools"))
+    import config3
+
+    rec = config3.run(100_000_000, 64, 6, 500, 5)
+    rec["note"] = ("nrep 500 of the config's 10000 per state (1/20), everything else at full size; the full config on 8 GPUs: "
+                   "profiles/r02_config3_8gpu.json")
+    return rec
 
 
 def config_c4(dev) -> dict:

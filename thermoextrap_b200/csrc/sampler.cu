@@ -844,7 +844,10 @@ SegPlan seg_plan(const BucketPlan& b, int64_t nsamp, int ks, int64_t nwin) {
     // efficient first, fewer segments on ties.
     const int64_t sms = sm_count();
     const int64_t max_seg = (int64_t)(b.m / (8.0 * BK_LINE));     // keep lists mostly full lines
-    int64_t lo_seg = (8 * sms + nwin - 1) / nwin, hi_seg = (40 * sms + nwin - 1) / nwin;
+    // histogram consumer (ks < 0): 8 .. 40 waves.  Comoment consumer: every extra segment is one more list (and
+    // one more padded last line) per (replicate, bucket) for k_bucket_consume -- measured +1.7 ms per 5 segments
+    // at config 2 -- so stay within [1x, 2x] of round 1's rule (>= 4 CTAs per SM overall)
+    int64_t lo_seg = ((ks < 0 ? 8 : 4) * sms + nwin - 1) / nwin, hi_seg = ((ks < 0 ? 40 : 8) * sms + nwin - 1) / nwin;
     if (lo_seg < 1) lo_seg = 1;
     if (hi_seg > max_seg) hi_seg = max_seg;
     if (hi_seg > 255) hi_seg = 255;   // k_bucket_hist keeps the segment sizes in a 256-entry shared array

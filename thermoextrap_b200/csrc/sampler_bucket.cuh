@@ -373,23 +373,46 @@ __global__ void __launch_bounds__(BK_THREADS) k_bucket_hist(const HistArgs c) {
     unsigned* h = reinterpret_cast<unsigned*>(bk_smem);
     const int b = blockIdx.x;
     const int64_t r = blockIdx.y;
-    __shared__ int s_nq[256];   // 16-byte chunks of every segment's list (nseg <= 255: seg_plan's max_seg)
+    // the lists of the (replicate, bucket)'s segments are walked as ONE flattened sequence of 16-byte chunks, so
+    // that all 512 threads stay busy however the draws are split into segments (37 segments of ~220 chunks at the
+    // target shape): s_off[sg] = first flattened chunk of segment sg (exclusive scan by warp 0)
+    __shared__ int s_off[257];
     for (int i = threadIdx.x; i < NWORD; i += BK_THREADS) h[i] = 0u;
     const int64_t list0 = (r * c.nb + b) * c.nseg;
-    for (int sg = threadIdx.x; sg < c.nseg; sg += BK_THREADS) s_nq[sg] = (int)c.nlines[list0 + sg] * 4;
-    __syncthreads();
-    // the (segment, chunk) pairs of this thread, flattened; U independent 16-byte loads in flight per thread (ncu on
-    // the one-load-at-a-time loop: 58 % of the stall samples on the list load's scoreboard)
-    constexpr int U = 4;
-    int seg = 0, i = threadIdx.x;
-    auto next_chunk = [&]() -> const uint4* {
-        while (seg < c.nseg && i >= s_nq[seg]) {
-            ++seg;
-            i = threadIdx.x;
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int v[8], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int sg = lane * 8 + k;
+            v[k] = sg < c.nseg ? (int)c.nlines[list0 + sg] * 4 : 0;
+            sum += v[k];
         }
-        if (seg >= c.nseg) return nullptr;
-        const uint4* p = reinterpret_cast<const uint4*>(c.lists + (list0 + seg) * c.cap_lines * BK_LINE) + i;
-        i += BK_THREADS;
+        int inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        int run = inc - sum;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s_off[lane * 8 + k] = run;
+            run += v[k];
+        }
+        if (lane == 31) s_off[256] = run;
+    }
+    __syncthreads();
+    const int total = s_off[256];
+    // U independent 16-byte loads in flight per thread (ncu on the one-load-at-a-time loop: 58 % of the stall
+    // samples on the list load's scoreboard)
+    constexpr int U = 4;
+    int seg = 0, f = threadIdx.x;
+    auto next_chunk = [&]() -> const uint4* {
+        if (f >= total) return nullptr;
+        while (f >= s_off[seg + 1]) ++seg;
+        const uint4* p = reinterpret_cast<const uint4*>(c.lists + (list0 + seg) * c.cap_lines * BK_LINE) + (f - s_off[seg]);
+        f += BK_THREADS;
         return p;
     };
     for (;;) {

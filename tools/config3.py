@@ -1,0 +1,163 @@
+"""BASELINE config 3 through the public API: beta InterpModel across 5 state points, order 6, 1e8 samples x 64
+observable channels per state, nrep = 1e4, sharded over the GPUs of one node.
+
+    python tools/config3.py [--nrep 10000] [--nsamp 1e8] [--states 5]                       (one GPU)
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29511 tools/config3.py                                                (8 GPUs)
+
+Per state: samples are generated on the device (one seed on every rank), copied to PINNED HOST arrays (each rank its
+1/N row shard) and the device copy is freed -- from there on only the public API runs, as a user would call it:
+    DataCentralMomentsVals.from_vals (H2D + K1) -> beta.factory_extrapmodel -> .resample({"nrep", "rng"}) (K6 + K2)
+then  InterpModel(resampled states).predict(betas)  (K7: generated device functions + Hermite combine, on the device).
+N > 1: ``parallel.enable()`` -- row shards exchanged once over NVLink, the sampler's counting pass split over the
+ranks, replicates sharded, slabs all_gathered.  Prints one JSON line (rank 0); copied to profiles/ by hand.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+BETAS0 = [0.1, 2.575, 5.05, 7.525, 10.0]   # Temperature_Interp.ipynb get_betas
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--nrep", type=int, default=10_000)
+    ap.add_argument("--nsamp", type=float, default=1e8)
+    ap.add_argument("--nchan", type=int, default=64)
+    ap.add_argument("--order", type=int, default=6)
+    ap.add_argument("--states", type=int, default=5)
+    a = ap.parse_args()
+    print(json.dumps(run(int(a.nsamp), a.nchan, a.order, a.nrep, a.states)), flush=True) if int(
+        os.environ.get("RANK", "0")) == 0 else run(int(a.nsamp), a.nchan, a.order, a.nrep, a.states)
+
+
+def run(nsamp: int, nchan: int, order: int, nrep: int, nstates: int, dev=None) -> dict:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import thermoextrap_b200 as xt
+    from thermoextrap_b200 import backend
+    from thermoextrap_b200 import kernels as K
+    from thermoextrap_b200 import parallel as par
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    own_pg = False
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+        own_pg = True
+    if world > 1:
+        par.enable()
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    lo, hi = par.shard_range(nsamp, rank, world)
+    xh = torch.empty((hi - lo, nchan), dtype=torch.float64).pin_memory()
+    uh = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    betas0 = BETAS0[:nstates]
+    legs = {"generate_s": 0.0, "from_vals_s": 0.0, "resample_s": 0.0}
+    boots = []
+    backend.transfer_bytes.update(h2d=0, d2h=0)
+    sync()
+    t_job = time.perf_counter()
+    for s, b0 in enumerate(betas0):
+        # state s: u ~ N(mu_s, sigma_s^2), x_c = a_c u + noise  (SURVEY.md 8d); identical on every rank
+        t0 = time.perf_counter()
+        g = torch.Generator(device=dev).manual_seed(200 + s)
+        u = torch.empty(nsamp, dtype=torch.float64, device=dev).normal_(175.0 - 3.0 * b0, 5.3 / (1.0 + 0.05 * b0), generator=g)
+        slope = torch.linspace(0.5e-3, 2e-3, nchan, dtype=torch.float64, device=dev)
+        uh.copy_(u[lo:hi])
+        step = 1 << 22
+        for i in range(lo, hi, step):   # this rank's rows only, in chunks: the full x never exists on the device
+            j = min(hi, i + step)
+            # the generator must advance identically on every rank: draw per global chunk index
+            gc = torch.Generator(device=dev).manual_seed(1000 * (200 + s) + i // step)
+            xs = torch.empty((j - i, nchan), dtype=torch.float64, device=dev).normal_(0.0, 0.02, generator=gc)
+            xs.addcmul_(u[i:j, None], slope[None, :])
+            xh[i - lo : j - lo].copy_(xs)
+        del u, xs
+        torch.cuda.empty_cache()
+        sync()
+        legs["generate_s"] += time.perf_counter() - t0
+        # ---- the public API from here on
+        t0 = time.perf_counter()
+        backend.clear_device_cache()
+        xv = xt.DataArray(xh.numpy(), dims=("rec", "val"))
+        uv = xt.DataArray(uh.numpy(), dims=("rec",))
+        data = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+        model = xt.beta.factory_extrapmodel(beta=b0, data=data)
+        sync()
+        legs["from_vals_s"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        boots.append(model.resample(sampler={"nrep": nrep, "rng": np.random.default_rng(10 + s)}))
+        sync()
+        legs["resample_s"] += time.perf_counter() - t0
+        del data, model, xv, uv
+        backend.clear_device_cache()
+        K._workspaces.clear()
+        torch.cuda.empty_cache()
+    t0 = time.perf_counter()
+    im = xt.InterpModel(boots)
+    alphas = np.linspace(betas0[0], betas0[-1], 21)
+    pred = im.predict(alphas)
+    sync()
+    legs["interp_predict_s"] = time.perf_counter() - t0
+    total = time.perf_counter() - t_job
+    vals = np.asarray(pred.values)
+    assert pred.dims == ("beta", "rep", "val") and vals.shape == (21, nrep, nchan) and np.isfinite(vals).all()
+    # size-independent checks: every replicate holds exactly nsamp draws; at the nodes the interpolant returns each
+    # state's own bootstrap mean; the replicate scatter there is the standard error of the mean
+    for b in boots:
+        w = np.asarray(b.data.values.values)[..., 0, 0]
+        assert (w == float(nsamp)).all(), "a replicate's total weight differs from nsamp"
+    node_err = 0.0
+    for i, (b0, b) in enumerate(zip(betas0, boots)):
+        at = im.predict([b0]).values[0]
+        own = np.asarray(b.data.values.values)[..., 1, 0]
+        node_err = max(node_err, float(np.max(np.abs(at - own) / np.abs(own))))
+    assert node_err < 1e-6, f"interpolant misses the states' own values by {node_err:.2e}"
+    timed = total - legs["generate_s"]
+    flops = 2.0 * (order + 1) * (nchan + 1) * nsamp * nrep * len(betas0)
+    h2d, d2h = backend.transfer_bytes["h2d"], backend.transfer_bytes["d2h"]
+    out = {
+        "workload": f"C3: beta InterpModel across {len(betas0)} state points, order {order}, {nsamp:.0e} samples x "
+                    f"{nchan} channels per state, nrep={nrep}, through the public API from pinned host arrays",
+        "n_gpus": world, "nsamp": nsamp, "nchan": nchan, "order": order, "nrep": nrep, "states": len(betas0),
+        "seconds_api": timed, "seconds_generate_untimed": legs["generate_s"],
+        "legs_s": {k: v for k, v in legs.items() if k != "generate_s"},
+        "replicates_per_s": nrep * len(betas0) / timed,
+        "samples_per_s_from_vals": nsamp * len(betas0) / legs["from_vals_s"],
+        "bootstrap_tflops_fp64": flops / legs["resample_s"] / 1e12,
+        "h2d_bytes_this_rank": int(h2d), "d2h_bytes_this_rank": int(d2h),
+        "interp_node_rel_err": node_err,
+        "sharding": "one GPU" if world == 1 else f"parallel.enable() over {world} GPUs: row shards all_gathered over "
+                    "NVLink, counting pass split, replicates sharded, slabs all_gathered",
+        "gpu": torch.cuda.get_device_name(0),
+    }
+    if world > 1:
+        par.disable()
+        if own_pg:
+            dist.barrier()
+            dist.destroy_process_group()
+    return out
+
+
+if __name__ == "__main__":
+    main()
