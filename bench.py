@@ -405,7 +405,7 @@ def run_b200(a) -> None:
 
     # per-kernel device time (outside the headline region)
     ksteps = max(1, min(a.steps, 2 if wide else a.steps))
-    tags = ("reduce", "sampler_count", "bucket_scatter", "bucket_hist", "resample") if wide else (
+    tags = ("reduce", "sampler_count", "bucket_scatter", "bucket_hist", "resample", "resample.wide") if wide else (
         "reduce", "sampler_count", "bucket_scatter", "bucket_consume", "sampler_gather")
     kernels = kernel_times(lib, job, ksteps, tags)
 
@@ -486,20 +486,38 @@ def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_i
     flops = 2.0 * (a.order + 1) * (nv + 1) * a.nsamp * a.nrep   # 2 (k+1) (C_u + C_x) per (rep, sample)
     fp64_peak = fp64_peak_tflops()
     shares = {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kernels.items()}
+    if "resample.wide" in shares and "resample" in shares:   # "resample" = wide + scalar: list them side by side
+        shares["resample.scalar"] = {
+            "ms_per_step": shares["resample"]["ms_per_step"] - shares["resample.wide"]["ms_per_step"],
+            "launches_per_step": shares["resample"]["launches_per_step"] - shares["resample.wide"]["launches_per_step"]}
+        shares["resample.scalar"]["share_of_step"] = shares["resample.scalar"]["ms_per_step"] / step_ms
+        del shares["resample"]
     if wide:
-        rs = kernels.get("resample", {"ms_per_step": float("nan"), "launches_per_step": 1})
+        # dominant kernel: the wide-x DMMA contraction alone (tag "resample.wide"); its algorithmic flops are the
+        # x columns' 2 (k+1) C_x per (rep, sample); the u-moment columns (2 (k+1) C_u) are k_resample_mma_scalar's
+        rs_all = kernels.get("resample", {"ms_per_step": float("nan"), "launches_per_step": 1})
+        rs = kernels.get("resample.wide", rs_all)
+        flops_wide = 2.0 * (a.order + 1) * nv * a.nsamp * a.nrep
         per_launch_s = rs["ms_per_step"] * 1e-3 / rs["launches_per_step"]
-        ach = flops / world / (rs["ms_per_step"] * 1e-3) / 1e12   # this rank contracts nrep / world replicates
+        ach = flops_wide / world / (rs["ms_per_step"] * 1e-3) / 1e12   # this rank contracts nrep / world replicates
+        # DRAM traffic of one launch from `ncu --set full` (profiles/r02_target_kernels_ncu_full.txt: 64.88 GB read +
+        # 0.03 GB written for a 128-replicate window = the window's table + one pass over the samples), scaled to
+        # this run's replicates per launch
+        reps_per_launch = a.nrep / world / rs["launches_per_step"]
+        traffic = a.nsamp * reps_per_launch + 8.0 * a.nsamp * (nv + 1) * (1 if reps_per_launch <= 128 else reps_per_launch / 128)
         roofline = {
-            "kernel": "k_resample_mma<6, uint8> (K2: frequency table x shifted power products on the fp64 tensor pipe, "
-                      "DMMA.8x8x4)",
+            "kernel": "k_resample_mma2<6, uint8, 16 warps> (K2: frequency table x shifted power products on the fp64 "
+                      "tensor pipe, DMMA.8x8x4)",
             "bound": "tensor", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak,
             "peak_source": "fp64 DFMA / DMMA micro-benchmark of this run (txb_fp64_peak_launch; MEASURED_PEAKS.json "
                            "carries bf16 only, and tcgen05 has no fp64 kind: mma.sync DMMA is the fp64 tensor path)",
-            "algorithmic_flops_per_launch": flops / world / rs["launches_per_step"],
+            "algorithmic_flops_per_launch": flops_wide / world / rs["launches_per_step"],
             "launch_ms": per_launch_s * 1e3, "launches_per_step": rs["launches_per_step"],
             "share_of_step": rs["ms_per_step"] / step_ms,
-            "traffic": None,
+            "traffic": traffic,
+            "traffic_source": "table bytes + one pass over the samples per 128-replicate tile; ncu --set full of a "
+                              "128-replicate launch measured 64.9 GB against this formula's 64.8 GB "
+                              "(profiles/r02_target_kernels_ncu_full.txt)",
             "whole_step_frac_fp64": flops / world / (step_ms * 1e-3) / 1e12 / fp64_peak,
             "kernels": shares,
         }

@@ -355,7 +355,8 @@ int txb_set_scatter_threads(int nthreads);
 
 /* Kernel timing for bench.py's roofline: between txb_profile_begin(tag) and
  * txb_profile_end, every launch of the kernel family `tag` ("reduce", "resample",
- * "sampler_count", "sampler_gather"; "reduce_ring" = only the copy-engine-staged reduce
+ * "sampler_count", "sampler_gather"; "resample.wide" / "resample.scalar" = only the DMMA contraction of wide x /
+ * of the scalar (u-moment) columns, both also counted under "resample"; "reduce_ring" = only the copy-engine-staged reduce
  * kernels, which is how the tests check which kernel ran) is bracketed by CUDA events on its own stream;
  * txb_profile_end synchronises on them and returns the summed duration and the number of
  * launches.  No effect on results; not thread safe (measurement only).            */

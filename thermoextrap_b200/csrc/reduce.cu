@@ -32,7 +32,10 @@ static cudaEvent_t g_prof_ev[2 * PROF_MAX];
 static int g_prof_made = 0, g_prof_used = 0;
 
 ProfScope::ProfScope(const char* tag, cudaStream_t st) : st_(st), slot_(-1) {
-    if (g_prof_tag[0] == 0 || strcmp(tag, g_prof_tag) != 0 || g_prof_used >= PROF_MAX) return;
+    // a scope "family.member" matches the active tag "family" as well as "family.member"
+    const size_t n = strlen(g_prof_tag);
+    const bool hit = n != 0 && strncmp(tag, g_prof_tag, n) == 0 && (tag[n] == 0 || tag[n] == '.');
+    if (!hit || g_prof_used >= PROF_MAX) return;
     while (g_prof_made <= g_prof_used) {
         if (cudaEventCreate(&g_prof_ev[2 * g_prof_made]) != cudaSuccess ||
             cudaEventCreate(&g_prof_ev[2 * g_prof_made + 1]) != cudaSuccess) {

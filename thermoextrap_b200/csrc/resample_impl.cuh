@@ -108,7 +108,7 @@ int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st)
     }
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
-        ProfScope prof("resample", st);
+        ProfScope prof("resample.wide", st);
         k_resample_mma<K, FT><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma");
@@ -139,7 +139,7 @@ int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st
     }
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
-        ProfScope prof("resample", st);
+        ProfScope prof("resample.wide", st);
         k_resample_mma2<K, FT, WM><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma2");
@@ -186,7 +186,7 @@ int rs_launch_mma_scalar(RsArgs a, double* S0, double* S1, double* ws, cudaStrea
     }
     const dim3 grid(1u, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
-        ProfScope prof("resample", st);
+        ProfScope prof("resample.scalar", st);
         k_resample_mma_scalar<K, HAS_X, FT><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma_scalar");
