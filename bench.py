@@ -595,7 +595,8 @@ def extra_configs(a, dev) -> dict:
     from thermoextrap_b200 import kernels as K
 
     out = {}
-    for name, fn in (("c1", config_c1), ("c2", config_c2), ("c3", config_c3), ("c4", config_c4), ("c5", config_c5)):
+    for name, fn in (("c1", config_c1), ("c2", config_c2), ("c3", config_c3), ("c4", config_c4), ("c5", config_c5),
+                     ("perturb", config_perturb)):
         if name == a.config:
             continue
         try:
@@ -705,6 +706,29 @@ def config_c4(dev) -> dict:
     return {"workload": "C4: lnPi macrostate extrapolation, order 4, 1e6 frames x 2000 macrostate channels",
             "reduce_ms": ms, "frames_per_s": n / ms * 1e3, "GBps": gbs, "frac_hbm": gbs / peaks["hbm_gbs"],
             "algorithmic_bytes": 8.0 * n * c, "model_predict_ms": t_model * 1e3, "peak_note": HBM_NOTE}
+
+
+def config_perturb(dev) -> dict:
+    """PerturbModel.predict kernel at three widths: device time and the fraction of the HBM
+    roofline (algorithmic bytes: one pass over x and u per tile of 4 alphas, plus the min/max pass over u)."""
+    import numpy as np
+    import torch
+
+    from thermoextrap_b200 import kernels as K
+
+    peaks = measured_peaks()
+    out = {"workload": "PerturbModel.predict (models.py:1009-1046): exp(-dalpha u) reweighting of x[rec, val]", "cases": []}
+    for n, c, na in [(100_000_000, 0, 8), (4_000_000, 64, 8), (400_000, 2000, 4)]:
+        u = torch.randn(n, dtype=torch.float64, device=dev) * 1.5 + 3.0
+        x = torch.randn((n, c) if c else (n,), dtype=torch.float64, device=dev)
+        da = np.linspace(-0.4, 0.5, na)
+        ms, _ = timed_ms(lambda: K.perturb_predict(x, u, da), reps=3, warm=2)
+        nbytes = 8.0 * n * (max(c, 1) + 1) * ((na + 3) // 4) + 8.0 * n
+        out["cases"].append({"nsamp": n, "nchan": c, "nalpha": na, "ms": ms, "GBps": nbytes / ms / 1e6,
+                             "frac_hbm": nbytes / ms / 1e6 / peaks["hbm_gbs"],
+                             "bound": "fp64 exp (scalar x)" if not c else "hbm"})
+        del x, u
+    return out
 
 
 def config_c5(dev) -> dict:

@@ -16,7 +16,7 @@ namespace txb {
 constexpr int PT_THREADS = 256;
 constexpr int PT_NW = PT_THREADS / 32;
 constexpr int PT_NA = 4;   // alphas per CTA
-constexpr int PT_QC = 4;   // 32-channel chunks per CTA
+constexpr int PT_QC = 4;   // 32-channel chunks per CTA (widest form; narrower x uses QC = 1 or 2 with deeper row unrolling)
 
 struct PtArgs {
     const double* x;       // [nsamp, ldx]
@@ -61,9 +61,13 @@ __global__ void k_minmax_final(const double* __restrict__ part, int nparts, doub
     if (threadIdx.x == 0) umm[0] = lo, umm[1] = hi;
 }
 
-template <bool SCALAR>
+// QC = 32-channel chunks per CTA, UNR = rows whose loads are in flight per warp.  ncu on the first form (QC = 4,
+// UNR = 4 for every width): long-scoreboard stalls at 16 warps per SM -- the row loop is a chain of UNR-row latency
+// rounds, so x of <= 64 channels (half the loads masked off) had 8 loads per lane in flight.  Narrow x now spends the
+// registers on rows instead of masked chunks: QC * UNR = 16 loads per lane in every form.
+template <bool SCALAR, int QC_, int UNR>
 __global__ void __launch_bounds__(PT_THREADS) k_perturb(const PtArgs a) {
-    constexpr int QC = SCALAR ? 1 : PT_QC;
+    constexpr int QC = SCALAR ? 1 : QC_;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int a0 = blockIdx.y * PT_NA;
     const int64_t c0 = (int64_t)blockIdx.z * (QC * 32);
@@ -99,17 +103,23 @@ __global__ void __launch_bounds__(PT_THREADS) k_perturb(const PtArgs a) {
             for (int i = 0; i < PT_NA; ++i) num[i][0] = fma(e[i], xx, num[i][0]);
         } else {
             const int nrow = (int)min((int64_t)32, s_end - s0);
-#pragma unroll 4
-            for (int j = 0; j < nrow; ++j) {
-                const double* row = a.x + (s0 + j) * a.ldx + c0 + lane;
-                double xv[QC];
+            for (int j0 = 0; j0 < nrow; j0 += UNR) {
+                double xv[UNR][QC];
 #pragma unroll
-                for (int q = 0; q < QC; ++q) xv[q] = c0 + 32 * q + lane < a.nchan ? ldg_stream1(row + 32 * q) : 0.0;
+                for (int jj = 0; jj < UNR; ++jj) {   // all loads of UNR rows first (rows past the slab end: zeros)
+                    const double* row = a.x + (s0 + j0 + jj) * a.ldx + c0 + lane;
 #pragma unroll
-                for (int i = 0; i < PT_NA; ++i) {
-                    const double ej = __shfl_sync(0xffffffffu, e[i], j);
+                    for (int q = 0; q < QC; ++q)
+                        xv[jj][q] = (j0 + jj < nrow && c0 + 32 * q + lane < a.nchan) ? ldg_stream1(row + 32 * q) : 0.0;
+                }
 #pragma unroll
-                    for (int q = 0; q < QC; ++q) num[i][q] = fma(ej, xv[q], num[i][q]);
+                for (int jj = 0; jj < UNR; ++jj) {
+#pragma unroll
+                    for (int i = 0; i < PT_NA; ++i) {
+                        const double ej = __shfl_sync(0xffffffffu, e[i], (j0 + jj) & 31);
+#pragma unroll
+                        for (int q = 0; q < QC; ++q) num[i][q] = fma(ej, xv[jj][q], num[i][q]);
+                    }
                 }
             }
         }
@@ -164,8 +174,12 @@ __global__ void __launch_bounds__(256) k_perturb_final(const double* __restrict_
     if (lane == 0) out[e] = num / den;
 }
 
+// 32-channel chunks per CTA for x of `nchan` channels
+static int pt_qc(int64_t nchan) { return nchan <= 32 ? 1 : nchan <= 64 ? 2 : PT_QC; }
+
 static int64_t pt_nslab(int64_t nsamp, int64_t nchan, int nalpha) {
-    const int64_t tiles = ((nalpha + PT_NA - 1) / PT_NA) * (nchan == 1 ? 1 : (nchan + PT_QC * 32 - 1) / (PT_QC * 32));
+    const int64_t cw = pt_qc(nchan) * 32;
+    const int64_t tiles = ((nalpha + PT_NA - 1) / PT_NA) * (nchan == 1 ? 1 : (nchan + cw - 1) / cw);
     int64_t n = (4 * (int64_t)sm_count() + tiles - 1) / tiles;
     const int64_t most = (nsamp + PT_THREADS - 1) / PT_THREADS;
     if (n > most) n = most;
@@ -215,10 +229,14 @@ extern "C" int txb_perturb_predict_f64(const double* x, const double* u, int64_t
     {
         ProfScope prof("perturb", st);
         if (nchan == 1) {
-            k_perturb<true><<<dim3((unsigned)nslab_used, atiles, 1), PT_THREADS, 0, st>>>(a);
+            k_perturb<true, 1, 1><<<dim3((unsigned)nslab_used, atiles, 1), PT_THREADS, 0, st>>>(a);
         } else {
-            const unsigned ctiles = (unsigned)((nchan + PT_QC * 32 - 1) / (PT_QC * 32));
-            k_perturb<false><<<dim3((unsigned)nslab_used, atiles, ctiles), PT_THREADS, 0, st>>>(a);
+            const int qc = pt_qc(nchan);
+            const unsigned ctiles = (unsigned)((nchan + qc * 32 - 1) / (qc * 32));
+            const dim3 grid((unsigned)nslab_used, atiles, ctiles);
+            if (qc == 1)      k_perturb<false, 1, 16><<<grid, PT_THREADS, 0, st>>>(a);
+            else if (qc == 2) k_perturb<false, 2, 8><<<grid, PT_THREADS, 0, st>>>(a);
+            else              k_perturb<false, PT_QC, 4><<<grid, PT_THREADS, 0, st>>>(a);
         }
     }
     TXB_CUDA_LAUNCH_CHECK("k_perturb");

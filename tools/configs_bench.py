@@ -28,7 +28,7 @@ import torch
 from bench import fp64_peak_tflops, measured_peaks
 from thermoextrap_b200 import kernels as K
 
-PEAK_HBM, _ = measured_peaks()
+PEAK_HBM = measured_peaks()["hbm_gbs"]
 
 
 def timeit(fn, warm=2, rep=5):
