@@ -50,16 +50,17 @@ elif which == "target":  # python tools/ncu_case.py target [nsamp nrep]: K6 tabl
     for i in range(0, nw, 1 << 22):
         xw[i : i + (1 << 22)].normal_(0.0, 0.02)
         xw[i : i + (1 << 22)].addcmul_(uw[i : i + (1 << 22), None], torch.linspace(0.5e-3, 2e-3, 64, dtype=torch.float64, device="cuda")[None])
-    plan = K.SamplerPlan(np.random.default_rng(1), rw, nw)
-    lib.txb_set_scatter_threads(512)
-    f8 = K.sampler_freq(plan, dtype=torch.uint8)
-    lib.txb_set_scatter_threads(1024)
-    del f8
-    f8 = K.sampler_freq(plan, dtype=torch.uint8)
-    lib.txb_set_resample_kernel(1)
-    K.resample_vals(xw, uw, f8, 6)
-    lib.txb_set_resample_kernel(2)
-    K.resample_vals(xw, uw, f8, 6)
+    plan = K.SamplerPlan(np.random.default_rng(1), rw, nw)            # k_sampler_count (+ scans)
+    if len(sys.argv) > 4 and sys.argv[4] == "forms":                   # every form, for A/B captures
+        for nth in (512, 1024):
+            lib.txb_set_scatter_threads(nth)
+            f8 = K.sampler_freq(plan, dtype=torch.uint8)
+        for ver in (1, 2, 3):
+            lib.txb_set_resample_kernel(ver)
+            K.resample_vals(xw, uw, f8, 6)
+    else:                                                              # the defaults bench.py runs
+        f8 = K.sampler_freq(plan, dtype=torch.uint8)                   # k_bucket_scatter<1, 512>, k_bucket_hist
+        K.resample_vals(xw, uw, f8, 6)                                 # k_resample_mma_scalar, k_resample_mma2<6, u8, 8>
 elif which == "perturb":
     xw = torch.randn((4_000_000, 64), dtype=torch.float64, device="cuda")
     K.perturb_predict(xw, u[:4_000_000] * 0.01, np.linspace(-0.4, 0.5, 8))
