@@ -363,3 +363,24 @@ def test_combine_and_mean_var_kernels(K):
     one = rng.normal(size=(2, 1, 3))
     mean, var = K.mean_var(one)
     assert np.array_equal(mean.cpu().numpy(), one[:, 0]) and not var.cpu().numpy().any()
+
+
+def test_wide_bootstrap_redoes_an_overflowed_window(K):
+    """kernels.sampler_resample_wide issues its uint8 windows without reading the status back; a window whose row-sum
+    check (folded into k_bucket_hist) reports a count above 255 is redone with an int32 table.  ndat = 6e5 samples
+    drawn 1.2e8 times per replicate (mean count 200: tens of samples exceed 255) -- the result must equal the
+    contraction of the int32 table built with global atomics (itself bit-exact against numpy,
+    tests/test_sampler_gpu.py::test_bucketed_histogram_overflow_is_loud)."""
+    import torch
+
+    ndat, nsamp, nrep, nchan, order = 600_000, 120_000_000, 2, 5, 3
+    rng = np.random.default_rng(6)
+    u = rng.normal(175.0, 5.3, ndat)
+    x = u[:, None] * np.linspace(0.5e-3, 2e-3, nchan)[None, :] + rng.normal(0.0, 0.02, (ndat, nchan))
+    got = K.sampler_resample_wide(np.random.default_rng(3), x, u, nrep, order, nsamp=nsamp).cpu().numpy()
+    f32 = K.sampler_freq(np.random.default_rng(3), nrep, nsamp, ndat, dtype=torch.int32, buckets=False)
+    assert int(f32.max()) > 255
+    ref = K.resample_vals(x, u, f32, order).cpu().numpy()
+    assert got.shape == ref.shape == (nrep, nchan, 2, order + 1)
+    assert (got[:, :, 0, 0] == float(nsamp)).all()
+    close(got, ref, oc.tolerance_scale(x, u, order), tol=1e-12)

@@ -540,6 +540,16 @@ inline int scatter_threads() {
     return g_scatter_threads;
 }
 
+// per-iteration drain of the partition kernel: compacted per-warp flush unless TXB_SCATTER_DRAIN=0
+inline int scatter_compact_drain() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("TXB_SCATTER_DRAIN");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v;
+}
+
 struct Plan {
     SamplerArgs a;
     int nblocks;
@@ -1075,6 +1085,7 @@ static int sampler_freq_impl(const txb_pcg64* rng, int64_t ndat, int64_t nrep, i
                 ba.nlines = nlines;
                 ba.nb = nbl;
                 ba.b_lo = b_lo;
+                ba.compact_drain = scatter_compact_drain();
                 ba.cap = bp.cap;
                 ba.cap_lines = sp.cap_lines;
                 ba.nseg = sp.nseg;
@@ -1273,6 +1284,7 @@ extern "C" int txb_sampler_resample_f64(const txb_pcg64* rng, const double* x, c
             ba.nseg = sp.nseg;
             ba.seg_len = sp.seg_len;
             ba.rep_lo = r0;
+            ba.compact_drain = scatter_compact_drain();
             {
                 ProfScope prof("bucket_scatter", st);
                 if (scatter_threads() == 1024)
