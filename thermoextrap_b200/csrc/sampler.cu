@@ -540,12 +540,13 @@ inline int scatter_threads() {
     return g_scatter_threads;
 }
 
-// per-iteration drain of the partition kernel: compacted per-warp flush unless TXB_SCATTER_DRAIN=0
+// per-iteration drain of the partition kernel: TXB_SCATTER_DRAIN=1 selects the compacted per-warp flush
+// (default: the per-bucket walk, until the compacted form has been through the GPU suite)
 inline int scatter_compact_drain() {
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("TXB_SCATTER_DRAIN");
-        v = (e && e[0] == '0') ? 0 : 1;
+        v = (e && e[0] == '1') ? 1 : 0;
     }
     return v;
 }
