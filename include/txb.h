@@ -317,6 +317,13 @@ int txb_perturb_predict_f64(const double* x, const double* u, int64_t nsamp, int
  *   dalpha  [nalpha] device doubles (alpha - alpha0).  order <= 10 (TXB_ERR_UNSUPPORTED above).     */
 int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim, int family, int order, int flags,
                          int mode, const double* dalpha, int nalpha, double* out, void* stream);
+/* The same launch for the lnPi family (lnpi.py:42-116: d_0 = lnPi0, d_1 = mu.N - <u>, d_n = -d^(n-1)<u>/dbeta^(n-1),
+ * i.e. the u_ave family one order lower, shifted): comom = x_is_u records [nelem, 2, kdim] with kdim >= order;
+ * central != 0 selects the central form; lnpi0 / mudotn [ninner] device doubles, element e reads index e % ninner
+ * (leading dims such as rep broadcast).  No -log flag (the reference has none for lnPi); modes as above.       */
+int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int mode,
+                         const double* dalpha, int nalpha, const double* lnpi0, const double* mudotn,
+                         int64_t ninner, double* out, void* stream);
 /* out[a, e] = (accumulate ? out[a, e] : 0) + sum_t W[a, t] D[t, e]: InterpModel.predict (models.py:909-932)
  * with W = alpha powers x inverse Hermite matrix folded on the host ([nalpha, nt], nt <= 512) and D = one
  * state's normalised derivatives [nt, nelem], both on the device.                                   */

@@ -35,7 +35,8 @@ def _funcs(key: str):
 
     rec = json.loads(GOLDEN.read_text())[key]
     names = rec.get("args") or ["X"]
-    loc = {n: (sp.Symbol(n) if n in {"x1"} or (n == "u" and "du" in names) else sp.IndexedBase(n)) for n in names}
+    scalars = {"x1", "lnPi0", "mudotN"}
+    loc = {n: (sp.Symbol(n) if n in scalars or (n == "u" and "du" in names) else sp.IndexedBase(n)) for n in names}
     args = [loc[n] for n in names]
     return [sp.lambdify(args, sp.sympify(e, locals=loc), "numpy") for e in rec["exprs"]]
 
@@ -95,6 +96,38 @@ def beta_derivs(comom, order: int, family: int, minus_log: bool = False, norm: b
     if norm:
         out = out / np.array([math.factorial(i) for i in range(order + 1)], dtype=np.longdouble)[:, None]
     return out.astype(np.float64)
+
+
+def lnpi_derivs(comom, order: int, central: bool, lnpi0, mudotn, norm: bool = False) -> np.ndarray:
+    """``[order+1, nelem]`` lnPi derivatives (golden key ``lnPi|central=...``, lnpi.py:42-116) from x_is_u records
+    ``[..., 2, K+1]``; ``lnpi0`` / ``mudotn`` (``ninner`` values) broadcast over the leading elements."""
+    c = np.asarray(comom, dtype=np.float64)
+    c = c.reshape(-1, 2, c.shape[-1])
+    funcs = _funcs(f"lnPi|central={bool(central)}")
+    if order + 1 > len(funcs):
+        raise NotImplementedError(f"oracle holds orders <= {len(funcs) - 1}")
+    ub, _, du, _ = central_rows(c, x_is_u=True)
+    nel = c.shape[0]
+    l0 = np.resize(np.asarray(lnpi0, dtype=np.longdouble).reshape(-1), nel)
+    mn = np.resize(np.asarray(mudotn, dtype=np.longdouble).reshape(-1), nel)
+    if central:
+        args = (ub, [du[:, n] for n in range(du.shape[1])], l0, mn)
+    else:
+        u_raw = [sum(math.comb(n, k) * du[:, k] * ub ** (n - k) for k in range(n + 1)) for n in range(du.shape[1])]
+        args = (u_raw, l0, mn)
+    out = np.stack([np.broadcast_to(funcs[i](*args), (nel,)) for i in range(order + 1)]).astype(np.longdouble)
+    if norm:
+        out = out / np.array([math.factorial(i) for i in range(order + 1)], dtype=np.longdouble)[:, None]
+    return out.astype(np.float64)
+
+
+def lnpi_predict(comom, order, central, lnpi0, mudotn, dalpha, mode=0) -> np.ndarray:
+    coefs = lnpi_derivs(comom, order, central, lnpi0, mudotn, norm=True).astype(np.longdouble)
+    d = np.atleast_1d(np.asarray(dalpha, dtype=np.longdouble))
+    terms = d[:, None, None] ** np.arange(order + 1)[None, :, None] * coefs[None]
+    if mode == 0:
+        return terms.sum(axis=1).astype(np.float64)
+    return (np.cumsum(terms, axis=1) if mode == 1 else terms).astype(np.float64)
 
 
 def beta_predict(comom, order, family, dalpha, minus_log=False, mode=0) -> np.ndarray:

@@ -275,6 +275,18 @@ def beta_predict(comom, order, family, dalpha=None, minus_log=False, mode=0, nor
     return _t(od.beta_predict(c, order, family, dalpha, minus_log=minus_log, mode=mode))
 
 
+LNPI_FAMILIES = {True: 4, False: 5}
+
+
+def lnpi_predict(comom, order, central, lnpi0, mudotn, dalpha=None, mode=0, norm=False):
+    from oracle import derivs as od
+
+    c = _np(comom)
+    if mode == PREDICT_DERIVS:
+        return _t(od.lnpi_derivs(c, order, central, _np(lnpi0), _np(mudotn), norm=norm))
+    return _t(od.lnpi_predict(c, order, central, _np(lnpi0), _np(mudotn), dalpha, mode=mode))
+
+
 def combine(W, D, out=None):
     res = np.asarray(_np(W), dtype=np.float64) @ _np(D)
     if out is not None:

@@ -172,7 +172,8 @@ def test_u_ave_fused_on_x_is_u_data(monkeypatch, calls):
 
 
 def test_fused_path_is_skipped_when_it_does_not_apply(monkeypatch, calls):
-    """post_func / n-th moment families, a deriv dimension or host-built comoments keep the table path."""
+    """post_func / n-th moment families keep the table path; comoments built on the host are uploaded (they are small)
+    and take the fused launch like the kernel-produced ones."""
     xv, uv = _samples()
     data = xtrap.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=3, central=True)
     before = calls["beta_predict"]
@@ -181,11 +182,74 @@ def test_fused_path_is_skipped_when_it_does_not_apply(monkeypatch, calls):
     m.predict([0.9])
     m2 = xtrap.beta.factory_extrapmodel(beta=1.0, data=data, name="dxdun_ave", n=2, order=1)
     m2.predict([0.9])
+    assert calls["beta_predict"] == before
     host = xtrap.DataCentralMoments.from_data(data.values, central=True)   # built from a host array: no device copy
     m3 = xtrap.beta.factory_extrapmodel(beta=1.0, data=host)
     assert m3.derivatives.family == 0
-    m3.predict([0.9])
-    assert calls["beta_predict"] == before
+    fast = m3.predict([0.9, 1.2]).values
+    assert calls["beta_predict"] == before + 1
+    monkeypatch.setattr(models, "FUSED_K7", False)
+    slow = xtrap.beta.factory_extrapmodel(beta=1.0, data=host).predict([0.9, 1.2]).values
+    _scaled_close(fast, slow)
+
+
+@pytest.mark.parametrize("central", [True, False])
+def test_lnpi_fused_equals_table_path(central, monkeypatch, backend_kernels):
+    """The lnPi family (lnpi.py:42-116) on the fused launch: d_0 = lnPi0, d_1 = mu.N - <u>, d_n = -d^(n-1)<u>:
+    from samples (uv[rec, n], x_is_u) and from pre-averaged moments (from_ave_raw, the reference's golden path),
+    model order = data order + 1."""
+    n_dim, order = 6, 3
+    rng = np.random.default_rng(4)
+    nvals = np.arange(1, n_dim + 1)
+    uv = rng.normal(-4.8 * nvals, 0.9 * np.sqrt(nvals), (900, n_dim))
+    lnpi0 = DataArray(rng.normal(size=n_dim), dims=("n",), coords={"n": nvals})
+    mu = DataArray(np.array([-2.63]), dims=("comp",))
+    n_calls = {"k": 0}
+    real = backend_kernels.lnpi_predict
+
+    def counted(*a, **k):
+        n_calls["k"] += 1
+        return real(*a, **k)
+
+    monkeypatch.setattr(backend_kernels, "lnpi_predict", counted)
+
+    def run():
+        meta = xtrap.lnpi.lnPiDataCallback(lnpi0, mu, dims_n=["n"], dims_comp="comp")
+        d1 = xtrap.DataCentralMomentsVals.from_vals(xv=None, uv=DataArray(uv, dims=("rec", "n")), order=order, central=central,
+                                                    x_is_u=True, meta=meta)
+        m1 = xtrap.lnpi.factory_extrapmodel_lnPi(beta=1.0, data=d1)
+        raw_u = np.stack([(uv**j).mean(0) for j in range(order + 2)], axis=-1)          # <u^j>, j = 0 .. order + 1
+        d2 = xtrap.DataCentralMoments.from_ave_raw(u=DataArray(raw_u, dims=("n", "umom")), xu=None, x_is_u=True,
+                                                   central=central, meta=meta)
+        m2 = xtrap.lnpi.factory_extrapmodel_lnPi(beta=1.0, data=d2)
+        return (m1.predict([0.9, 1.1]), m1.derivs(), m2.predict([0.9, 1.1], cumsum=True), m2.coefs(),
+                m1.predict(1.05, order=2))
+
+    fast, slow = _both(run, monkeypatch)
+    assert n_calls["k"] >= 5, "the fused lnPi entry was not used"
+    # tolerance scale per order: the u_ave polynomial's |coef| |moment| products one order lower (raw form: <u^j> of
+    # macrostate n reaches |4.8 n|^j and cancels), plus |lnPi0| and |mu.N| for orders 0 and 1
+    monkeypatch.setattr(models, "FUSED_K7", False)
+    meta = xtrap.lnpi.lnPiDataCallback(lnpi0, mu, dims_n=["n"], dims_comp="comp")
+    d1 = xtrap.DataCentralMomentsVals.from_vals(xv=None, uv=DataArray(uv, dims=("rec", "n")), order=order, central=central,
+                                                x_is_u=True, meta=meta)
+    L = order + 1
+    Su = _term_scales(d1.values.values, 1 if central else 3, L - 1)                 # [L, n]
+    Sl = np.concatenate([np.abs(lnpi0.values)[None], (np.abs(meta.mudotN.values) + Su[0])[None], Su[1:]], axis=0)
+    fact = np.array([math.factorial(i) for i in range(L + 1)], dtype=float)
+
+    def pred_scale(dbs, upto, cumsum=False):
+        w = np.array([[abs(db) ** p / fact[p] for p in range(upto + 1)] for db in dbs])
+        terms = w[:, :, None] * Sl[None, : upto + 1]
+        return np.cumsum(terms, 1) if cumsum else terms.sum(1)
+
+    for f, s in zip(fast, slow):
+        assert f.dims == s.dims and f.shape == s.shape
+    _scaled_close(fast[0].values, slow[0].values, pred_scale([-0.1, 0.1], L))
+    _scaled_close(fast[1].values, slow[1].values, Sl)
+    _scaled_close(fast[2].values, slow[2].values, pred_scale([-0.1, 0.1], L, cumsum=True))
+    _scaled_close(fast[3].values, slow[3].values, Sl / fact[:, None])
+    _scaled_close(fast[4].values, slow[4].values, pred_scale([0.05], 2)[0])
 
 
 def test_interpmodel_fused_equals_table_path(monkeypatch, calls):

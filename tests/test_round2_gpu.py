@@ -384,3 +384,32 @@ def test_wide_bootstrap_redoes_an_overflowed_window(K):
     assert got.shape == ref.shape == (nrep, nchan, 2, order + 1)
     assert (got[:, :, 0, 0] == float(nsamp)).all()
     close(got, ref, oc.tolerance_scale(x, u, order), tol=1e-12)
+
+
+@pytest.mark.parametrize("central", [True, False])
+@pytest.mark.parametrize("order", [0, 1, 2, 5, 8])
+def test_lnpi_fused_matches_reference_expressions(K, central, order):
+    """txb_lnpi_predict_f64 against the reference's lnPi expression strings (tests/golden/exprs.json, lnpi.py:42-116)
+    evaluated by oracle/derivs.py: x_is_u records, lnPi0 / mu.N broadcast over a leading replicate axis."""
+    from oracle import derivs as od
+    from test_fused_k7 import _term_scales
+
+    nrep, nn = 5, 11
+    rec = _records(60 + order, nrep * nn, max(order, 1), x_is_u=True).reshape(nrep, nn, 2, max(order, 1) + 1)
+    rng = np.random.default_rng(3)
+    lnpi0, mudotn = rng.normal(size=nn), -2.63 * np.arange(nn)
+    ref = od.lnpi_derivs(rec, order, central, lnpi0, mudotn)
+    got = K.lnpi_predict(rec, order, central, lnpi0, mudotn, mode=K.PREDICT_DERIVS).cpu().numpy()
+    S = np.zeros_like(ref)
+    S[0] = np.tile(np.abs(lnpi0), nrep)
+    if order >= 1:
+        Su = _term_scales(rec.reshape(-1, 2, rec.shape[-1]), 1 if central else 3, order - 1)
+        S[1] = np.tile(np.abs(mudotn), nrep) + Su[0]
+        S[2:] = Su[1:]
+    close(got, ref, S)
+    dal = np.array([-0.2, 0.3])
+    fact = np.array([math.factorial(i) for i in range(order + 1)], dtype=float)
+    terms = (np.abs(dal)[:, None] ** np.arange(order + 1)[None, :] / fact[None, :])[:, :, None] * S[None]
+    for mode, sc in ((K.PREDICT_SUM, terms.sum(1)), (K.PREDICT_CUMSUM, np.cumsum(terms, 1)), (K.PREDICT_TERMS, terms)):
+        close(K.lnpi_predict(rec, order, central, lnpi0, mudotn, dal, mode=mode).cpu().numpy(),
+              od.lnpi_predict(rec, order, central, lnpi0, mudotn, dal, mode=mode), sc)

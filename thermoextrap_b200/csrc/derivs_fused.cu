@@ -26,6 +26,10 @@ struct BetaFusedArgs {
     const double* dalpha;  // [nalpha] (device)
     int nalpha;
     double* out;
+    // lnPi families (4 central, 5 raw; lnpi.py:42-116): d_0 = lnPi0, d_1 = mu.N - <u>, d_n = -d^(n-1)<u>/dbeta^(n-1)
+    const double* lnpi0;   // [ninner]
+    const double* mudotn;  // [ninner]; element e uses index e % ninner (leading dims such as rep broadcast)
+    int64_t ninner;
 };
 
 template <int FAM, int ORDER>
@@ -33,29 +37,33 @@ __global__ void __launch_bounds__(128) k_beta_fused(const BetaFusedArgs a) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= a.nelem) return;
     const double* rec = a.comom + e * 2 * a.kdim;
+    // BF / BO: the beta family and order actually evaluated.  The lnPi families are the u_ave families one order
+    // lower, shifted by one and offset by lnPi0 and mu.N.
+    constexpr int BF = FAM < 4 ? FAM : (FAM == 4 ? 1 : 3);
+    constexpr int BO = FAM < 4 ? ORDER : (ORDER > 0 ? ORDER - 1 : 0);
     // central moments of the record.  x_ave families (0, 2): <du^n> from row 0, <dx du^n> from row 1.
     // u_ave families (1, 3) are used with x_is_u data (x == u, beta.py:633-646): <du^n> = <dx du^(n-1)>, which
-    // reaches n = ORDER + 1 -- the moment the ORDER-th derivative of <u> needs.
-    constexpr int NU = ORDER + 2;
+    // reaches n = BO + 1 -- the moment the BO-th derivative of <u> needs.
+    constexpr int NU = BO + 2;
     double r0[NU], r1[NU];
     double ub, xb;
-    if (FAM == 0 || FAM == 2) {
+    if (BF == 0 || BF == 2) {
 #pragma unroll
-        for (int n = 0; n <= ORDER; ++n) {
+        for (int n = 0; n <= BO; ++n) {
             r0[n] = rec[n];
             r1[n] = rec[a.kdim + n];
         }
-        r0[ORDER + 1] = r1[ORDER + 1] = 0.0;
+        r0[BO + 1] = r1[BO + 1] = 0.0;
         ub = r0[1], xb = r1[0];
     } else {
 #pragma unroll
-        for (int n = 1; n <= ORDER + 1; ++n) r0[n] = rec[a.kdim + n - 1];
+        for (int n = 1; n <= BO + 1; ++n) r0[n] = rec[a.kdim + n - 1];
 #pragma unroll
         for (int n = 0; n < NU; ++n) r1[n] = 0.0;
         r0[0] = 1.0;
         ub = r0[1], xb = r0[1];
     }
-    if (FAM >= 2) {
+    if (BF >= 2) {
         // central -> raw (what DataCentralMomentsBase.rmom() hands the raw families, data.py:845-848):
         //   <u^n> = sum_k C(n,k) <du^k> ubar^(n-k),  <x u^n> = sum_k C(n,k) ubar^(n-k) (xbar <du^k> + <dx du^k>)
         double cdu[NU], cdx[NU], up[NU];
@@ -80,11 +88,22 @@ __global__ void __launch_bounds__(128) k_beta_fused(const BetaFusedArgs a) {
             r1[n] = s1;
         }
     }
+    double db[BO + 1];
+    if (BF == 0) beta_derivs_x_ave_central<BO>(r0, r1, db);
+    if (BF == 1) beta_derivs_u_ave_central<BO>(r0, r1, db);
+    if (BF == 2) beta_derivs_x_ave_raw<BO>(r0, r1, db);
+    if (BF == 3) beta_derivs_u_ave_raw<BO>(r0, r1, db);
     double d[ORDER + 1];
-    if (FAM == 0) beta_derivs_x_ave_central<ORDER>(r0, r1, d);
-    if (FAM == 1) beta_derivs_u_ave_central<ORDER>(r0, r1, d);
-    if (FAM == 2) beta_derivs_x_ave_raw<ORDER>(r0, r1, d);
-    if (FAM == 3) beta_derivs_u_ave_raw<ORDER>(r0, r1, d);
+    if (FAM < 4) {
+#pragma unroll
+        for (int n = 0; n <= ORDER; ++n) d[n] = db[n < BO + 1 ? n : BO];
+    } else {
+        const int64_t ei = e % a.ninner;
+        d[0] = a.lnpi0[ei];
+        if (ORDER >= 1) d[1 <= ORDER ? 1 : 0] = a.mudotn[ei] - db[0];
+#pragma unroll
+        for (int n = 2; n <= ORDER; ++n) d[n] = -db[n - 1];
+    }
 
     if (a.flags & BF_FLAG_MINUS_LOG) {
         // y = -log f (models.py:261-281 SymMinusLog): with g = log f,  f g' = f'  differentiated n - 1 times gives
@@ -233,7 +252,7 @@ extern "C" int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim
         return TXB_ERR_UNSUPPORTED;
     }
     if (nelem == 0 || (mode != BF_MODE_DERIVS && nalpha == 0)) return TXB_OK;
-    BetaFusedArgs a{comom, nelem, kdim, flags, mode, dalpha, nalpha, out};
+    BetaFusedArgs a{comom, nelem, kdim, flags, mode, dalpha, nalpha, out, nullptr, nullptr, 1};
     cudaStream_t st = (cudaStream_t)stream;
     int rc = TXB_OK;
     switch (family) {
@@ -244,6 +263,30 @@ extern "C" int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim
     }
     if (rc != TXB_OK) return rc;
     TXB_CUDA_LAUNCH_CHECK("k_beta_fused");
+    return TXB_OK;
+}
+
+extern "C" int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int mode,
+                                    const double* dalpha, int nalpha, const double* lnpi0, const double* mudotn,
+                                    int64_t ninner, double* out, void* stream) {
+    TXB_CHECK_ARG(comom && out && lnpi0 && mudotn, "txb_lnpi_predict_f64: null pointer");
+    TXB_CHECK_ARG(mode >= BF_MODE_SUM && mode <= BF_MODE_DERIVS, "txb_lnpi_predict_f64: bad mode %d", mode);
+    TXB_CHECK_ARG(order >= 0 && kdim >= order && kdim >= 1,
+                  "txb_lnpi_predict_f64: x_is_u records of %d moments cannot give lnPi order %d", kdim, order);
+    TXB_CHECK_ARG(ninner >= 1 && nelem % ninner == 0, "txb_lnpi_predict_f64: nelem=%lld is not a multiple of ninner=%lld",
+                  (long long)nelem, (long long)ninner);
+    TXB_CHECK_ARG(mode == BF_MODE_DERIVS || (dalpha && nalpha >= 0), "txb_lnpi_predict_f64: dalpha is NULL");
+    if (order > BETA_GEN_MAX_ORDER) {
+        set_error("txb_lnpi_predict_f64: order %d above the generated maximum %d (use txb_eval_exprs_f64)", order,
+                  BETA_GEN_MAX_ORDER);
+        return TXB_ERR_UNSUPPORTED;
+    }
+    if (nelem == 0 || (mode != BF_MODE_DERIVS && nalpha == 0)) return TXB_OK;
+    BetaFusedArgs a{comom, nelem, kdim, 0, mode, dalpha, nalpha, out, lnpi0, mudotn, ninner};
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rc = central ? launch_beta_fused<4>(a, order, st) : launch_beta_fused<5>(a, order, st);
+    if (rc != TXB_OK) return rc;
+    TXB_CUDA_LAUNCH_CHECK("k_beta_fused<lnPi>");
     return TXB_OK;
 }
 

@@ -994,6 +994,53 @@ def beta_predict(comom, order: int, family: int, dalpha=None, minus_log: bool = 
     return out
 
 
+#: family indices of the lnPi forms (central, raw): evaluated by :func:`lnpi_predict`
+LNPI_FAMILIES = {True: 4, False: 5}
+
+
+def lnpi_predict(comom, order: int, central: bool, lnpi0, mudotn, dalpha=None, mode: int = PREDICT_SUM,
+                 norm: bool = False) -> torch.Tensor:
+    """The lnPi family on x_is_u comoment records ``comom[..., 2, K+1]``: ``d_0 = lnPi0``, ``d_1 = mu.N - <u>``,
+    ``d_n = -d^(n-1)<u>/dbeta^(n-1)`` (lnpi.py:42-116), fused with ``/ i!`` and the Taylor sum as :func:`beta_predict`.
+    ``lnpi0`` / ``mudotn`` hold ``ninner`` values each and broadcast over the leading dims of ``comom``."""
+    global launch_count
+    lib = _lib.load()
+    dev = device()
+    c = _as_f64(comom, dev)
+    if c.ndim < 2 or c.shape[-2] != 2 or not c.is_contiguous():
+        msg = f"comom must be a contiguous [..., 2, K+1] array; got {tuple(c.shape)}"
+        raise ValueError(msg)
+    kdim = c.shape[-1]
+    nelem = c.numel() // (2 * kdim)
+    l0 = _as_f64(np.ascontiguousarray(lnpi0, dtype=np.float64).reshape(-1) if isinstance(lnpi0, np.ndarray) else lnpi0, dev)
+    mn = _as_f64(np.ascontiguousarray(mudotn, dtype=np.float64).reshape(-1) if isinstance(mudotn, np.ndarray) else mudotn, dev)
+    ninner = l0.numel()
+    if mn.numel() != ninner or ninner < 1 or nelem % ninner:
+        msg = f"lnpi0 ({l0.numel()}) and mudotn ({mn.numel()}) must have equal sizes dividing {nelem} records"
+        raise ValueError(msg)
+    if mode == PREDICT_DERIVS:
+        d, na = None, 0
+        shape = (order + 1, nelem)
+    else:
+        d = _as_f64(np.atleast_1d(np.asarray(dalpha, dtype=np.float64)), dev)
+        na = d.shape[0]
+        shape = (na, nelem) if mode == PREDICT_SUM else (na, order + 1, nelem)
+    out = torch.empty(shape, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        st = lib.txb_lnpi_predict_f64(c.data_ptr(), nelem, kdim, 1 if central else 0, order, mode, _ptr(d), na,
+                                      l0.data_ptr(), mn.data_ptr(), ninner, out.data_ptr(), _stream_ptr())
+    check(st, "txb_lnpi_predict_f64")
+    launch_count += 1
+    if mode == PREDICT_DERIVS and not norm:   # the kernel's derivative mode honours the NORM flag only; lnPi has no flags
+        return out
+    if mode == PREDICT_DERIVS:
+        import math
+
+        fact = torch.tensor([math.factorial(i) for i in range(order + 1)], dtype=torch.float64, device=dev)
+        return out / fact[:, None]
+    return out
+
+
 def combine(W, D, out: torch.Tensor | None = None) -> torch.Tensor:
     """``out[a, e] (+)= sum_t W[a, t] D[t, e]`` on the device; accumulates into ``out`` when it is given."""
     global launch_count

@@ -80,7 +80,10 @@ def factory_derivatives(name="lnPi", n=None, d=None, xalpha=False, central=False
     func = lnPi_func_central(beta) if central else lnPi_func_raw(beta)
     derivs = beta_xpan.SymDerivBeta(func=func, expand=expand, post_func=post_func)
     exprs = SymSubs(derivs, subs_all={derivs.beta: "None"}, expand=False, simplify=False)
-    return Derivatives.from_sympy(exprs, args=derivs.args)
+    # the plain lnPi derivatives also exist as generated device functions (kernels.LNPI_FAMILIES): the u_ave family
+    # one order lower, shifted, plus lnPi0 and mu.N
+    family = (4 if central else 5) if post_func is None else None
+    return Derivatives.from_sympy(exprs, args=derivs.args, family=family)
 
 
 @attrs.define

@@ -383,29 +383,74 @@ def taylor_series_norm(order, order_dim="order"):
 FUSED_K7 = True
 
 
-def _fused_records(model, order):
-    """``(records, lead_dims, lead_shape, coords)`` when ``model`` qualifies for the fused K7 kernels: plain beta
-    derivatives of ``x_ave`` / ``u_ave`` (``derivatives.family``), comoment data whose array a kernel of this package
-    left on the device, no ``deriv`` dimension, the default ``meta`` callback, order within the generated range."""
+class _FusedPlan:
+    """What the fused K7 launch needs: the comoment records on the device, the dims / coords of their leading axes,
+    the generated family, and (lnPi) the two offset arrays."""
+
+    __slots__ = ("rec", "lead_dims", "lead_shape", "coords", "family", "lnpi0", "mudotn")
+
+    def __init__(self, rec, lead_dims, lead_shape, coords, family, lnpi0=None, mudotn=None) -> None:
+        self.rec, self.lead_dims, self.lead_shape, self.coords = rec, lead_dims, lead_shape, coords
+        self.family, self.lnpi0, self.mudotn = family, lnpi0, mudotn
+
+    def launch(self, order, dalpha=None, minus_log=False, mode=None, norm=False):
+        K = cm.K
+        mode = K.PREDICT_SUM if mode is None else mode
+        if self.family >= 4:
+            return K.lnpi_predict(self.rec, order, self.family == 4, self.lnpi0, self.mudotn, dalpha, mode=mode, norm=norm)
+        return K.beta_predict(self.rec, order, self.family, dalpha, minus_log=bool(minus_log), mode=mode, norm=norm)
+
+
+def _fused_records(model, order, minus_log=False):
+    """A :class:`_FusedPlan` when ``model`` qualifies for the fused K7 kernels: plain beta derivatives of ``x_ave`` /
+    ``u_ave`` or the lnPi family (``derivatives.family``), comoment data (left on the device by a kernel of this
+    package, else uploaded: the records are small), no ``deriv`` dimension, the default ``meta`` callback (lnPi: its
+    own callback), order within the generated range.  None otherwise: the expression-table path runs."""
     from .data import DataCallback, DataCentralMomentsBase
 
     fam = getattr(model.derivatives, "family", None)
     data = model.data
     if not FUSED_K7 or fam is None or not isinstance(data, DataCentralMomentsBase):
         return None
-    if order > min(cm.K.BETA_MAX_ORDER, data.order) or data.xalpha or type(data.meta) is not DataCallback:
+    lnpi = fam >= 4
+    if order > cm.K.BETA_MAX_ORDER or data.xalpha or (lnpi and minus_log):
         return None
-    if bool(data.central) != (fam < 2) or bool(data.x_is_u) != (fam in (1, 3)):
+    if order > (data.order + 1 if lnpi else data.order):
+        return None
+    if bool(data.central) != (fam in (0, 1, 4)) or bool(data.x_is_u) != (fam in (1, 3, 4, 5)):
         return None
     if data.dxduave.mom_ndim != 2 or tuple(data.dxduave.mom_dims) != (data.xmom_dim, data.umom_dim):
         return None
-    rec = data.dxduave.device_records()
-    if rec is None:
-        return None
     obj = data.dxduave.obj
     lead_dims = tuple(obj.dims[:-2])
+    lead_shape = tuple(obj.shape[:-2])
+    lnpi0 = mudotn = None
+    if lnpi:
+        meta = data.meta
+        if type(meta).__name__ != "lnPiDataCallback":
+            return None
+        # lnPi0 and mu.N broadcast against each other must span a SUFFIX of the records' leading dims
+        l0, mn = meta.lnPi0_ave, meta.mudotN
+        inner = tuple(d for d in lead_dims if d in l0.dims or d in mn.dims)
+        if set(l0.dims) | set(mn.dims) != set(inner) or inner != lead_dims[len(lead_dims) - len(inner):] or not inner:
+            return None
+        shape = tuple(obj.sizes[d] for d in inner)
+
+        def spread(a):
+            v = np.asarray(a.transpose(*[d for d in inner if d in a.dims]).values, dtype=np.float64)
+            v = v.reshape([obj.sizes[d] if d in a.dims else 1 for d in inner])
+            return np.ascontiguousarray(np.broadcast_to(v, shape)).reshape(-1)
+
+        if any(a.sizes[d] != obj.sizes[d] for a in (l0, mn) for d in a.dims):
+            return None
+        lnpi0, mudotn = spread(l0), spread(mn)
+    elif type(data.meta) is not DataCallback:
+        return None
+    rec = data.dxduave.device_records()
+    if rec is None:
+        rec = cm.to_device(np.ascontiguousarray(np.asarray(obj.values, dtype=np.float64)))
     coords = {k: np.asarray(c.values) for k, c in obj.coords.items() if k in lead_dims}
-    return rec, lead_dims, tuple(obj.shape[:-2]), coords
+    return _FusedPlan(rec, lead_dims, lead_shape, coords, fam, lnpi0, mudotn)
 
 
 def _predict_series(coefs: DataArray, order_dim: str, dvals: np.ndarray, mode: int) -> np.ndarray:
@@ -432,12 +477,11 @@ class ExtrapModel(MyAttrsMixin):
 
     @cached.meth
     def _derivs(self, order, order_dim, minus_log):
-        fused = _fused_records(self, order) if order_dim is not None else None
+        fused = _fused_records(self, order, minus_log) if order_dim is not None else None
         if fused is not None:
-            rec, lead_dims, lead_shape, coords = fused
-            out = cm._host(cm.K.beta_predict(rec, order, self.derivatives.family, minus_log=bool(minus_log),
-                                             mode=cm.K.PREDICT_DERIVS))
-            return DataArray(out.reshape(order + 1, *lead_shape), dims=(order_dim, *lead_dims), coords=coords or None)
+            out = cm._host(fused.launch(order, minus_log=minus_log, mode=cm.K.PREDICT_DERIVS))
+            return DataArray(out.reshape(order + 1, *fused.lead_shape), dims=(order_dim, *fused.lead_dims),
+                             coords=fused.coords or None)
         return self.derivatives.derivs(
             data=self.data, order=order, norm=False, minus_log=minus_log, order_dim=order_dim
         )
@@ -474,15 +518,14 @@ class ExtrapModel(MyAttrsMixin):
             raise ValueError(msg)
         mode = cm.K.PREDICT_TERMS if no_sum else (cm.K.PREDICT_CUMSUM if cumsum else cm.K.PREDICT_SUM)
         dvals = np.atleast_1d(np.asarray(dalpha.values, dtype=np.float64))
-        fused = _fused_records(self, order)
+        fused = _fused_records(self, order, minus_log)
         if fused is not None:
             # records -> derivatives -> -log -> / i! -> Taylor sum in ONE launch; only the predictions come back
-            rec, rest_dims, lead_shape, fcoords = fused
-            vals = cm._host(cm.K.beta_predict(rec, order, self.derivatives.family, dvals, minus_log=bool(minus_log),
-                                              mode=mode))
+            rest_dims = fused.lead_dims
+            vals = cm._host(fused.launch(order, dvals, minus_log=minus_log, mode=mode))
             lead = (len(dvals),) if mode == cm.K.PREDICT_SUM else (len(dvals), order + 1)
-            vals = vals.reshape(*lead, *lead_shape)
-            coords = {alpha_name: np.atleast_1d(np.asarray(alpha.values)), **fcoords}
+            vals = vals.reshape(*lead, *fused.lead_shape)
+            coords = {alpha_name: np.atleast_1d(np.asarray(alpha.values)), **fused.coords}
         else:
             coefs = self.coefs(order=order, order_dim=order_dim, minus_log=minus_log)
             vals, rest_dims = _predict_series(coefs, order_dim, dvals, mode)
@@ -680,16 +723,16 @@ class InterpModel(StateCollection):
         """Polynomial coefficients ``[npoly, nelem]`` ON THE DEVICE when every state qualifies for the fused K7
         kernels (same leading dims): per state one launch for the derivatives of all records, one for its share of
         ``mat_inv . derivs``.  Returns ``(coefs_dev, lead_dims, lead_shape, coords)`` or None."""
-        fused = [_fused_records(m, order) for m in self.states]
-        if any(f is None for f in fused) or len({(f[1], f[2]) for f in fused}) != 1:
+        mls = [m.minus_log if minus_log is None else minus_log for m in self.states]
+        fused = [_fused_records(m, order, ml) for m, ml in zip(self.states, mls)]
+        if any(f is None for f in fused) or len({(f.lead_dims, f.lead_shape) for f in fused}) != 1:
             return None
         mat_inv = self._mat_inv(order)
         coefs_dev = None
-        for s, (m, f) in enumerate(zip(self.states, fused)):
-            ml = m.minus_log if minus_log is None else minus_log
-            d = cm.K.beta_predict(f[0], order, m.derivatives.family, minus_log=bool(ml), mode=cm.K.PREDICT_DERIVS)
+        for s, (f, ml) in enumerate(zip(fused, mls)):
+            d = f.launch(order, minus_log=ml, mode=cm.K.PREDICT_DERIVS)
             coefs_dev = cm.K.combine(np.ascontiguousarray(mat_inv[:, s, :]), d, out=coefs_dev)
-        return coefs_dev, fused[0][1], fused[0][2], fused[0][3]
+        return coefs_dev, fused[0].lead_dims, fused[0].lead_shape, fused[0].coords
 
     @cached.meth
     def coefs(self, order=None, order_dim="porder", minus_log=None):
