@@ -657,6 +657,11 @@ def config_c2(dev) -> dict:
     return {"workload": workload_name(b), "ms_per_step": step_ms, "replicates_per_s": 1000 / step_ms * 1e3,
             "samples_per_s_reduce": None if "reduce" not in kern else 1e7 / (kern["reduce"]["ms_per_step"] * 1e-3),
             "whole_step_frac_fp64": flops / (step_ms * 1e-3) / 1e12 / fp64_peak_tflops(),
+            "bound": "instruction issue (partition: integer PCG64 + ring bookkeeping, 44 % issue-active, ALU 35 % + IMAD "
+                     "17 % of the pipes) and the fp64 pipe (consume: 26 fp64 instructions per draw for 18 counted FMAs); "
+                     "profiles/r02_target_kernels_ncu_full.txt",
+            "note": "device-timed steps run with sync_rng=False and a deferred status word (no host sync inside the timed "
+                    "region); the public API call pays one D2H of raw_used per call to hand the generator state back",
             "kernels": {k: {**v, "share_of_step": v["ms_per_step"] / step_ms} for k, v in kern.items()}}
 
 

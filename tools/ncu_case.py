@@ -23,6 +23,12 @@ if which == "gather":
     K.sampler_resample(np.random.default_rng(1), x, u, nrep, 8, sync_rng=False)
 elif which == "reduce":
     K.reduce_vals(x, u, 8)
+elif which == "reduce_scalar":  # python tools/ncu_case.py reduce_scalar [nsamp order]: scalar K1 at HBM-resident size
+    nw, kw = (int(v) for v in (sys.argv[2:4] if len(sys.argv) > 3 else (100_000_000, 8)))
+    uw = torch.randn(nw, dtype=torch.float64, device="cuda") * 5.3 + 175
+    xw = 1e-3 * uw + 0.02 * torch.randn(nw, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        K.reduce_vals(xw, uw, kw)
 elif which == "wide":  # python tools/ncu_case.py wide nsamp nchan order   (TXB_WIDE_TMA picks the kernel)
     nw, cw, kw = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
     xw = torch.randn((nw, cw), dtype=torch.float64, device="cuda")
