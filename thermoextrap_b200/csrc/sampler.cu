@@ -686,8 +686,8 @@ int run_scan(const Plan& p, EmitArgs& e, cudaStream_t st) {
     TXB_CUDA_LAUNCH_CHECK("k_sampler_scan");
     k_sampler_iter_scan<<<(p.nblocks + 7) / 8, 256, 0, st>>>(e.block_base, e.iter_count, e.iter_base, p.nblocks, p.ipb);
     TXB_CUDA_LAUNCH_CHECK("k_sampler_iter_scan");
-    k_sampler<MODE_LOCATE, 1, false, false, int64_t><<<p.nblocks, SMP_THREADS, 0, st>>>(p.a, e);
-    TXB_CUDA_LAUNCH_CHECK("k_sampler<locate>");
+    k_sampler_locate<<<1, BK_THREADS, 0, st>>>(p.a, e.iter_base, (int64_t)p.nblocks * p.ipb, e.raw_used);
+    TXB_CUDA_LAUNCH_CHECK("k_sampler_locate");
     return TXB_OK;
 }
 

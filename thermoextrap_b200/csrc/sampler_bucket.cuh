@@ -321,6 +321,62 @@ __global__ void __launch_bounds__(NTH, 1)
     }
 }
 
+// Raw position of output #count-1 (what numpy's generator has consumed when the table is complete), from the
+// per-iteration position table: binary-search the iteration that emits it, regenerate that ONE iteration (4096 LCG
+// steps) and scan.  Replaces the MODE_LOCATE pass of k_sampler, where the single block holding the last output
+// walked its whole range serially (30 ms on the critical path of every 1e11-draw plan, ncu launch list r2).
+__global__ void __launch_bounds__(BK_THREADS, 1)
+    k_sampler_locate(const __grid_constant__ SamplerArgs a, const int64_t* __restrict__ iter_base, int64_t niter,
+                     int64_t* __restrict__ raw_used) {
+    constexpr int T = SMP_T, NSLOT = 2 * T;
+    __shared__ int sm_warp[BK_THREADS / 32];
+    __shared__ long long sm_j;
+    const int64_t target = a.count - 1;
+    if (threadIdx.x == 0) {
+        int64_t lo = 0, hi = niter - 1;
+        while (lo < hi) {   // last iteration whose first output position is <= target
+            const int64_t mid = (lo + hi + 1) >> 1;
+            if (iter_base[mid] <= target) lo = mid; else hi = mid - 1;
+        }
+        sm_j = lo;
+    }
+    __syncthreads();
+    const int64_t j = sm_j;
+    const int64_t P = iter_base[j];
+    const int64_t q0 = (j * BK_THREADS + threadIdx.x) * T;   // first LCG step of this thread
+    uint64_t hi = a.s_hi, lo = a.s_lo;
+    {
+        uint64_t q = (uint64_t)q0;
+        for (int i = 0; q != 0 && i < SMP_NPOW; ++i, q >>= 1)
+            if (q & 1) affine_apply(hi, lo, a.pow2[i]);
+    }
+    const uint32_t n = a.n, thresh = a.thresh;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int k = 0; k < T; ++k) {
+        const uint64_t o = pcg_step_out(hi, lo, a.inc_hi, a.inc_lo);
+        if ((uint32_t)((uint64_t)(uint32_t)o * n) >= thresh) mask |= 1u << (2 * k);
+        if ((uint32_t)((o >> 32) * (uint64_t)n) >= thresh) mask |= 1u << (2 * k + 1);
+    }
+    const bool pre_acc = j == 0 && threadIdx.x == 0 && a.pre_valid != 0 &&
+                         (uint32_t)((uint64_t)a.pre_u32 * n) >= thresh;
+    int total;
+    int off = bk_block_scan<BK_THREADS>(__popc(mask) + (pre_acc ? 1 : 0), sm_warp, total);
+    // raw 32-bit draw number of slot 0 of this thread (0-based, the buffered half is #0)
+    const int64_t raw0 = (int64_t)a.pre_valid + 2 * q0;
+    if (pre_acc) {
+        if (P + off == target) *raw_used = 1;
+        ++off;
+    }
+#pragma unroll
+    for (int k = 0; k < NSLOT; ++k) {
+        if (mask & (1u << k)) {
+            if (P + off == target) *raw_used = raw0 + k + 1;
+            ++off;
+        }
+    }
+}
+
 struct ConsumeArgs {
     const double2* packed;   // [ndat] (x - cx, u - cu)
     const double* w;         // [ndat] or NULL
