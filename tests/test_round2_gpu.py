@@ -194,7 +194,7 @@ def test_binomials_per_device(K):
 
 
 # ------------------------------------------------------------------ wide-x contraction kernels, every form
-@pytest.mark.parametrize("version", [0, 1, 2, 3])
+@pytest.mark.parametrize("version", [0, 1, 2, 3, 4])
 @pytest.mark.parametrize("dtype", ["uint8", "uint16", "int32", "int64"])
 @pytest.mark.parametrize("n,nv,nrep,order,kind", [
     (1500, 17, 150, 1, "x"), (2111, 64, 130, 6, "x"), (1203, 33, 70, 7, "xw"), (1500, 5, 129, 6, "x"),

@@ -103,7 +103,7 @@ extern "C" int txb_indices_to_freq(const int64_t* indices, int64_t nrep, int64_t
 
 extern "C" int txb_set_resample_kernel(int version) {
     const int prev = rs_mma_version();
-    if (version >= 0 && version <= 3) g_rs_mma_version = version;
+    if (version >= 0 && version <= 4) g_rs_mma_version = version;
     return prev;
 }
 

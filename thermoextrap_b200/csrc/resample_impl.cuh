@@ -79,7 +79,7 @@ extern int g_rs_mma_version;   // resample.cu; txb_set_resample_kernel overrides
 inline int rs_mma_version() {
     if (g_rs_mma_version < 0) {
         const char* e = getenv("TXB_RESAMPLE_MMA");
-        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 3;
+        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '4') ? e[0] - '0' : 3;
     }
     return g_rs_mma_version;
 }
@@ -116,7 +116,7 @@ int rs_launch_mma(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st)
 }
 
 // second form (operand generation overlapped with the DMMAs); WM = 4: 8 warps, WM = 8: 16 warps
-template <int K, typename FT, int WM>
+template <int K, typename FT, int WM, bool LUT = false>
 int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
     using C = Rm2Cfg<K, FT, WM>;
     const RsPlan p = rs_plan(a.nsamp, a.nchan, a.nrep, C::RT, C::ST, C::CT);
@@ -129,7 +129,7 @@ int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st
     a.aligned = ((reinterpret_cast<uintptr_t>(a.freq) & 15) == 0) && ((a.ldf * es) % 16 == 0);
     static bool attr_done = false;
     if (!attr_done) {
-        if (cudaFuncSetAttribute(k_resample_mma2<K, FT, WM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(k_resample_mma2<K, FT, WM, LUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)C::SMEM) != cudaSuccess) {
             set_error("k_resample_mma2: cannot opt in to %zu bytes of shared memory", (size_t)C::SMEM);
             cudaGetLastError();
@@ -140,7 +140,7 @@ int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st
     const dim3 grid((unsigned)p.nctile, (unsigned)p.nreptile, (unsigned)p.nslab);
     {
         ProfScope prof("resample.wide", st);
-        k_resample_mma2<K, FT, WM><<<grid, C::NT, C::SMEM, st>>>(a);
+        k_resample_mma2<K, FT, WM, LUT><<<grid, C::NT, C::SMEM, st>>>(a);
     }
     TXB_CUDA_LAUNCH_CHECK("k_resample_mma2");
     return launch_sum_parts(ws, p.nslab, n, upc ? S0 : S1, st);
@@ -150,6 +150,10 @@ int rs_launch_mma2(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st
 template <int K, typename FT>
 int rs_launch_wide_mma(const RsArgs& a, double* S0, double* S1, double* ws, cudaStream_t st) {
     const int v = rs_mma_version();
+    if (v == 4) {   // 16 warps + shared-memory conversion table (uint8 tables; other dtypes: form 3)
+        if constexpr (sizeof(FT) == 1) return rs_launch_mma2<K, FT, 8, true>(a, S0, S1, ws, st);
+        else return rs_launch_mma2<K, FT, 8>(a, S0, S1, ws, st);
+    }
     if (v == 3) return rs_launch_mma2<K, FT, 8>(a, S0, S1, ws, st);
     if (v == 2) return rs_launch_mma2<K, FT, 4>(a, S0, S1, ws, st);
     if (v == 1) return rs_launch_mma<K, FT>(a, S0, S1, ws, st);

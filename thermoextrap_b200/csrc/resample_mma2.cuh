@@ -82,9 +82,13 @@ template <int I> __device__ __forceinline__ uint32_t apack_get(const APack<8>& a
     return I == 0 ? a.w0.x : I == 1 ? a.w0.z : I == 2 ? a.w1.x : a.w1.z;
 }
 
-template <int K, typename FT, int WM>
+// LUT: table entries become fp64 through a 256-entry shared-memory table instead of the 2^52 magic DADD (uint8 tables
+// only).  ncu on the DADD form: the hottest stalled instructions of the kernel are those DADDs, queued behind the
+// DMMAs in the same fp64 pipe with the warp's next fragments waiting on them.
+template <int K, typename FT, int WM, bool LUT = false>
 __global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
     using C = Rm2Cfg<K, FT, WM>;
+    static_assert(!LUT || sizeof(FT) == 1, "the conversion table covers uint8 entries");
     constexpr int ES = C::ES, VS = C::VS, NT = C::NT, MT = C::MT, NTL = C::NTL, RT = C::RT, CT = C::CT;
     constexpr int PP = C::PP, ST = C::ST, NG = C::NG, PITCH = C::PITCH, NSTAGE = C::NSTAGE, NGRP = C::NGRP;
     constexpr int NPIECE = C::NPIECE, PROWS = C::PROWS, GPP = C::GPP;
@@ -103,6 +107,10 @@ __global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
     const int nstage = (int)((s_end - s_begin + ST - 1) / ST);
     const bool has_x = a.x != nullptr, has_w = a.w != nullptr;
     const bool upc = a.ldu != 0;
+    __shared__ double s_cvt[LUT ? 256 : 1];
+    if (LUT) {
+        for (int i = tid; i < 256; i += NT) s_cvt[i] = (double)i;   // visible after the prologue's barrier
+    }
 
     const unsigned char* fbase = reinterpret_cast<const unsigned char*>(a.freq);
     auto issue_A = [&](int it) {
@@ -229,7 +237,7 @@ __global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
                 for (int m = 0; m < MT; ++m) {
                     const uint32_t v = i == 0 ? apack_get<0>(ac[m]) : i == 1 ? apack_get<1>(ac[m])
                                      : i == 2 ? apack_get<2>(ac[m]) : apack_get<3>(ac[m]);
-                    af[m] = u32_to_f64(v);
+                    af[m] = LUT ? s_cvt[v] : u32_to_f64(v);
                 }
 #pragma unroll
                 for (int n = 0; n < NTL; ++n) bc[n] = bf[n];

@@ -42,7 +42,7 @@ def main() -> None:
     tags = ("reduce", "sampler_count", "bucket_scatter", "bucket_hist", "resample")
     ref = None
     rows = []
-    for ver, nth in ((1, 512), (3, 512), (3, 1024)):
+    for ver, nth in ((3, 512), (4, 512)):
         lib.txb_set_resample_kernel(ver)
         lib.txb_set_scatter_threads(nth)
         job.step()
