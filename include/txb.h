@@ -348,7 +348,7 @@ int txb_smem_atomic_peak_launch(int iters, int blocks_per_sm, int nbins, double*
 
 /* Which wide-x (> 4 channels) contraction kernel txb_resample_* launches: 0 = register-tiled DFMA,
  * 1 = k_resample_mma (DMMA, round 1), 2 = k_resample_mma2 (operand generation overlapped with the DMMAs,
- * 4-sample table loads; 8 warps), 3 = k_resample_mma2 with 16 warps (the default), 4 = form 3 with the uint8 table
+ * 4-sample table loads; 8 warps), 3 = k_resample_mma2 with 16 warps, 4 (the default) = form 3 with uint8 table
  * entries converted through a shared-memory table instead of a DADD (other table dtypes: as form 3).
  * Same results within rounding; exists so tests and bench.py can A/B the forms in one process (also
  * TXB_RESAMPLE_MMA in the environment).  Returns the previous setting; other values only query.  No

@@ -72,14 +72,15 @@ int rs_launch(RsArgs a, double* S0, double* S1, double* ws, cudaStream_t st) {
 }
 
 // wide x on the fp64 tensor cores.  TXB_RESAMPLE_MMA = 0: DFMA tile; 1: k_resample_mma (round 1);
-// 2: k_resample_mma2 (operand generation overlapped with the DMMAs), 8 warps; 3 (default): the same with 16
+// 2: k_resample_mma2 (operand generation overlapped with the DMMAs), 8 warps; 3: the same with 16
 // warps -- measured at 1e8 x 64, order 6, uint8 table, 256 replicates (profiles/r02_exp_mma_forms.json):
-// form 1 31.4, form 2 31.2, form 3 32.1 TFLOP/s
+// form 1 31.4, form 2 31.2, form 3 32.1 TFLOP/s; 4 (default): form 3 with uint8 entries converted through a
+// shared-memory table instead of the 2^52 DADD: 32.6 TFLOP/s
 extern int g_rs_mma_version;   // resample.cu; txb_set_resample_kernel overrides the environment
 inline int rs_mma_version() {
     if (g_rs_mma_version < 0) {
         const char* e = getenv("TXB_RESAMPLE_MMA");
-        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '4') ? e[0] - '0' : 3;
+        g_rs_mma_version = (e && e[0] >= '0' && e[0] <= '4') ? e[0] - '0' : 4;
     }
     return g_rs_mma_version;
 }

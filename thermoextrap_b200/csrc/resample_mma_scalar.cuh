@@ -54,6 +54,13 @@ __global__ void __launch_bounds__(256, 3) k_resample_mma_scalar(const RsArgs a) 
     const int64_t s_end = min(a.nsamp, s_begin + a.slab_len);
     const int nstage = (int)((s_end - s_begin + ST - 1) / ST);
     const bool has_w = a.w != nullptr;
+    // uint8 entries become fp64 through a shared-memory table, not the 2^52 DADD (which queues behind the DMMAs in the
+    // fp64 pipe: resample_mma2.cuh); visible after the first block-wide barrier of the stage loop
+    constexpr bool LUT = sizeof(FT) == 1;
+    __shared__ double s_cvt[LUT ? 256 : 1];
+    if (LUT) {
+        for (int i = tid; i < 256; i += NT) s_cvt[i] = (double)i;
+    }
 
     const unsigned char* fbase = reinterpret_cast<const unsigned char*>(a.freq);
     auto issue_A = [&](int it) {
@@ -141,7 +148,7 @@ __global__ void __launch_bounds__(256, 3) k_resample_mma_scalar(const RsArgs a) 
 #pragma unroll
             for (int m = 0; m < MT; ++m) {
                 const FT v = *reinterpret_cast<const FT*>(bufA + (size_t)(m * 8) * PITCH + sl * ES);
-                af[m] = u32_to_f64((uint32_t)v);  // counts are < 2^31
+                af[m] = LUT ? s_cvt[(uint32_t)v & 0xffu] : u32_to_f64((uint32_t)v);  // counts are < 2^31
             }
 #pragma unroll
             for (int n = 0; n < NTL; ++n) bf[n] = bufP[(size_t)sl * PP + n * 8];
