@@ -172,3 +172,32 @@ def test_product_has_no_cpu_fallback():
 def test_product_does_not_import_oracle():
     for p in (ROOT / "thermoextrap_b200").rglob("*.py"):
         assert "oracle" not in p.read_text(), p
+
+
+def test_new_entry_points_reject_bad_arguments_before_any_launch():
+    """Argument validation of the round-2 entry points returns an error code and a message without touching the
+    device (so this runs without a GPU): null pointers, unknown family / mode, records too short for the order,
+    orders above the generated range (TXB_ERR_UNSUPPORTED = 2), ninner not dividing nelem, ddof >= nrep."""
+    import ctypes as C
+
+    from thermoextrap_b200 import _lib
+
+    lib = _lib.load()
+    one = C.c_void_p(8)   # a non-null placeholder: every call below fails validation before dereferencing
+    err = lambda: lib.txb_last_error_string().decode()  # noqa: E731
+    assert lib.txb_beta_predict_f64(None, 4, 7, 0, 6, 0, 0, one, 1, one, None) == 1 and "null" in err()
+    assert lib.txb_beta_predict_f64(one, 4, 7, 9, 6, 0, 0, one, 1, one, None) == 1 and "family" in err()
+    assert lib.txb_beta_predict_f64(one, 4, 7, 0, 6, 0, 7, one, 1, one, None) == 1 and "mode" in err()
+    assert lib.txb_beta_predict_f64(one, 4, 5, 0, 6, 0, 0, one, 1, one, None) == 1 and "order 6" in err()
+    assert lib.txb_beta_predict_f64(one, 4, 20, 0, 12, 0, 0, one, 1, one, None) == 2 and "generated maximum" in err()
+    assert lib.txb_beta_predict_f64(one, 4, 7, 0, 6, 0, 0, None, 1, one, None) == 1 and "dalpha" in err()
+    assert lib.txb_beta_predict_f64(one, 0, 7, 0, 6, 0, 0, one, 1, one, None) == 0     # nothing to do
+    assert lib.txb_lnpi_predict_f64(one, 6, 7, 1, 6, 0, one, 1, None, one, 3, one, None) == 1 and "null" in err()
+    assert lib.txb_lnpi_predict_f64(one, 7, 7, 1, 6, 0, one, 1, one, one, 3, one, None) == 1 and "multiple" in err()
+    assert lib.txb_lnpi_predict_f64(one, 6, 5, 1, 6, 0, one, 1, one, one, 3, one, None) == 1 and "order 6" in err()
+    assert lib.txb_combine_f64(one, 3, 600, one, 10, 0, one, None) == 1 and "nt <= 512" in err()
+    assert lib.txb_combine_f64(one, 0, 5, one, 10, 0, one, None) == 0
+    assert lib.txb_mean_var_f64(one, 2, 5, 3, 5, one, one, None) == 1 and "ddof" in err()
+    assert lib.txb_mean_var_f64(None, 2, 5, 3, 0, one, one, None) == 1 and "null" in err()
+    assert lib.txb_set_resample_kernel(-1) in (0, 1, 2, 3, 4)
+    assert lib.txb_set_scatter_threads(-1) in (512, 1024)
