@@ -179,12 +179,17 @@ __global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
             du = pu[q] - piv_u;
             lead = pwt[q] * (px[q] - piv_c);
         }
-        double p = lead;
+        // powers by squaring (depth log2 K instead of K): these multiplies share the fp64 pipe with the DMMAs and
+        // each waits in its queue -- ncu's per-instruction samples put the dependent `p *= du` chain at the top of
+        // the stalled instructions once the table conversion had left the pipe
+        double pw[K + 1];
+        pw[0] = 1.0;
+        if (K >= 1) pw[1] = du;
 #pragma unroll
-        for (int j = 0; j <= K; ++j) {
-            row[cl * (K + 1) + j] = p;
-            p *= du;
-        }
+        for (int j = 2; j <= K; ++j) pw[j] = pw[j >> 1] * pw[j - (j >> 1)];
+        row[cl * (K + 1)] = lead;
+#pragma unroll
+        for (int j = 1; j <= K; ++j) row[cl * (K + 1) + j] = lead * pw[j];
     };
 
     double acc[MT][NTL][2];
