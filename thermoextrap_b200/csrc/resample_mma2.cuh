@@ -18,6 +18,10 @@
 #pragma once
 #include "resample_mma.cuh"
 
+#ifndef TXB_MMA2_ST96
+#define TXB_MMA2_ST96 1
+#endif
+
 namespace txb {
 
 template <int K, typename FT, int WM_>
@@ -33,7 +37,11 @@ struct Rm2Cfg {
     static constexpr int NCOL = CT * (K + 1);
     static constexpr int PP = NCOL + 5;                   // odd pitch (NCOL is even): see header note 2
     static constexpr size_t SMEM64 = (size_t)3 * RT * (64 * ES + 16) + 2 * (size_t)64 * PP * 8;
-    static constexpr int ST = SMEM64 <= 200 * 1024 ? 64 : 32;
+    static constexpr size_t SMEM96 = (size_t)3 * RT * (96 * ES + 16) + 2 * (size_t)96 * PP * 8;
+    // samples per stage = samples per block-wide barrier: as many as shared memory holds (227 KB per CTA minus the
+    // 2 KB conversion table and the runtime's 1 KB)
+    static constexpr int ST = (TXB_MMA2_ST96 && ES == 1 && SMEM96 <= 222 * 1024 && (96 * CT) % NT == 0)
+                                  ? 96 : SMEM64 <= 200 * 1024 ? 64 : 32;
     static constexpr int NGRP = ST / 16;                  // 16-sample groups per stage
     static constexpr int NG = ST / VS;
     static constexpr int PITCH = ST * ES + 16;
@@ -179,17 +187,14 @@ __global__ void __launch_bounds__(WM * 64, 1) k_resample_mma2(const RsArgs a) {
             du = pu[q] - piv_u;
             lead = pwt[q] * (px[q] - piv_c);
         }
-        // powers by squaring (depth log2 K instead of K): these multiplies share the fp64 pipe with the DMMAs and
-        // each waits in its queue -- ncu's per-instruction samples put the dependent `p *= du` chain at the top of
-        // the stalled instructions once the table conversion had left the pipe
-        double pw[K + 1];
-        pw[0] = 1.0;
-        if (K >= 1) pw[1] = du;
+        // (powers by squaring -- depth log2 K, 5 more multiplies -- measured 0.8 % slower: the extra fp64 ops cost more
+        // in the shared pipe than the shorter dependency chain saves)
+        double p = lead;
 #pragma unroll
-        for (int j = 2; j <= K; ++j) pw[j] = pw[j >> 1] * pw[j - (j >> 1)];
-        row[cl * (K + 1)] = lead;
-#pragma unroll
-        for (int j = 1; j <= K; ++j) row[cl * (K + 1) + j] = lead * pw[j];
+        for (int j = 0; j <= K; ++j) {
+            row[cl * (K + 1) + j] = p;
+            p *= du;
+        }
     };
 
     double acc[MT][NTL][2];
