@@ -320,8 +320,9 @@ int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim, int famil
 /* The same launch for the lnPi family (lnpi.py:42-116: d_0 = lnPi0, d_1 = mu.N - <u>, d_n = -d^(n-1)<u>/dbeta^(n-1),
  * i.e. the u_ave family one order lower, shifted): comom = x_is_u records [nelem, 2, kdim] with kdim >= order;
  * central != 0 selects the central form; lnpi0 / mudotn [ninner] device doubles, element e reads index e % ninner
- * (leading dims such as rep broadcast).  No -log flag (the reference has none for lnPi); modes as above.       */
-int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int mode,
+ * (leading dims such as rep broadcast).  flags: 2 = divide by i! in mode 3; 1 (-log) is rejected (the reference has
+ * none for lnPi); modes as above.                                                                            */
+int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int flags, int mode,
                          const double* dalpha, int nalpha, const double* lnpi0, const double* mudotn,
                          int64_t ninner, double* out, void* stream);
 /* out[a, e] = (accumulate ? out[a, e] : 0) + sum_t W[a, t] D[t, e]: InterpModel.predict (models.py:909-932)

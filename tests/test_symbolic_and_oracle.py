@@ -192,9 +192,10 @@ def test_new_entry_points_reject_bad_arguments_before_any_launch():
     assert lib.txb_beta_predict_f64(one, 4, 20, 0, 12, 0, 0, one, 1, one, None) == 2 and "generated maximum" in err()
     assert lib.txb_beta_predict_f64(one, 4, 7, 0, 6, 0, 0, None, 1, one, None) == 1 and "dalpha" in err()
     assert lib.txb_beta_predict_f64(one, 0, 7, 0, 6, 0, 0, one, 1, one, None) == 0     # nothing to do
-    assert lib.txb_lnpi_predict_f64(one, 6, 7, 1, 6, 0, one, 1, None, one, 3, one, None) == 1 and "null" in err()
-    assert lib.txb_lnpi_predict_f64(one, 7, 7, 1, 6, 0, one, 1, one, one, 3, one, None) == 1 and "multiple" in err()
-    assert lib.txb_lnpi_predict_f64(one, 6, 5, 1, 6, 0, one, 1, one, one, 3, one, None) == 1 and "order 6" in err()
+    assert lib.txb_lnpi_predict_f64(one, 6, 7, 1, 6, 0, 0, one, 1, None, one, 3, one, None) == 1 and "null" in err()
+    assert lib.txb_lnpi_predict_f64(one, 7, 7, 1, 6, 0, 0, one, 1, one, one, 3, one, None) == 1 and "multiple" in err()
+    assert lib.txb_lnpi_predict_f64(one, 6, 5, 1, 6, 0, 0, one, 1, one, one, 3, one, None) == 1 and "order 6" in err()
+    assert lib.txb_lnpi_predict_f64(one, 6, 7, 1, 6, 1, 0, one, 1, one, one, 3, one, None) == 1 and "-log" in err()
     assert lib.txb_combine_f64(one, 3, 600, one, 10, 0, one, None) == 1 and "nt <= 512" in err()
     assert lib.txb_combine_f64(one, 0, 5, one, 10, 0, one, None) == 0
     assert lib.txb_mean_var_f64(one, 2, 5, 3, 5, one, one, None) == 1 and "ddof" in err()

@@ -80,7 +80,7 @@ SIGNATURES = {
     "txb_perturb_workspace_bytes": (_sz, [_i64, _i64, _int]),
     "txb_perturb_predict_f64": (_int, [_p, _p, _i64, _i64, _i64, _p, _int, _p, _p, _sz, _p]),
     "txb_beta_predict_f64": (_int, [_p, _i64, _int, _int, _int, _int, _int, _p, _int, _p, _p]),
-    "txb_lnpi_predict_f64": (_int, [_p, _i64, _int, _int, _int, _int, _p, _int, _p, _p, _i64, _p, _p]),
+    "txb_lnpi_predict_f64": (_int, [_p, _i64, _int, _int, _int, _int, _int, _p, _int, _p, _p, _i64, _p, _p]),
     "txb_combine_f64": (_int, [_p, _int, _int, _p, _i64, _int, _p, _p]),
     "txb_mean_var_f64": (_int, [_p, _i64, _i64, _i64, _int, _p, _p, _p]),
     "txb_set_resample_kernel": (_int, [_int]),

@@ -266,9 +266,9 @@ extern "C" int txb_beta_predict_f64(const double* comom, int64_t nelem, int kdim
     return TXB_OK;
 }
 
-extern "C" int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int mode,
-                                    const double* dalpha, int nalpha, const double* lnpi0, const double* mudotn,
-                                    int64_t ninner, double* out, void* stream) {
+extern "C" int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim, int central, int order, int flags,
+                                    int mode, const double* dalpha, int nalpha, const double* lnpi0,
+                                    const double* mudotn, int64_t ninner, double* out, void* stream) {
     TXB_CHECK_ARG(comom && out && lnpi0 && mudotn, "txb_lnpi_predict_f64: null pointer");
     TXB_CHECK_ARG(mode >= BF_MODE_SUM && mode <= BF_MODE_DERIVS, "txb_lnpi_predict_f64: bad mode %d", mode);
     TXB_CHECK_ARG(order >= 0 && kdim >= order && kdim >= 1,
@@ -282,7 +282,8 @@ extern "C" int txb_lnpi_predict_f64(const double* comom, int64_t nelem, int kdim
         return TXB_ERR_UNSUPPORTED;
     }
     if (nelem == 0 || (mode != BF_MODE_DERIVS && nalpha == 0)) return TXB_OK;
-    BetaFusedArgs a{comom, nelem, kdim, 0, mode, dalpha, nalpha, out, lnpi0, mudotn, ninner};
+    TXB_CHECK_ARG((flags & BF_FLAG_MINUS_LOG) == 0, "txb_lnpi_predict_f64: the lnPi family has no -log form");
+    BetaFusedArgs a{comom, nelem, kdim, flags & BF_FLAG_NORM, mode, dalpha, nalpha, out, lnpi0, mudotn, ninner};
     cudaStream_t st = (cudaStream_t)stream;
     const int rc = central ? launch_beta_fused<4>(a, order, st) : launch_beta_fused<5>(a, order, st);
     if (rc != TXB_OK) return rc;

@@ -1027,17 +1027,10 @@ def lnpi_predict(comom, order: int, central: bool, lnpi0, mudotn, dalpha=None, m
         shape = (na, nelem) if mode == PREDICT_SUM else (na, order + 1, nelem)
     out = torch.empty(shape, dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
-        st = lib.txb_lnpi_predict_f64(c.data_ptr(), nelem, kdim, 1 if central else 0, order, mode, _ptr(d), na,
-                                      l0.data_ptr(), mn.data_ptr(), ninner, out.data_ptr(), _stream_ptr())
+        st = lib.txb_lnpi_predict_f64(c.data_ptr(), nelem, kdim, 1 if central else 0, order, 2 if norm else 0, mode,
+                                      _ptr(d), na, l0.data_ptr(), mn.data_ptr(), ninner, out.data_ptr(), _stream_ptr())
     check(st, "txb_lnpi_predict_f64")
     launch_count += 1
-    if mode == PREDICT_DERIVS and not norm:   # the kernel's derivative mode honours the NORM flag only; lnPi has no flags
-        return out
-    if mode == PREDICT_DERIVS:
-        import math
-
-        fact = torch.tensor([math.factorial(i) for i in range(order + 1)], dtype=torch.float64, device=dev)
-        return out / fact[:, None]
     return out
 
 
