@@ -143,6 +143,44 @@ def test_x_to_u_substitution(central, post_func):
         assert sp.expand(e.subs(subs) - fu.exprs[i]) == 0
 
 
+def test_named_constructors_keep_reference_signatures():
+    """reference beta.py:291-470: positional order of each named constructor, its validation errors, and
+    ``from_name`` rejecting unknown quantities."""
+    from thermoextrap_b200.beta import SymDerivBeta, du_func, u_func_central, x_func_central_beta, xu_func
+
+    def same(a, b, n=4):
+        assert [str(a[i]) for i in range(n)] == [str(b[i]) for i in range(n)]
+        assert [str(x) for x in a.args] == [str(x) for x in b.args]
+
+    same(SymDerivBeta.x_ave(True, True), SymDerivBeta.x_ave(xalpha=True, central=True))
+    same(SymDerivBeta.u_ave(True), SymDerivBeta.from_name("u_ave", central=True))
+    same(SymDerivBeta.dun_ave(3), SymDerivBeta.from_name("dun_ave", n=3))
+    same(SymDerivBeta.dxdun_ave(2, True, True, None, 1), SymDerivBeta.dxdun_ave(n=2, xalpha=True, d=1))
+    same(SymDerivBeta.un_ave(2), SymDerivBeta.from_name("un_ave", n=2, central=False))
+    same(SymDerivBeta.xun_ave(2, 1, True), SymDerivBeta.from_name("xun_ave", n=2, d=1, xalpha=True))
+    for bad in (lambda: SymDerivBeta.dun_ave(1), lambda: SymDerivBeta.dun_ave(2, central=False),
+                lambda: SymDerivBeta.dxdun_ave(0),
+                lambda: SymDerivBeta.un_ave(0), lambda: SymDerivBeta.un_ave(2, central=True),
+                lambda: SymDerivBeta.xun_ave(-1), lambda: SymDerivBeta.xun_ave(1, central=True),
+                lambda: SymDerivBeta.from_name("nope")):
+        with pytest.raises(ValueError):
+            bad()
+    with pytest.raises(TypeError):
+        SymDerivBeta.dun_ave()
+    with pytest.raises(TypeError):   # xalpha needs an integer d (reference beta.py:395-397)
+        SymDerivBeta.dxdun_ave(1, xalpha=True)
+    with pytest.raises(TypeError):
+        SymDerivBeta.u_ave(True, True, None, 1)
+    # the function classes: boundary values, symbols, argument lists
+    b = sp.Symbol("beta")
+    assert du_func(b, 0) == 1 and du_func(b, 1) == 0 and xu_func(b, 0).nargs is not None
+    assert str(du_func(None, 3)) == "du[3]" and str(u_func_central(None)) == "u"
+    assert str(x_func_central_beta(None, 2)) == "x1[2]" and str(xu_func(None, 2, 1)) == "xu[2, 1]"
+    assert [str(a) for a in x_func_central_beta.deriv_args()] == ["x1", "du", "dxdu"]
+    assert [str(a) for a in xu_func.deriv_args()] == ["u", "xu"]
+    assert str(sp.diff(du_func(b, 3), b)) == str(3 * du_func(b, 2) ** 2 - du_func(b, 4))
+
+
 # ------------------------------------------------------------------ ABI surface
 def test_library_exports_every_declared_symbol():
     from thermoextrap_b200 import _lib
