@@ -56,6 +56,7 @@ class MomentRule:
     inherits: tuple = ()
     attr: str | None = None   # class attribute holding the sympy symbol (the reference's spelling)
     prepend: bool = False     # own symbol before the inherited ones in deriv_args
+    extras: tuple = ()        # further plain symbols the recurrence uses, appended to deriv_args (lnpi.py)
 
 
 F = SimpleNamespace()   # name -> sympy.Function class, filled below (the recurrences look each other up here)
@@ -65,9 +66,11 @@ def _function_class(rule: MomentRule):
     indexed = rule.index(*([0] * (rule.nargs[0] if isinstance(rule.nargs, tuple) else rule.nargs - 1))) != ()
     sym = get_default_indexed(rule.symbol) if indexed else get_default_symbol(rule.symbol)
 
+    extras = [get_default_symbol(e) for e in rule.extras]
+
     def deriv_args(cls):
         inherited = [a for fam in rule.inherits for a in getattr(F, fam).deriv_args()]
-        return [sym, *inherited] if rule.prepend else [*inherited, sym]
+        return [sym, *inherited, *extras] if rule.prepend else [*inherited, sym, *extras]
 
     def fdiff(self, argindex=1):
         beta, *rest = self.args
@@ -85,9 +88,15 @@ def _function_class(rule: MomentRule):
     body = {
         "nargs": rule.nargs, "__doc__": f"sympy function of the {rule.symbol!r} moments (rule table, beta.py)",
         "deriv_args": classmethod(deriv_args), "fdiff": fdiff, "eval": classmethod(eval_), "rule": rule,
-        rule.attr or rule.symbol: sym,
+        rule.attr or rule.symbol: sym, **{str(e): e for e in extras},
     }
     return type(rule.name, (SymFuncBase,), body)
+
+
+def register_rule(rule: MomentRule):
+    """Add a family to the namespace ``F`` and return its ``sympy.Function`` class."""
+    setattr(F, rule.name, _function_class(rule))
+    return getattr(F, rule.name)
 
 
 def _n_only(n):
@@ -123,8 +132,7 @@ _RULES = (
                inherits=("u_func",)),
 )
 for _rule in _RULES:
-    setattr(F, _rule.name, _function_class(_rule))
-    globals()[_rule.name] = getattr(F, _rule.name)   # importable by the reference's names (lnpi.py uses two of them)
+    globals()[_rule.name] = register_rule(_rule)   # importable by the reference's names (lnpi.py uses two of them)
 
 
 # ---------------------------------------------------------------- the quantities SymDerivBeta can expand

@@ -22,52 +22,25 @@ from attrs import validators as attv
 from . import beta as beta_xpan
 from .core import cached
 from .core.attrs_utils import convert_dims_to_tuple
-from .core.sputils import get_default_indexed, get_default_symbol
+from .core.sputils import get_default_symbol
 from .core.xr import DataArray, dot
 from .data import DataCallbackABC
-from .models import Derivatives, ExtrapModel, SymFuncBase, SymSubs
+from .models import Derivatives, ExtrapModel, SymSubs
 
 
-class lnPi_func_central(SymFuncBase):
-    """lnPi with derivatives in central moments of u: first derivative ``mudotN - <u>``."""
-
-    nargs = 1
-    u = get_default_symbol("u")
-    lnPi0 = get_default_symbol("lnPi0")
-    mudotN = get_default_symbol("mudotN")
-
-    @classmethod
-    def deriv_args(cls):
-        return [*beta_xpan.u_func_central.deriv_args(), cls.lnPi0, cls.mudotN]
-
-    def fdiff(self, argindex=1):
-        (beta,) = self.args
-        return self.mudotN - beta_xpan.u_func_central(beta)
-
-    @classmethod
-    def eval(cls, beta):
-        return cls.lnPi0 if beta is None else None
+def _lnpi_rule(name, energy_family, energy):
+    """lnPi as one more family of the beta rule table: value ``lnPi0`` at beta0, first derivative ``mu.N - <u>``
+    (``energy(F, beta)`` is ``<u>`` in the chosen moment form), arguments = those of ``<u>`` + (lnPi0, mudotN)."""
+    mudotn = get_default_symbol("mudotN")
+    return beta_xpan.MomentRule(
+        name, "lnPi0", 1, index=lambda: (), fixed=lambda: None,
+        ddbeta=lambda F, b: mudotn - energy(F, b), inherits=(energy_family,), extras=("mudotN",))
 
 
-class lnPi_func_raw(SymFuncBase):
-    """Raw-moment version of :class:`lnPi_func_central`."""
-
-    nargs = 1
-    u = get_default_indexed("u")
-    lnPi0 = get_default_symbol("lnPi0")
-    mudotN = get_default_symbol("mudotN")
-
-    @classmethod
-    def deriv_args(cls):
-        return [*beta_xpan.u_func.deriv_args(), cls.lnPi0, cls.mudotN]
-
-    def fdiff(self, argindex=1):
-        (beta,) = self.args
-        return self.mudotN - beta_xpan.u_func(beta, 1)
-
-    @classmethod
-    def eval(cls, beta):
-        return cls.lnPi0 if beta is None else None
+#: lnPi with its derivatives in central moments of u (reference lnpi.py:42-78) / in raw moments (lnpi.py:81-116)
+lnPi_func_central = beta_xpan.register_rule(
+    _lnpi_rule("lnPi_func_central", "u_func_central", lambda F, b: F.u_func_central(b)))
+lnPi_func_raw = beta_xpan.register_rule(_lnpi_rule("lnPi_func_raw", "u_func", lambda F, b: F.u_func(b, 1)))
 
 
 @lru_cache(5)
