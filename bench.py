@@ -483,6 +483,8 @@ NCU_DRAM_BYTES_PER_DRAW = {"bucket_scatter": (0.001503 + 1.255659) * 1e9 / 6.4e8
 def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_info, z, dev) -> None:
     import torch
 
+    from thermoextrap_b200 import kernels as K
+
     peaks = measured_peaks()
     step_ms = t_dev / a.steps * 1e3
     nv = max(a.nchan, 1)
@@ -569,7 +571,11 @@ def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_i
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": t_e2e / e2e_steps * 1e3, "steps": e2e_steps,
                 "path": "DataCentralMomentsVals.from_vals -> beta.factory_extrapmodel -> .resample({'nrep','rng'}) -> "
                         ".predict, from pinned host arrays" + ("" if world == 1 else
-                        f" (parallel.enable(): each rank uploads its 1/{world} row shard, shards all_gathered over NVLink)")},
+                        f" (parallel.enable(): each rank uploads its 1/{world} row shard, shards all_gathered over NVLink)"),
+                "upload": ("x in 16 row chunks on a copy stream: the sampler's integer kernels and the first replicate "
+                           f"window's contraction run behind it chunk by chunk ({K.follow_windows} windows followed an "
+                           "upload in this run); K1 deferred to first use") if K.follow_windows else
+                          "one copy on the compute stream ahead of the kernels"},
         "gpu_launches": int(launches),
         "samples_per_s_reduce": None if not reduce_rec else reduce_rec["samples_per_s"],
         "roofline": roofline,

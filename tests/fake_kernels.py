@@ -20,6 +20,11 @@ def device():
     return torch.device("cpu")
 
 
+def pending_upload(t):
+    """No copy stream on the CPU: nothing is ever in flight."""
+    return None
+
+
 def _np(t):
     if t is None:
         return None

@@ -132,6 +132,35 @@ def test_resample_random_spec_equals_numpy_table(fx):
     assert np.array_equal(s.freq.sum(axis=1), [50] * 3)
 
 
+def test_deferred_reduce_launches_on_first_use(fx, monkeypatch):
+    """K1 of ``from_vals`` may be deferred (samples still uploading: backend.wrap_reduce_vals): building the data
+    object, the model and a bootstrap must not launch it; asking for values does, once, with the same result."""
+    import thermoextrap_b200.backend as backend
+
+    eager = fx.vals()
+    ref_pred = xtrap.beta.factory_extrapmodel(beta=fx.beta0, data=eager).predict(fx.betas).values
+    calls = []
+    real = backend.K.reduce_vals
+
+    def counted(*a, **k):
+        calls.append(1)
+        return real(*a, **k)
+
+    monkeypatch.setattr(backend.K, "reduce_vals", counted)
+    monkeypatch.setattr(backend, "DEFER_REDUCE", True)
+    data = fx.vals()
+    assert not calls and data.dxduave.dims == eager.dxduave.dims and data.dxduave.mom == eager.dxduave.mom
+    assert dict(data.dxduave.sizes) == dict(eager.dxduave.sizes)
+    model = xtrap.beta.factory_extrapmodel(beta=fx.beta0, data=data)
+    boot = model.resample(sampler={"nrep": 4, "rng": np.random.default_rng(1)})
+    assert not calls, "the bootstrap needs the samples, not their comoments"
+    assert boot.predict(fx.betas).sizes["rep"] == 4
+    np.testing.assert_allclose(model.predict(fx.betas).values, ref_pred, rtol=1e-13, atol=0)
+    assert len(calls) == 1
+    np.testing.assert_array_equal(data.dxduave.obj.values, eager.dxduave.obj.values)
+    assert len(calls) == 1 and data.dxduave.device_records() is not None
+
+
 def test_block_resample_and_reduce(fx):
     """DataCentralMoments over pre-reduced blocks (data.py:974-1055; notebook cells 39-41)."""
     xx = DataArray(fx.x[:, 0].reshape(10, 10), dims=("rec", "block"))

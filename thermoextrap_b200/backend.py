@@ -53,6 +53,11 @@ from collections import OrderedDict as _OrderedDict
 _dev_cache: "_OrderedDict[tuple, tuple[Any, bytes, Any]]" = _OrderedDict()
 _dev_cache_on = _os.environ.get("THERMOEXTRAP_B200_DEVICE_CACHE", "1") not in ("", "0")
 _dev_cache_max_bytes: int | None = None   # None: half of the device's memory
+#: large float64 sample arrays are uploaded in chunks on a copy stream, overlapped with the kernels that do not
+#: need them yet (``THERMOEXTRAP_B200_ASYNC_UPLOAD=0``: one copy on the compute stream, as for small arrays)
+ASYNC_UPLOAD = _os.environ.get("THERMOEXTRAP_B200_ASYNC_UPLOAD", "1") not in ("", "0")
+#: test hook: defer K1 of ``wrap_reduce_vals`` even when no upload is in flight
+DEFER_REDUCE = False
 
 #: bytes actually copied host->device / device->host by this module (bench.py reads these)
 transfer_bytes = {"h2d": 0, "d2h": 0}
@@ -92,6 +97,11 @@ def to_device(arr: np.ndarray):
         t = torch.from_numpy(host)
         if host.nbytes >= (1 << 20) and dev.type == "cuda":
             t = t.pin_memory()
+        if (ASYNC_UPLOAD and _dist is None and dev.type == "cuda" and host.dtype == np.float64 and host.ndim >= 1
+                and host.nbytes >= K.ASYNC_UPLOAD_MIN_BYTES):
+            # a large sample array: row chunks on the copy stream; consumers are ordered after it on their own
+            # stream by the kernel wrappers, the wide bootstrap follows it chunk by chunk (kernels.upload_async)
+            return K.upload_async(t, dev)
         return t.to(dev, non_blocking=True)
 
     if not _dev_cache_on:
@@ -122,6 +132,8 @@ def to_device(arr: np.ndarray):
 
 def clear_device_cache() -> None:
     _dev_cache.clear()
+    if hasattr(K, "purge_uploads"):
+        K.purge_uploads()
 
 
 # ------------------------------------------------------------------ N-GPU mode (parallel.enable)
@@ -380,11 +392,41 @@ class CentralMomentsData:
             if d not in obj.dims:
                 msg = f"moment dimension {d!r} not in {obj.dims}"
                 raise ValueError(msg)
-        self.obj = obj.transpose(..., *self.mom_dims)
+        self._obj = obj.transpose(..., *self.mom_dims)
+        self._thunk = None
         # device-resident copy of ``obj.values`` (same shape, dims order ``_dev_dims``) when a kernel of this
         # package produced the array: the fused K7 kernels read it in place (models.ExtrapModel.predict)
         self._dev = None
         self._dev_dims: tuple = ()
+
+    @classmethod
+    def deferred(cls, thunk, *, shape, dims, mom_dims) -> CentralMomentsData:
+        """Comoments whose kernel has not been launched yet: ``thunk()`` launches it and returns the device array
+        ``[*shape]``; it runs (once) when the values, or the device records, are first asked for.  Shape, dims and
+        ``mom`` are known without it."""
+        self = cls.__new__(cls)
+        self.mom_dims = _mom_dims_tuple(mom_dims, len(tuple(mom_dims)))
+        self.mom_ndim = len(self.mom_dims)
+        self._obj = None
+        self._thunk = thunk
+        self._lazy = (tuple(int(n) for n in shape), tuple(dims))
+        self._dev = None
+        self._dev_dims = ()
+        return self
+
+    @property
+    def obj(self) -> DataArray:
+        if self._obj is None:
+            shape, dims = self._lazy
+            dev = self._thunk().reshape(shape)
+            self._thunk = None
+            self._obj = DataArray(_host(dev), dims=dims)
+            self._dev, self._dev_dims = dev, dims
+        return self._obj
+
+    @obj.setter
+    def obj(self, value: DataArray) -> None:
+        self._obj = value
 
     def _set_dev(self, tensor, dims) -> CentralMomentsData:
         if tensor is not None and tuple(dims) == tuple(self.obj.dims) and tuple(tensor.shape) == tuple(self.obj.shape):
@@ -393,6 +435,8 @@ class CentralMomentsData:
 
     def device_records(self):
         """The comoment array on the device (contiguous, dims as ``obj.dims``), or None if it only lives on the host."""
+        if self._obj is None:
+            _ = self.obj   # a deferred kernel: launch it now
         if self._dev is not None and self._dev_dims == tuple(self.obj.dims):
             return self._dev
         return None
@@ -400,11 +444,13 @@ class CentralMomentsData:
     # -- protocol ------------------------------------------------------------
     @property
     def sizes(self):
+        if self._obj is None:
+            return dict(zip(self._lazy[1], self._lazy[0]))
         return self.obj.sizes
 
     @property
     def dims(self):
-        return self.obj.dims
+        return self._lazy[1] if self._obj is None else self.obj.dims
 
     @property
     def values(self):
@@ -412,7 +458,7 @@ class CentralMomentsData:
 
     @property
     def mom(self) -> tuple[int, ...]:
-        return tuple(self.obj.sizes[d] - 1 for d in self.mom_dims)
+        return tuple(self.sizes[d] - 1 for d in self.mom_dims)
 
     def new_like(self, obj: DataArray) -> CentralMomentsData:
         return type(self)(obj, mom_ndim=self.mom_ndim, mom_dims=self.mom_dims)
@@ -555,10 +601,16 @@ def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dim
         msg = f"u has dims {extra} that x lacks"
         raise ValueError(msg)
     if u.ndim == 1:
-        xd, ud = to_device(np.asarray(x.values, dtype=np.float64)), to_device(np.asarray(u.values, dtype=np.float64))
+        ud = to_device(np.asarray(u.values, dtype=np.float64))   # the short array first: x may travel in chunks
+        xd = to_device(np.asarray(x.values, dtype=np.float64))
+        dims = (*rest_dims, *md)
+        if _dist is None and (DEFER_REDUCE or K.pending_upload(xd) is not None):
+            # the samples are still on their way: K1 is queued when its result is first asked for, so that kernels
+            # which do not read the samples (the bootstrap's sampler) are not held up behind it on the stream
+            return CentralMomentsData.deferred(lambda: K.reduce_vals(xd, ud, k, w=wd),
+                                               shape=(*x.shape[1:], 2, k + 1), dims=dims, mom_dims=md)
         dev_out = K.reduce_vals(xd, ud, k, w=wd) if _dist is None else _dist.reduce_vals(xd, ud, k, w=wd)
         out = _host(dev_out)
-        dims = (*rest_dims, *md)
         return CentralMomentsData(DataArray(out, dims=dims), mom_ndim=2, mom_dims=md)._set_dev(
             dev_out.reshape(out.shape), dims)
     if _dist is not None:
@@ -609,8 +661,8 @@ def wrap_resample_vals(
         raise NotImplementedError(msg)
     md = _mom_dims_tuple(mom_dims, 2)
     wd = None if weight is None else to_device(np.ascontiguousarray(weight.values, dtype=np.float64))
-    xd = to_device(np.asarray(x.values, dtype=np.float64))
     ud = to_device(np.asarray(u.values, dtype=np.float64))
+    xd = to_device(np.asarray(x.values, dtype=np.float64))
     dev_out = resample_device(xd, ud, wd, sampler, k)
     out = _host(dev_out)
     rest_dims = x.dims[1:]

@@ -53,9 +53,111 @@ def _ptr(t: torch.Tensor | None) -> int | None:
     return None if t is None else t.data_ptr()
 
 
-def _as_f64(t, dev) -> torch.Tensor:
+# ---------------------------------------------------------------- uploads in flight
+# A large sample array travels host -> device in row chunks on a dedicated copy stream, one event per chunk
+# (backend.to_device).  The device tensor is handed out at once; every wrapper of this module passes its inputs
+# through ``_as_f64``, which makes the launching stream wait for the last chunk.  The wide bootstrap
+# (``sampler_resample_wide``) does better: its integer kernels do not read the samples at all, and its first
+# replicate window contracts chunk after chunk as they land, so the upload hides behind work the job does anyway.
+ASYNC_UPLOAD_MIN_BYTES = 1 << 30
+UPLOAD_CHUNKS = 16
+UPLOAD_TEST_DELAY_CYCLES = 0   # tests: hold the copy stream back this many SM cycles so that consumers find it in flight
+follow_windows = 0             # replicate windows contracted chunk by chunk behind an upload (tests, bench)
+# how many windows follow an upload: enough contraction work to cover the copy (measured on B200: pinned host -> HBM
+# 55 GB/s over PCIe gen5 x16; contraction 32.8 TFLOP/s fp64), within half of the free memory for the extra tables
+FOLLOW_H2D_BYTES_PER_S = 50e9
+FOLLOW_FLOPS_PER_S = 30e12
+FOLLOW_MAX_WINDOWS = 8
+upload_trace: dict | None = None   # tools/e2e_probe.py: set to {} to collect timed events of one upload + follow
+
+
+class _Upload:
+    __slots__ = ("tensor", "src", "bounds", "events", "pivot_rows", "pivot_idx", "pivot_landed", "_keep")
+
+    def __init__(self, tensor, src) -> None:
+        self.tensor, self.src = tensor, src   # both kept alive until the last chunk has landed
+        self.bounds: list = []
+        self.events: list = []
+
+
+def pivot_row_index(nsamp: int, dev=None) -> torch.Tensor:
+    """The <= 256 strided rows whose means txb_pivot_f64 centres the sums on (reduce.cu, k_colmean_sample)."""
+    nrows = min(int(nsamp), 256)
+    return (torch.arange(nrows, dtype=torch.int64, device=dev) * int(nsamp)) // nrows
+
+
+_uploads: dict[int, _Upload] = {}
+_copy_streams: dict[int, torch.cuda.Stream] = {}
+
+
+def _storage_key(t: torch.Tensor) -> int:
+    return t.untyped_storage().data_ptr()
+
+
+def purge_uploads() -> None:
+    """Forget the uploads whose last chunk has landed (releases the references they hold)."""
+    for key in [k for k, up in _uploads.items() if up.events[-1].query()]:
+        del _uploads[key]
+
+
+def upload_async(src: torch.Tensor, dev: torch.device) -> torch.Tensor:
+    """Start the chunked copy of the pinned host tensor ``src[rows, ...]`` and return the device tensor."""
+    purge_uploads()
+    t = torch.empty(src.shape, dtype=src.dtype, device=dev)
+    main = torch.cuda.current_stream(dev)
+    cs = _copy_streams.get(dev.index or 0)
+    if cs is None:
+        cs = _copy_streams[dev.index or 0] = torch.cuda.Stream(dev)
+    cs.wait_stream(main)   # the block may be recycled memory that queued work of this stream still reads
+    rows = src.shape[0]
+    step = -(-(-(-rows // UPLOAD_CHUNKS)) // 4096) * 4096
+    up = _Upload(t, src)
+    # the pivot rows go first (128 KB): a consumer that follows the chunks needs them before any chunk
+    up.pivot_idx = pivot_row_index(rows)
+    up._keep = src.reshape(rows, -1)[up.pivot_idx].pin_memory()
+    up.pivot_rows = torch.empty(up._keep.shape, dtype=src.dtype, device=dev)
+    timed = upload_trace is not None
+    with torch.cuda.stream(cs):
+        if UPLOAD_TEST_DELAY_CYCLES:
+            torch.cuda._sleep(int(UPLOAD_TEST_DELAY_CYCLES))
+        up.pivot_rows.copy_(up._keep, non_blocking=True)
+        up.pivot_landed = torch.cuda.Event(enable_timing=timed)
+        up.pivot_landed.record(cs)
+        for a in range(0, rows, step):
+            b = min(rows, a + step)
+            t[a:b].copy_(src[a:b], non_blocking=True)
+            ev = torch.cuda.Event(enable_timing=timed)
+            ev.record(cs)
+            up.bounds.append((a, b))
+            up.events.append(ev)
+    _uploads[_storage_key(t)] = up
+    return t
+
+
+def pending_upload(t) -> _Upload | None:
+    """The upload still in flight into the storage of ``t``, or None."""
+    if not _uploads or not isinstance(t, torch.Tensor) or not t.is_cuda:
+        return None
+    key = _storage_key(t)
+    up = _uploads.get(key)
+    if up is not None and up.events[-1].query():
+        del _uploads[key]
+        return None
+    return up
+
+
+def wait_upload(t) -> None:
+    """Order the current stream after the upload into ``t`` (no host wait)."""
+    up = pending_upload(t)
+    if up is not None:
+        torch.cuda.current_stream(t.device).wait_event(up.events[-1])
+
+
+def _as_f64(t, dev, wait: bool = True) -> torch.Tensor:
     if isinstance(t, np.ndarray):
         t = torch.from_numpy(np.ascontiguousarray(t, dtype=np.float64))
+    if _uploads and wait:
+        wait_upload(t)
     if t.dtype != torch.float64:
         t = t.to(torch.float64)
     if t.device != dev:
@@ -63,9 +165,9 @@ def _as_f64(t, dev) -> torch.Tensor:
     return t.contiguous()
 
 
-def _layout(x, u, w, dev):
+def _layout(x, u, w, dev, wait: bool = True):
     """Normalise (x, u, w) to x[nsamp, nchan] | None, u[nsamp] | u[nsamp, nchan], w[nsamp] | None."""
-    u = _as_f64(u, dev)
+    u = _as_f64(u, dev, wait)
     nsamp = u.shape[0]
     ldu = 0
     if u.ndim > 1:
@@ -74,7 +176,7 @@ def _layout(x, u, w, dev):
     val_shape: tuple[int, ...] = ()
     nchan = 1
     if x is not None:
-        x = _as_f64(x, dev)
+        x = _as_f64(x, dev, wait)
         if x.shape[0] != nsamp:
             msg = f"x has {x.shape[0]} samples but u has {nsamp}"
             raise ValueError(msg)
@@ -556,14 +658,14 @@ def sampler_freq_cols(plan: SamplerPlan, col_lo: int, col_hi: int, reps=None, dt
     return buf[:, :ncol], rowsum
 
 
-def resample_sums(x, u, freq: torch.Tensor, order: int, pivot: torch.Tensor, w=None):
+def resample_sums(x, u, freq: torch.Tensor, order: int, pivot: torch.Tensor, w=None, wait: bool = True):
     """K2 without the re-centring: additive pivot sums ``(S0[nrep, 1, order+1], S1[nrep, nchan, order+1])`` of
     ``x[nsamp, nchan]``, ``u[nsamp]`` about ``pivot = [cx[nchan], cu]`` reweighted by ``freq[nrep, nsamp]``.  Sums
     about a common pivot add across sample shards (``all_reduce``); :func:`finalize_sums` re-centres the total."""
     global launch_count
     lib = _lib.load()
     dev = device()
-    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev)
+    x, u, w, nsamp, nchan, ldu, val_shape = _layout(x, u, w, dev, wait)
     if x is None or ldu != 0:
         msg = "resample_sums needs x[nsamp, *val] and u[nsamp]"
         raise ValueError(msg)
@@ -727,13 +829,24 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     bootstraps only that slice of the plan's replicates (a rank's share, parallel.bootstrap_sharded).
     """
     dev = device()
-    xs = None if x_is_u else _as_f64(x, dev)
+    xs = None if x_is_u else _as_f64(x, dev, wait=False)
     us = _as_f64(u, dev)
     ndat = us.shape[0]
     plan = _plan_of(src, nrep, ndat if nsamp is None else nsamp, ndat)
     if plan.ndat != ndat:
         msg = f"sampler ndat={plan.ndat} does not match {ndat} samples"
         raise ValueError(msg)
+    # samples still on their way (backend.to_device's chunked upload)?  The sampler kernels do not read them, and
+    # the first window's contraction can follow the chunks as they land
+    arriving = None if xs is None else pending_upload(xs)
+    if arriving is not None and not (timing is None and w is None and us.ndim == 1 and xs.ndim >= 2 and xs.data_ptr() == arriving.tensor.data_ptr()
+                                     and xs.shape == arriving.tensor.shape):
+        wait_upload(xs)
+        arriving = None
+    follow_pivot = None
+    if arriving is not None:
+        torch.cuda.current_stream(dev).wait_event(arriving.pivot_landed)
+        follow_pivot = sample_pivot(arriving.pivot_rows, us[pivot_row_index(ndat, dev)])   # no H2D copy here
     if table_bytes is None:
         table_bytes = free_table_bytes()
     ldf = -(-ndat // 16) * 16
@@ -745,6 +858,21 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     # status reports an overflowed count (a sample drawn > 255 times) or an overflowed bucket list is then redone
     # on the careful path (int32 table / global atomics) -- a < 1e-12 event at bootstrap sizes.
     table = torch.empty((min(win, last - first), ldf), dtype=torch.uint8, device=dev)
+    # following an upload: as many windows as it takes to keep the tensor pipe busy until the last chunk has landed
+    # get a table each and are contracted chunk-major (every chunk against all of them as it lands)
+    extra: list = []
+    if arriving is not None:
+        nchan = int(np.prod(xs.shape[1:], dtype=np.int64))
+        upload_s = xs.numel() * 8 / FOLLOW_H2D_BYTES_PER_S
+        window_s = 2.0 * (order + 1) * (nchan + 1) * ndat * table.shape[0] / FOLLOW_FLOPS_PER_S
+        want_tables = min(-(-(last - first) // win), max(1, int(np.ceil(upload_s / window_s))), FOLLOW_MAX_WINDOWS)
+        # free = what the driver reports + what torch's allocator holds cached (last step's tables come back from there)
+        room = (torch.cuda.mem_get_info(dev)[0] + torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev)) // 2
+        while len(extra) + 1 < want_tables and table.numel() * (len(extra) + 1) <= room:
+            try:
+                extra.append(torch.empty_like(table))
+            except torch.OutOfMemoryError:
+                break
     # scratch of the bucketed histogram, sized once (no driver query per window)
     lib = _lib.load()
     want = lib.txb_sampler_freq_workspace_bytes(plan.ndat, plan.nrep, plan.nsamp, table.shape[0])
@@ -755,6 +883,24 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     pending: list = []
     spans: list = []
     lo = first
+    if arriving is not None:
+        freqs = []
+        for tb in [table, *extra]:
+            if lo >= last:
+                break
+            hi = min(last, lo + win)
+            freqs.append(sampler_freq(plan, dtype=torch.uint8, reps=(lo, hi), out=tb, status_out=pending,
+                                      scratch_bytes=scratch))
+            spans.append((lo, hi))
+            lo = hi
+        parts = _resample_windows_following(arriving, xs, us, freqs, order, follow_pivot)
+        if lo < last or len(parts) > 1:
+            out = torch.empty((last - first, *parts[0].shape[1:]), dtype=torch.float64, device=dev)
+            for (a, b), part in zip(spans, parts):
+                out[a - first : b - first] = part
+        else:
+            out = parts[0]
+        del freqs, parts, extra   # the later windows find the whole array resident (stream order) and share `table`
     while lo < last:
         hi = min(last, lo + win)
         marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if ev is not None else None
@@ -790,6 +936,48 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
         timing["contract_ms"] = sum(m[1].elapsed_time(m[2]) for m in ev)
         timing["windows"] = len(ev)
     return out
+
+
+def sample_pivot(x, u) -> torch.Tensor:
+    """``[cx[nchan], cu]``: the strided-subsample means the kernels centre their sums on (txb_pivot_f64)."""
+    lib = _lib.load()
+    dev = device()
+    x, u, _, nsamp, nchan, ldu, _ = _layout(x, u, None, dev)
+    pivot = torch.empty(nchan + (nchan if ldu else 1), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.txb_pivot_f64(_ptr(x), _ptr(u), nsamp, nchan, nchan, ldu, pivot.data_ptr(), _stream_ptr()),
+              "txb_pivot_f64")
+    return pivot
+
+
+def _resample_windows_following(up: _Upload, xs, us, freqs: list, order: int, pivot) -> list:
+    """Replicate windows of :func:`sampler_resample_wide` contracted WHILE the samples upload: pivot sums are
+    additive over samples, so every row chunk is contracted against each window's table as soon as its copy has
+    landed (the stream waits on that chunk's event only) and the windows are re-centred once at the end.  The pivot
+    is the one the resident path computes -- the means of the same <= 256 strided rows, uploaded ahead of the
+    chunks -- so the two paths differ only in the order the partial sums are added."""
+    global follow_windows
+    follow_windows += len(freqs)
+    main = torch.cuda.current_stream(xs.device)
+    sums: list = [None] * len(freqs)
+    trace = upload_trace
+    if trace is not None:
+        trace.update(t0=up.pivot_landed, landed=list(up.events), done=[], start=torch.cuda.Event(enable_timing=True),
+                     windows=len(freqs))
+        trace["start"].record(main)
+    for (a, b), landed in zip(up.bounds, up.events):
+        main.wait_event(landed)
+        for i, freq in enumerate(freqs):
+            s0, s1, _ = resample_sums(xs[a:b], us[a:b], freq[:, a:b], order, pivot, wait=False)
+            if sums[i] is None:
+                sums[i] = (s0, s1)
+            else:
+                sums[i][0].add_(s0)
+                sums[i][1].add_(s1)
+        if trace is not None:
+            trace["done"].append(torch.cuda.Event(enable_timing=True))
+            trace["done"][-1].record(main)
+    return [finalize_sums(pivot, s0, s1, order, x_is_u=False, val_shape=tuple(xs.shape[1:])) for s0, s1 in sums]
 
 
 def _resample_window_careful(plan, xs, us, order, w, x_is_u, lo, hi, overflow: bool) -> torch.Tensor:
