@@ -573,7 +573,7 @@ def emit(a, world, t_dev, t_e2e, e2e_steps, kernels, launches, h2d, d2h, clock_i
                         ".predict, from pinned host arrays" + ("" if world == 1 else
                         f" (parallel.enable(): each rank uploads its 1/{world} row shard, shards all_gathered over NVLink)"),
                 "upload": ("x in 16 row chunks on a copy stream: the sampler's integer kernels and the first replicate "
-                           f"window's contraction run behind it chunk by chunk ({K.follow_windows} windows followed an "
+                           f"windows' contraction run behind it chunk by chunk ({K.follow_windows} windows followed an "
                            "upload in this run); K1 deferred to first use") if K.follow_windows else
                           "one copy on the compute stream ahead of the kernels"},
         "gpu_launches": int(launches),
