@@ -92,3 +92,27 @@ def test_integer_tables_take_the_plain_copy(small_async):
     idx = np.random.default_rng(0).integers(0, 1000, size=(300, 1000))   # 2.4 MB of int64
     t = backend.to_device(idx)
     assert K.pending_upload(t) is None and torch.equal(t.cpu(), torch.from_numpy(idx))
+
+
+def test_following_windows_with_trailing_value_dims(small_async, monkeypatch):
+    """x[rec, val, deriv] (the xalpha layout): the followed windows flatten the trailing dims like the resident path."""
+    backend, K = small_async
+    n, nrep, order = 12_000, 200, 3
+    rng = np.random.default_rng(5)
+    u = rng.normal(size=n) + 2.0
+    x = rng.normal(size=(n, 6, 3)) + 0.2 * u[:, None, None]
+    plan = lambda: K.SamplerPlan(np.random.default_rng(3), nrep, n)   # noqa: E731
+    ud = backend.to_device(u)
+    xd = backend.to_device(x)                      # 1.7 MB: chunked, held back by the artificial delay
+    assert K.pending_upload(xd) is not None
+    before = K.follow_windows
+    got = K.sampler_resample_wide(plan(), xd, ud, order=order, table_bytes=128 * n)
+    assert K.follow_windows == before + 2 and got.shape == (nrep, 6, 3, 2, order + 1)
+    torch.cuda.synchronize()
+    ref = K.sampler_resample_wide(plan(), xd, ud, order=order, table_bytes=128 * n)   # resident now
+    assert K.follow_windows == before + 2
+    from oracle import comoments as oc
+
+    scale = oc.tolerance_scale(x, u, order)
+    g, r = got.cpu().numpy(), ref.cpu().numpy()
+    assert np.all(np.abs(g - r) <= 1e-12 * np.maximum(np.abs(r), scale[None]))
