@@ -161,6 +161,16 @@ def test_deferred_reduce_launches_on_first_use(fx, monkeypatch):
     assert len(calls) == 1 and data.dxduave.device_records() is not None
 
 
+def test_pinned_empty_is_a_plain_numpy_array():
+    import thermoextrap_b200.backend as backend
+
+    a = backend.pinned_empty((7, 3))
+    assert isinstance(a, np.ndarray) and a.shape == (7, 3) and a.dtype == np.float64 and a.flags.c_contiguous
+    a[:] = 2.5
+    assert float(a.sum()) == 52.5
+    assert backend.pinned_empty(5, np.int64).shape == (5,)
+
+
 def test_block_resample_and_reduce(fx):
     """DataCentralMoments over pre-reduced blocks (data.py:974-1055; notebook cells 39-41)."""
     xx = DataArray(fx.x[:, 0].reshape(10, 10), dims=("rec", "block"))

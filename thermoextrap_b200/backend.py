@@ -130,6 +130,20 @@ def to_device(arr: np.ndarray):
     return t
 
 
+def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
+    """Uninitialised host array in page-locked memory.  ``to_device`` copies from such arrays without staging, and
+    large float64 sample arrays in them travel asynchronously, hidden behind the kernels (pageable arrays are
+    snapshotted into pinned memory first, a host-side copy of the whole array).  Plain numpy otherwise; without a
+    CUDA device it is ordinary memory."""
+    import torch
+
+    t = torch.empty(tuple(np.atleast_1d(shape)) if np.ndim(shape) else (int(shape),),
+                    dtype=getattr(torch, np.dtype(dtype).name))
+    if torch.cuda.is_available():
+        t = t.pin_memory()
+    return t.numpy()
+
+
 def clear_device_cache() -> None:
     _dev_cache.clear()
     if hasattr(K, "purge_uploads"):
