@@ -13,7 +13,9 @@ metric: bootstrap replicates/s of the WHOLE job.  N > 1 is STRONG scaling: the s
 sharded (each rank bootstraps nrep / N replicates of the ONE numpy table), slabs all_gathered.
 ``value`` times K1 + K6 + K2 with the samples resident in HBM; ``e2e`` times the public API call chain from pinned
 HOST arrays to HOST predictions (H2D + every kernel + K7 + D2H inside the timed region; with N > 1 every rank
-uploads its 1/N row shard and the shards are exchanged over NVLink).
+uploads its 1/N row shard and the shards are exchanged over NVLink).  At N = 1 the API hides the upload: x travels in
+chunks on a copy stream while the sampler kernels run and the first replicate windows contract each chunk as it
+lands -- still every byte inside the timed region, counted in ``h2d_bytes_per_step``.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config target|c2]
 
