@@ -25,6 +25,10 @@ def pending_upload(t):
     return None
 
 
+def wait_upload(t):
+    return None
+
+
 def _np(t):
     if t is None:
         return None

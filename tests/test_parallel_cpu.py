@@ -96,6 +96,28 @@ def _worker(rank, world, port, out_dir):
         # an explicit index table over the GLOBAL row numbering
         b2 = model.resample(sampler={"indices": idx}).data.dxduave.obj.values
         assert np.all(np.abs(b2 - wref) <= 1e-9 * np.maximum(np.abs(wref), oc.tolerance_scale(x, u, order)))
+        # opt-in N-GPU upload pipeline, host logic: K1 (collectives included) deferred at from_vals, launched by the
+        # flush at the end of the bootstrap -- on every rank, in the same order
+        backend.ASYNC_UPLOAD_DIST, backend.DEFER_REDUCE = True, True
+        calls = []
+        real = fake_kernels.reduce_sums
+
+        def counted(*a, **k):
+            calls.append(1)
+            return real(*a, **k)
+
+        fake_kernels.reduce_sums = counted
+        try:
+            data2 = xt.DataCentralMomentsVals.from_vals(xv=xv, uv=uv, order=order, central=True)
+            assert not calls and data2.dxduave.mom == (1, order)
+            boot2 = xt.beta.factory_extrapmodel(beta=0.5, data=data2).resample(
+                sampler={"nrep": nrep, "rng": np.random.default_rng(123)})
+            assert calls and data2.dxduave._obj is not None and not backend._deferred   # flushed by the bootstrap
+            assert np.array_equal(boot2.data.dxduave.obj.values, bv)
+            assert np.array_equal(data2.dxduave.obj.values, got)
+        finally:
+            fake_kernels.reduce_sums = real
+            backend.ASYNC_UPLOAD_DIST, backend.DEFER_REDUCE = False, False
     finally:
         par.disable()
     (Path(out_dir) / f"ok{rank}").write_text("ok")

@@ -56,8 +56,22 @@ _dev_cache_max_bytes: int | None = None   # None: half of the device's memory
 #: large float64 sample arrays are uploaded in chunks on a copy stream, overlapped with the kernels that do not
 #: need them yet (``THERMOEXTRAP_B200_ASYNC_UPLOAD=0``: one copy on the compute stream, as for small arrays)
 ASYNC_UPLOAD = _os.environ.get("THERMOEXTRAP_B200_ASYNC_UPLOAD", "1") not in ("", "0")
+#: opt-in: the same in N-GPU mode (``parallel.enable()``): shards are uploaded in chunks, all-gathered chunk by chunk
+#: on a side stream and contracted as they arrive; K1 -- collectives included -- is deferred until the bootstrap has
+#: been queued (or until its values are asked for, which must then happen on EVERY rank).  Off by default.
+ASYNC_UPLOAD_DIST = _os.environ.get("THERMOEXTRAP_B200_ASYNC_UPLOAD_DIST", "0") not in ("", "0")
 #: test hook: defer K1 of ``wrap_reduce_vals`` even when no upload is in flight
 DEFER_REDUCE = False
+_deferred: list = []   # weak references to deferred comoment records of N-GPU mode, flushed at collective points
+
+
+def flush_deferred() -> None:
+    """Launch every deferred K1 of N-GPU mode (their collectives must be issued by all ranks in the same order)."""
+    pending, _deferred[:] = list(_deferred), []
+    for ref in pending:
+        rec = ref()
+        if rec is not None:
+            _ = rec.obj
 
 #: bytes actually copied host->device / device->host by this module (bench.py reads these)
 transfer_bytes = {"h2d": 0, "d2h": 0}
@@ -97,7 +111,7 @@ def to_device(arr: np.ndarray):
         t = torch.from_numpy(host)
         if host.nbytes >= (1 << 20) and dev.type == "cuda":
             t = t.pin_memory()
-        if (ASYNC_UPLOAD and _dist is None and dev.type == "cuda" and host.dtype == np.float64 and host.ndim >= 1
+        if (ASYNC_UPLOAD and (_dist is None or ASYNC_UPLOAD_DIST) and dev.type == "cuda" and host.dtype == np.float64 and host.ndim >= 1
                 and host.nbytes >= K.ASYNC_UPLOAD_MIN_BYTES):
             # a large sample array: row chunks on the copy stream; consumers are ordered after it on their own
             # stream by the kernel wrappers, the wide bootstrap follows it chunk by chunk (kernels.upload_async)
@@ -618,11 +632,16 @@ def wrap_reduce_vals(x, *y, mom, weight=None, axis=MISSING, dim=MISSING, mom_dim
         ud = to_device(np.asarray(u.values, dtype=np.float64))   # the short array first: x may travel in chunks
         xd = to_device(np.asarray(x.values, dtype=np.float64))
         dims = (*rest_dims, *md)
-        if _dist is None and (DEFER_REDUCE or K.pending_upload(xd) is not None):
+        if (_dist is None or ASYNC_UPLOAD_DIST) and (DEFER_REDUCE or K.pending_upload(xd) is not None):
             # the samples are still on their way: K1 is queued when its result is first asked for, so that kernels
             # which do not read the samples (the bootstrap's sampler) are not held up behind it on the stream
-            return CentralMomentsData.deferred(lambda: K.reduce_vals(xd, ud, k, w=wd),
-                                               shape=(*x.shape[1:], 2, k + 1), dims=dims, mom_dims=md)
+            mode = _dist
+            rec = CentralMomentsData.deferred(
+                lambda: K.reduce_vals(xd, ud, k, w=wd) if mode is None else mode.reduce_vals(xd, ud, k, w=wd),
+                shape=(*x.shape[1:], 2, k + 1), dims=dims, mom_dims=md)
+            if mode is not None:
+                _deferred.append(weakref.ref(rec))
+            return rec
         dev_out = K.reduce_vals(xd, ud, k, w=wd) if _dist is None else _dist.reduce_vals(xd, ud, k, w=wd)
         out = _host(dev_out)
         return CentralMomentsData(DataArray(out, dims=dims), mom_ndim=2, mom_dims=md)._set_dev(

@@ -72,12 +72,16 @@ upload_trace: dict | None = None   # tools/e2e_probe.py: set to {} to collect ti
 
 
 class _Upload:
-    __slots__ = ("tensor", "src", "bounds", "events", "pivot_rows", "pivot_idx", "pivot_landed", "_keep")
+    __slots__ = ("tensor", "src", "bounds", "events", "pivot_rows", "pivot_idx", "pivot_landed", "_keep", "pivot",
+                 "eta_bytes")
 
     def __init__(self, tensor, src) -> None:
         self.tensor, self.src = tensor, src   # both kept alive until the last chunk has landed
-        self.bounds: list = []
-        self.events: list = []
+        self.bounds: list = []                # row ranges in arrival order ...
+        self.events: list = []                # ... and the event that marks each one landed
+        self.pivot = None                     # a ready-made pivot (parallel.py's gathered arrivals), else from pivot_rows
+        self.pivot_landed = None
+        self.eta_bytes = None                 # bytes still to cross PCIe into this GPU (None: the whole tensor)
 
 
 def pivot_row_index(nsamp: int, dev=None) -> torch.Tensor:
@@ -844,7 +848,9 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
         wait_upload(xs)
         arriving = None
     follow_pivot = None
-    if arriving is not None:
+    if arriving is not None and arriving.pivot is not None:
+        follow_pivot = arriving.pivot
+    elif arriving is not None:
         torch.cuda.current_stream(dev).wait_event(arriving.pivot_landed)
         follow_pivot = sample_pivot(arriving.pivot_rows, us[pivot_row_index(ndat, dev)])   # no H2D copy here
     if table_bytes is None:
@@ -863,7 +869,7 @@ def sampler_resample_wide(src, x, u, nrep: int | None = None, order: int = 1, w=
     extra: list = []
     if arriving is not None:
         nchan = int(np.prod(xs.shape[1:], dtype=np.int64))
-        upload_s = xs.numel() * 8 / FOLLOW_H2D_BYTES_PER_S
+        upload_s = (arriving.eta_bytes or xs.numel() * 8) / FOLLOW_H2D_BYTES_PER_S
         window_s = 2.0 * (order + 1) * (nchan + 1) * ndat * table.shape[0] / FOLLOW_FLOPS_PER_S
         want_tables = min(-(-(last - first) // win), max(1, int(np.ceil(upload_s / window_s))), FOLLOW_MAX_WINDOWS)
         # free = what the driver reports + what torch's allocator holds cached (last step's tables come back from there)
@@ -962,8 +968,8 @@ def _resample_windows_following(up: _Upload, xs, us, freqs: list, order: int, pi
     sums: list = [None] * len(freqs)
     trace = upload_trace
     if trace is not None:
-        trace.update(t0=up.pivot_landed, landed=list(up.events), done=[], start=torch.cuda.Event(enable_timing=True),
-                     windows=len(freqs))
+        trace.update(t0=up.pivot_landed or up.events[0], landed=list(up.events), done=[],
+                     start=torch.cuda.Event(enable_timing=True), windows=len(freqs))
         trace["start"].record(main)
     for (a, b), landed in zip(up.bounds, up.events):
         main.wait_event(landed)
