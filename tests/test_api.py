@@ -159,6 +159,14 @@ def test_deferred_reduce_launches_on_first_use(fx, monkeypatch):
     assert len(calls) == 1
     np.testing.assert_array_equal(data.dxduave.obj.values, eager.dxduave.obj.values)
     assert len(calls) == 1 and data.dxduave.device_records() is not None
+    # a deferred record pickles as its values
+    import pickle
+
+    lazy = fx.vals().dxduave
+    assert lazy._obj is None
+    back = pickle.loads(pickle.dumps(lazy))
+    np.testing.assert_array_equal(back.obj.values, eager.dxduave.obj.values)
+    assert back.mom_dims == eager.dxduave.mom_dims and back.device_records() is None
 
 
 def test_pinned_empty_is_a_plain_numpy_array():

@@ -456,6 +456,12 @@ class CentralMomentsData:
     def obj(self, value: DataArray) -> None:
         self._obj = value
 
+    def __getstate__(self) -> dict:
+        """Pickle / copy the VALUES: a deferred kernel is launched first, the device copy stays behind."""
+        state = dict(self.__dict__, _obj=self.obj)
+        state.update(_thunk=None, _dev=None, _dev_dims=())
+        return state
+
     def _set_dev(self, tensor, dims) -> CentralMomentsData:
         if tensor is not None and tuple(dims) == tuple(self.obj.dims) and tuple(tensor.shape) == tuple(self.obj.shape):
             self._dev, self._dev_dims = tensor, tuple(dims)
