@@ -16,7 +16,7 @@ def small_async(monkeypatch):
 
     monkeypatch.setattr(K, "ASYNC_UPLOAD_MIN_BYTES", 1 << 20)
     monkeypatch.setattr(K, "UPLOAD_CHUNKS", 4)
-    monkeypatch.setattr(K, "UPLOAD_TEST_DELAY_CYCLES", 1_000_000_000)   # ~0.5 s
+    monkeypatch.setattr(K, "UPLOAD_TEST_DELAY_CYCLES", 2_000_000_000)   # ~1 s
     monkeypatch.setattr(backend, "ASYNC_UPLOAD", True)
     backend.clear_device_cache()
     yield backend, K
@@ -102,11 +102,12 @@ def test_following_windows_with_trailing_value_dims(small_async, monkeypatch):
     u = rng.normal(size=n) + 2.0
     x = rng.normal(size=(n, 6, 3)) + 0.2 * u[:, None, None]
     plan = lambda: K.SamplerPlan(np.random.default_rng(3), nrep, n)   # noqa: E731
+    first = plan()                                 # built (and its kernels loaded) before the clock of the delay starts
     ud = backend.to_device(u)
     xd = backend.to_device(x)                      # 1.7 MB: chunked, held back by the artificial delay
     assert K.pending_upload(xd) is not None
     before = K.follow_windows
-    got = K.sampler_resample_wide(plan(), xd, ud, order=order, table_bytes=128 * n)
+    got = K.sampler_resample_wide(first, xd, ud, order=order, table_bytes=128 * n)
     assert K.follow_windows == before + 2 and got.shape == (nrep, 6, 3, 2, order + 1)
     torch.cuda.synchronize()
     ref = K.sampler_resample_wide(plan(), xd, ud, order=order, table_bytes=128 * n)   # resident now
