@@ -99,7 +99,13 @@ def _fingerprint(host: np.ndarray) -> bytes:
 
 def to_device(arr: np.ndarray):
     """Device copy of a host array: uploaded per call, or -- when the validated cache is on and the same
-    host buffer is seen again with unchanged (fingerprinted) contents -- the copy already resident."""
+    host buffer is seen again with unchanged (fingerprinted) contents -- the copy already resident.
+
+    Arrays of 1 MiB and more go through pinned memory (a pageable array is snapshotted into a pinned buffer).  A
+    float64 array of ``kernels.ASYNC_UPLOAD_MIN_BYTES`` (1 GiB) and more is copied in row chunks on a copy stream and
+    the tensor is returned while the copy runs: the kernel wrappers order their stream after it, the wide bootstrap
+    follows it chunk by chunk (``kernels.upload_async``).  The host array must then stay untouched until the first
+    result computed from it has been read."""
     import torch
 
     arr = np.asarray(arr)
